@@ -1,0 +1,284 @@
+"""oracle/oracle.py — TEST INFRASTRUCTURE: numpy/ctypes front-end of the parity checkers.
+
+Three libraries, none of them product code:
+  libffemb_oracle.so            plain-C restatement (oracle/ffemb_oracle.c), always available
+  _ref/libffref_cpu[_ndebug].so the reference's own src/ops/embedding.cc, compiled unmodified
+  _ref/libffref_gpu.so          the reference's own src/ops/embedding.cu (+ zero-fill, sgd_update)
+                                for sm_100a; device pointers only (GPU box)
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import
+this module.  Reference line numbers are cited in the C sources.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+AGGR_NONE, AGGR_SUM, AGGR_AVG, AGGR_MEAN = 20, 21, 22, 122
+
+_i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+_i64, _int, _f32 = C.c_int64, C.c_int, C.c_float
+
+
+def build(ref=True):
+    """make oracle (+ ref when /root/reference is present). Returns the list of built libs."""
+    targets = ["oracle"]
+    if ref and os.path.isdir("/root/reference/src/ops"):
+        targets.append("ref")
+    subprocess.run(["make", "-s", "-C", HERE] + targets, check=True,
+                   stdout=subprocess.DEVNULL, stderr=subprocess.PIPE)
+    return [p for p in (os.path.join(HERE, "libffemb_oracle.so"),
+                        os.path.join(HERE, "_ref", "libffref_cpu.so"),
+                        os.path.join(HERE, "_ref", "libffref_cpu_ndebug.so"),
+                        os.path.join(HERE, "_ref", "libffref_gpu.so")) if os.path.exists(p)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(HERE, "libffemb_oracle.so")
+        if not os.path.exists(path):
+            build(ref=False)
+        L = C.CDLL(path)
+        L.oracle_embed_forward.argtypes = [_i64p, _f32p, _f32p, _i64, _i64, _i64, _int, _i64]
+        L.oracle_embed_backward.argtypes = [_i64p, _f32p, _f32p, _i64, _i64, _i64, _int, _i64]
+        L.oracle_embed_backward_f64.argtypes = [_i64p, _f32p, _f64p, _i64, _i64, _i64, _int, _i64]
+        L.oracle_sgd_update.argtypes = [_i64, _f32, _f32, _f32, _int, _f32p, C.c_void_p, _f32p, _int]
+        L.oracle_sgd_update.restype = None
+        L.oracle_reference_step.argtypes = [_i64p, _f32p, _f32p, _f32p, _i64, _i64, _i64, _i64,
+                                            _int, _f32, _int]
+        L.oracle_table_owner.argtypes = [_i64, _i64]
+        L.oracle_batch_block.argtypes = [_i64, _i64, _i64, C.POINTER(_i64), C.POINTER(_i64)]
+        L.oracle_batch_block.restype = None
+        L.oracle_rows_per_shard.argtypes = [_i64, _i64]
+        L.oracle_rows_per_shard.restype = _i64
+        L.oracle_row_owner.argtypes = [_i64, _i64, _i64]
+        L.oracle_row_local.argtypes = [_i64, _i64, _i64]
+        L.oracle_row_local.restype = _i64
+        L.oracle_route_rows.argtypes = [_i64p, _i64, _i64, _i64, _i64p, _i64p, _i64p]
+        L.oracle_count_unique.argtypes = [_i64p, _i64]
+        L.oracle_count_unique.restype = _i64
+        L.oracle_concat_forward.argtypes = [_f32p, C.POINTER(C.c_void_p), _i64p, _i64, _i64]
+        L.oracle_concat_forward.restype = None
+        L.oracle_concat_backward.argtypes = [_f32p, C.POINTER(C.c_void_p), _i64p, _i64, _i64]
+        L.oracle_concat_backward.restype = None
+        _lib = L
+    return _lib
+
+
+def _chk(rc):
+    if rc == 1:
+        raise ValueError("oracle: invalid aggr mode (reference asserts aggr == AGGR_MODE_AVG)")
+    if rc == 2:
+        raise IndexError("oracle: index out of range")
+
+
+def _shape(idx, W):
+    idx = np.ascontiguousarray(idx, np.int64)
+    assert idx.ndim == 2 and W.ndim == 2
+    return idx, idx.shape[0], idx.shape[1], W.shape[0], W.shape[1]
+
+
+def forward(idx, W, aggr=AGGR_SUM, check_range=True):
+    """embed_forward (src/ops/embedding.cu:166-190). idx [B][L] int64, W [R][D] f32 -> [B][D]."""
+    W = np.ascontiguousarray(W, np.float32)
+    idx, B, L, R, D = _shape(idx, W)
+    out = np.empty((B, D), np.float32)
+    _chk(lib().oracle_embed_forward(idx, out, W, L, D, B, aggr, R if check_range else 0))
+    return out
+
+
+def backward_dense(idx, outgrad, R, aggr=AGGR_SUM, Wgrad=None):
+    """embed_backward (src/ops/embedding.cu:192-217) into a dense [R][D] gradient."""
+    idx = np.ascontiguousarray(idx, np.int64)
+    outgrad = np.ascontiguousarray(outgrad, np.float32)
+    B, L = idx.shape
+    D = outgrad.shape[1]
+    if Wgrad is None:
+        Wgrad = np.zeros((R, D), np.float32)
+    _chk(lib().oracle_embed_backward(idx, outgrad, Wgrad, L, D, B, aggr, R))
+    return Wgrad
+
+
+def backward_dense_f64(idx, outgrad, R, aggr=AGGR_SUM):
+    idx = np.ascontiguousarray(idx, np.int64)
+    outgrad = np.ascontiguousarray(outgrad, np.float32)
+    B, L = idx.shape
+    D = outgrad.shape[1]
+    Wgrad = np.zeros((R, D), np.float64)
+    _chk(lib().oracle_embed_backward_f64(idx, outgrad, Wgrad, L, D, B, aggr, R))
+    return Wgrad
+
+
+def sgd_update(W, Wgrad, lr, weight_decay=0.0, use_fma=True):
+    """sgd_update (src/runtime/optimizer_kernel.cu:23-41), momentum 0. Returns the new table."""
+    W = np.array(W, np.float32, order="C", copy=True)
+    Wgrad = np.ascontiguousarray(Wgrad, np.float32)
+    lib().oracle_sgd_update(W.size, lr, weight_decay, 0.0, 0, Wgrad.reshape(-1), None,
+                            W.reshape(-1), int(use_fma))
+    return W
+
+
+def reference_step(idx, outgrad, W, aggr=AGGR_SUM, lr=0.01, use_fma=True):
+    """zero-fill -> embed_backward -> sgd_update: the table after one reference step."""
+    W = np.array(W, np.float32, order="C", copy=True)
+    idx, B, L, R, D = _shape(idx, W)
+    outgrad = np.ascontiguousarray(outgrad, np.float32)
+    scratch = np.empty((R, D), np.float32)
+    _chk(lib().oracle_reference_step(idx, outgrad, W, scratch, L, D, B, R, aggr, lr, int(use_fma)))
+    return W
+
+
+def table_owner(t, G):
+    return lib().oracle_table_owner(t, G)
+
+
+def batch_block(B, G, g):
+    lo, hi = _i64(), _i64()
+    lib().oracle_batch_block(B, G, g, C.byref(lo), C.byref(hi))
+    return lo.value, hi.value
+
+
+def rows_per_shard(R, G):
+    return lib().oracle_rows_per_shard(R, G)
+
+
+def route_rows(idx_flat, R, G):
+    idx_flat = np.ascontiguousarray(idx_flat, np.int64).reshape(-1)
+    n = idx_flat.size
+    offsets = np.zeros(G + 1, np.int64)
+    perm = np.empty(n, np.int64)
+    local = np.empty(n, np.int64)
+    _chk(lib().oracle_route_rows(idx_flat, n, R, G, offsets, perm, local))
+    return offsets, perm, local
+
+
+def count_unique(idx):
+    idx = np.ascontiguousarray(idx, np.int64).reshape(-1)
+    return lib().oracle_count_unique(idx, idx.size)
+
+
+def concat_forward(inputs):
+    """Concat axis=1 (src/ops/concat.cu:211-251): [B][w_i] inputs -> [B][sum w_i]."""
+    inputs = [np.ascontiguousarray(x, np.float32) for x in inputs]
+    B = inputs[0].shape[0]
+    widths = np.array([x.shape[1] for x in inputs], np.int64)
+    out = np.empty((B, int(widths.sum())), np.float32)
+    ptrs = (C.c_void_p * len(inputs))(*[x.ctypes.data for x in inputs])
+    lib().oracle_concat_forward(out, ptrs, widths, len(inputs), B)
+    return out
+
+
+def concat_backward(out_grad, widths):
+    out_grad = np.ascontiguousarray(out_grad, np.float32)
+    B = out_grad.shape[0]
+    widths = np.array(widths, np.int64)
+    grads = [np.zeros((B, int(w)), np.float32) for w in widths]
+    ptrs = (C.c_void_p * len(grads))(*[g.ctypes.data for g in grads])
+    lib().oracle_concat_backward(out_grad, ptrs, widths, len(grads), B)
+    return grads
+
+
+# ------------------------------------------------------------------------------------------
+# The reference's own code (oracle/_ref). CPU: numpy arrays. GPU: raw device pointers (ints).
+# ------------------------------------------------------------------------------------------
+_ref_cpu = {}
+_ref_gpu = None
+_vp = C.c_void_p
+
+
+def ref_cpu_available(ndebug=False):
+    return os.path.exists(os.path.join(HERE, "_ref",
+                                       "libffref_cpu_ndebug.so" if ndebug else "libffref_cpu.so"))
+
+
+def ref_cpu(ndebug=False):
+    """libffref_cpu.so (asserts on: idx < 1,000,000, bag 1) or the -DNDEBUG build."""
+    if ndebug not in _ref_cpu:
+        name = "libffref_cpu_ndebug.so" if ndebug else "libffref_cpu.so"
+        L = C.CDLL(os.path.join(HERE, "_ref", name))
+        L.ffref_cpu_forward_task.argtypes = [_i64p, _f32p, _f32p, _i64, _i64, _i64, _i64]
+        L.ffref_cpu_forward_task.restype = None
+        L.ffref_cpu_backward_task.argtypes = [_i64p, _f32p, _f32p, _i64, _i64, _i64, _i64]
+        L.ffref_cpu_backward_task.restype = None
+        L.ffref_cpu_lookup.argtypes = [_i64p, _f32p, _f32p, _i64, _i64, _i64, _i64, _int]
+        L.ffref_cpu_lookup.restype = None
+        L.ffref_cpu_run_tables.argtypes = [_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
+                                           C.POINTER(_vp), C.POINTER(_vp), _i64p, _i64, _i64,
+                                           _i64, _int, _int, _int, _int]
+        L.ffref_cpu_run_tables.restype = C.c_double
+        _ref_cpu[ndebug] = L
+    return _ref_cpu[ndebug]
+
+
+def ref_cpu_forward_task(idx, W, ndebug=False):
+    """Embedding::forward_task_cpu (src/ops/embedding.cc:377-415); bag size must be 1."""
+    W = np.ascontiguousarray(W, np.float32)
+    idx, B, L, R, D = _shape(idx, W)
+    out = np.full((B, D), np.nan, np.float32)
+    ref_cpu(ndebug).ffref_cpu_forward_task(idx, out, W, L, D, B, R)
+    return out
+
+
+def ref_cpu_backward_task(idx, outgrad, Wgrad, ndebug=False):
+    """Embedding::backward_task_cpu (src/ops/embedding.cc:417-453); accumulates into Wgrad."""
+    idx = np.ascontiguousarray(idx, np.int64)
+    outgrad = np.ascontiguousarray(outgrad, np.float32)
+    B, L = idx.shape
+    R, D = Wgrad.shape
+    ref_cpu(ndebug).ffref_cpu_backward_task(idx, outgrad, Wgrad, L, D, B, R)
+    return Wgrad
+
+
+def ref_cpu_lookup(idx, W, normalize=False, ndebug=True):
+    """EmbeddingLookup_int64_t_float_float__avx2_fma (src/ops/embedding.cc:23-319) directly."""
+    W = np.ascontiguousarray(W, np.float32)
+    idx, B, L, R, D = _shape(idx, W)
+    out = np.full((B, D), np.nan, np.float32)
+    ref_cpu(ndebug).ffref_cpu_lookup(idx, out, W, L, D, B, R, int(normalize))
+    return out
+
+
+def ref_cpu_run_tables(idx_batches, outs, Ws, outgrads, Wgrads, P, steps, fwd_only=False,
+                       ndebug=False):
+    """Time the reference CPU tasks: table t on worker thread t % P (see ref_glue_cpu.cc).
+    idx_batches[t]: int64 [nbatches][B][L]."""
+    T = len(Ws)
+    nb, B, L = idx_batches[0].shape
+    D = Ws[0].shape[1]
+    arr = lambda xs: (_vp * T)(*[x.ctypes.data for x in xs])
+    R = np.array([w.shape[0] for w in Ws], np.int64)
+    return ref_cpu(ndebug).ffref_cpu_run_tables(T, arr(idx_batches), arr(outs), arr(Ws),
+                                                arr(outgrads), arr(Wgrads), R, L, D, B, P, steps,
+                                                nb, int(fwd_only))
+
+
+def ref_gpu_available():
+    return os.path.exists(os.path.join(HERE, "_ref", "libffref_gpu.so"))
+
+
+def ref_gpu():
+    """libffref_gpu.so: all arguments are device pointers passed as ints (tensor.data_ptr())."""
+    global _ref_gpu
+    if _ref_gpu is None:
+        L = C.CDLL(os.path.join(HERE, "_ref", "libffref_gpu.so"))
+        L.ffref_gpu_forward_task.argtypes = [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _int]
+        L.ffref_gpu_forward_task.restype = None
+        L.ffref_gpu_backward_task.argtypes = [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _int]
+        L.ffref_gpu_backward_task.restype = None
+        L.ffref_gpu_forward_kernel.argtypes = [_vp, _vp, _vp, _int, _int, _int, _int, _vp]
+        L.ffref_gpu_forward_kernel.restype = None
+        L.ffref_gpu_backward_kernel.argtypes = [_vp, _vp, _vp, _int, _int, _int, _int, _vp]
+        L.ffref_gpu_backward_kernel.restype = None
+        L.ffref_gpu_zero_task.argtypes = [_vp, _i64, _i64]
+        L.ffref_gpu_zero_task.restype = None
+        L.ffref_gpu_sgd_task.argtypes = [_vp, _vp, _i64, _i64, C.c_double, C.c_double]
+        L.ffref_gpu_sgd_task.restype = None
+        _ref_gpu = L
+    return _ref_gpu
