@@ -1,0 +1,265 @@
+// ffemb_api.cu — the extern "C" surface of libffemb.so (include/ffemb.h): argument checking,
+// descriptor packing, error text.  No allocation, no synchronisation, no device selection.
+#include <stdarg.h>
+#include <string.h>
+
+#include <atomic>
+#include <mutex>
+#include <vector>
+
+#include "ffemb_internal.cuh"
+
+namespace ffemb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+  if (e == cudaSuccess) return FFEMB_OK;
+  set_error("%s: %s", what, cudaGetErrorString(e));
+  return FFEMB_ECUDA;
+}
+
+// ---- profiling ------------------------------------------------------------------------------
+struct ProfRec { int phase; cudaEvent_t a, b; };
+static std::mutex g_prof_mu;
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof_recs;
+static std::vector<cudaEvent_t> g_prof_open;  // begin events awaiting their end, per nesting
+static std::atomic<long long> g_launches{0};
+static long long g_phase_launches[FFEMB_NUM_PHASES] = {0};
+
+void prof_begin(int phase, cudaStream_t s) {
+  (void)phase;
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  cudaEvent_t e;
+  if (cudaEventCreate(&e) != cudaSuccess) return;
+  cudaEventRecord(e, s);
+  g_prof_open.push_back(e);
+}
+
+void prof_end(int phase, int launches, cudaStream_t s) {
+  g_launches.fetch_add(launches, std::memory_order_relaxed);
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (g_prof_open.empty()) return;
+  ProfRec r;
+  r.phase = phase;
+  r.a = g_prof_open.back();
+  g_prof_open.pop_back();
+  if (cudaEventCreate(&r.b) != cudaSuccess) { cudaEventDestroy(r.a); return; }
+  cudaEventRecord(r.b, s);
+  g_prof_recs.push_back(r);
+  g_phase_launches[phase] += launches;
+}
+
+// Validate and pack a batched call.  Mirrors the shape checks of the reference's task bodies
+// (src/ops/embedding.cu:251-258: input/output batch agree, weight/output width agree) as far
+// as raw pointers allow, plus what the reference leaves to UB.
+static int pack(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B, int aggr,
+                TableBatch &tb) {
+  if (!aggr_valid(aggr)) {
+    // AGGR_MODE_NONE reaches assert(aggr == AGGR_MODE_AVG) in the reference kernels
+    // (src/ops/embedding.cu:185,209)
+    set_error("invalid aggr %d (expected 21 SUM, 22 AVG, 122 MEAN)", aggr);
+    return FFEMB_EINVAL;
+  }
+  if (!tables || num_tables < 0 || num_tables > FFEMB_MAX_TABLES || D <= 0 || B < 0 ||
+      D > (1 << 20) || B >= (1ll << 31)) {
+    set_error("invalid batched call (tables=%p num_tables=%d D=%lld B=%lld)", (const void *)tables,
+              num_tables, (long long)D, (long long)B);
+    return FFEMB_EINVAL;
+  }
+  memset(&tb, 0, sizeof(tb));
+  tb.num_tables = num_tables;
+  uint64_t rows = 0, lookups = 0;
+  for (int t = 0; t < num_tables; t++) {
+    const ffemb_table_t &x = tables[t];
+    if (x.L < 0 || x.R < 0 || (B > 0 && (!x.out || !x.table || (x.L > 0 && !x.idx)))) {
+      set_error("table %d: invalid descriptor (idx=%p out=%p table=%p R=%lld L=%d)", t,
+                (const void *)x.idx, (void *)x.out, (void *)x.table, (long long)x.R, x.L);
+      return FFEMB_EINVAL;
+    }
+    tb.t[t].idx = x.idx;
+    tb.t[t].out = x.out;
+    tb.t[t].table = x.table;
+    tb.t[t].R = x.R;
+    tb.t[t].L = x.L;
+    tb.t[t].lookup_base = (uint32_t)lookups;
+    tb.row_base[t] = rows;
+    rows += (uint64_t)x.R;
+    lookups += (uint64_t)B * (uint64_t)x.L;
+    if (lookups >= (1ull << 31)) {
+      set_error("more than 2^31 lookups in one call; split the tables");
+      return FFEMB_EINVAL;
+    }
+  }
+  tb.row_base[num_tables] = rows;
+  return FFEMB_OK;
+}
+
+static int pack1(const int64_t *idx, const float *out, const float *table, int64_t L, int64_t D,
+                 int64_t B, int64_t R, int aggr, TableBatch &tb) {
+  if (L < 0 || L >= (1ll << 31)) {
+    set_error("invalid bag width %lld", (long long)L);
+    return FFEMB_EINVAL;
+  }
+  ffemb_table_t x;
+  x.idx = idx;
+  x.out = const_cast<float *>(out);
+  x.table = const_cast<float *>(table);
+  x.R = R;
+  x.L = (int32_t)L;
+  x.reserved = 0;
+  return pack(&x, 1, D, B, aggr, tb);
+}
+
+__global__ void check_indices_kernel(const int64_t *idx, int64_t n, int64_t R,
+                                     unsigned long long *bad) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long mine = 0;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) mine += (idx[i] < 0 || idx[i] >= R);
+  if (mine) atomicAdd(bad, mine);
+}
+
+}  // namespace ffemb
+
+using namespace ffemb;
+
+extern "C" {
+
+const char *ffemb_last_error(void) { return g_err; }
+int ffemb_version(void) { return FFEMB_VERSION; }
+
+int ffemb_forward(const int64_t *idx, float *out, const float *table, int64_t L, int64_t D,
+                  int64_t B, int aggr, ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack1(idx, out, table, L, D, B, 0, aggr, tb);
+  if (rc) return rc;
+  return launch_forward(tb, D, B, aggr, (cudaStream_t)stream);
+}
+
+int ffemb_forward_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                          int aggr, ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack(tables, num_tables, D, B, aggr, tb);
+  if (rc) return rc;
+  return launch_forward(tb, D, B, aggr, (cudaStream_t)stream);
+}
+
+int ffemb_backward_dense_atomic(const int64_t *idx, const float *outgrad, float *wgrad, int64_t L,
+                                int64_t D, int64_t B, int aggr, ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack1(idx, outgrad, wgrad, L, D, B, 0, aggr, tb);
+  if (rc) return rc;
+  return launch_backward_atomic(tb, D, B, aggr, (cudaStream_t)stream);
+}
+
+int ffemb_backward_dense(const int64_t *idx, const float *outgrad, float *wgrad, int64_t L,
+                         int64_t D, int64_t B, int64_t R, int aggr, void *workspace,
+                         size_t workspace_bytes, ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack1(idx, outgrad, wgrad, L, D, B, R, aggr, tb);
+  if (rc) return rc;
+  if (R <= 0 && B * L > 0) {
+    set_error("backward_dense needs the row count R > 0");
+    return FFEMB_EINVAL;
+  }
+  return launch_backward_sorted(tb, D, B, aggr, 0.f, APPLY_GRAD, workspace, workspace_bytes,
+                                (cudaStream_t)stream);
+}
+
+int ffemb_backward_sgd(const int64_t *idx, const float *outgrad, float *table, int64_t L,
+                       int64_t D, int64_t B, int64_t R, int aggr, float lr, void *workspace,
+                       size_t workspace_bytes, ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack1(idx, outgrad, table, L, D, B, R, aggr, tb);
+  if (rc) return rc;
+  if (R <= 0 && B * L > 0) {
+    set_error("backward_sgd needs the row count R > 0");
+    return FFEMB_EINVAL;
+  }
+  return launch_backward_sorted(tb, D, B, aggr, lr, APPLY_SGD, workspace, workspace_bytes,
+                                (cudaStream_t)stream);
+}
+
+int ffemb_backward_sgd_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                               int aggr, float lr, void *workspace, size_t workspace_bytes,
+                               ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack(tables, num_tables, D, B, aggr, tb);
+  if (rc) return rc;
+  return launch_backward_sorted(tb, D, B, aggr, lr, APPLY_SGD, workspace, workspace_bytes,
+                                (cudaStream_t)stream);
+}
+
+int ffemb_backward_dense_batched(const ffemb_table_t *tables, int num_tables, int64_t D,
+                                 int64_t B, int aggr, void *workspace, size_t workspace_bytes,
+                                 ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack(tables, num_tables, D, B, aggr, tb);
+  if (rc) return rc;
+  return launch_backward_sorted(tb, D, B, aggr, 0.f, APPLY_GRAD, workspace, workspace_bytes,
+                                (cudaStream_t)stream);
+}
+
+int ffemb_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_on = on != 0;
+  return FFEMB_OK;
+}
+
+int ffemb_profile_collect(float *ms_per_phase, int64_t *launches_per_phase) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  float ms[FFEMB_NUM_PHASES] = {0};
+  int rc = FFEMB_OK;
+  for (auto &r : g_prof_recs) {
+    float t = 0.f;
+    cudaError_t e = cudaEventSynchronize(r.b);
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&t, r.a, r.b);
+    if (e != cudaSuccess) rc = cuda_fail(e, "profile collect");
+    else ms[r.phase] += t;
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  g_prof_recs.clear();
+  for (auto e : g_prof_open) cudaEventDestroy(e);
+  g_prof_open.clear();
+  for (int p = 0; p < FFEMB_NUM_PHASES; p++) {
+    if (ms_per_phase) ms_per_phase[p] = ms[p];
+    if (launches_per_phase) launches_per_phase[p] = g_phase_launches[p];
+    g_phase_launches[p] = 0;
+  }
+  return rc;
+}
+
+int64_t ffemb_launch_count(void) { return (int64_t)g_launches.load(); }
+
+size_t ffemb_backward_workspace(int64_t num_lookups, int64_t total_rows, int64_t D) {
+  return backward_workspace_bytes(num_lookups, total_rows, D);
+}
+
+int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int64_t *bad_count,
+                        ffemb_stream_t stream) {
+  if (!bad_count || n < 0 || (n > 0 && !idx)) {
+    set_error("check_indices: invalid arguments");
+    return FFEMB_EINVAL;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(bad_count, 0, sizeof(int64_t), s);
+  if (e != cudaSuccess) return cuda_fail(e, "memset");
+  if (n > 0) {
+    int blocks = (int)((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184);
+    check_indices_kernel<<<blocks, 256, 0, s>>>(idx, n, R, (unsigned long long *)bad_count);
+  }
+  return cuda_fail(cudaGetLastError(), "check_indices launch");
+}
+
+}  // extern "C"

@@ -1,0 +1,518 @@
+// ffemb_backward.cu — deterministic sort-then-segmented-reduce scatter-add, fused with the
+// sparse SGD row update, for sm_100a; plus the atomic variant kept as the measured comparison.
+//
+// Replaces, per training step (reference = /root/reference):
+//   Op::zero_grad's dense zero-fill of the weight-grad   src/runtime/model.cc:466-490
+//   embed_backward's B*L*D float atomicAdds               src/ops/embedding.cu:192-217
+//   sgd_update over all R*D elements                      src/runtime/optimizer_kernel.cu:23-41
+// with work proportional to the lookups only; no dense gradient exists.
+//
+// Pipeline (all tables of a GPU at once):
+//   1. keygen : lookup n=(table t, bag b, slot j) -> key = row_base[t] + idx  (global row id),
+//               val = t*B + b (global bag id).  Lookups are enumerated in (t, b, j) order.
+//   2. sort   : stable LSD radix sort of (key, val) on the ceil(log2(total_rows)) key bits
+//               (cub::DeviceRadixSort, onesweep) -> equal rows adjacent, bags ascending.
+//   3. level 1: the sorted array is cut into fixed tiles of CH1 entries; a slot of G=D/4 lanes
+//               walks one tile sequentially (entries prefetched UNR at a time: the gathered
+//               output-grad row AND, for an entry that ends a run, the table row), summing
+//               runs of equal keys in order.  A run that lies inside the tile is applied
+//               straight to the table: W[r] = fma(-lr, sum, W[r]).  A run cut by a tile edge
+//               is written out as a partial row (head partial -> slot 0, tail partial ->
+//               slot 1 of the tile) with its key.
+//   4. level k: the same walk over the previous level's partial rows (fixed tiles of CH2
+//               entries, invalid slots are transparent) until one tile covers everything.
+//               Small inputs finish all remaining levels inside one CTA (one launch).
+// The shape of the summation tree depends only on (sorted order, CH1, CH2): bit-reproducible
+// run to run, unlike the reference's atomics.  Rows with a single lookup get exactly the
+// reference's arithmetic (g summed into 0, then one FFMA), i.e. bit-identical updates.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "ffemb_internal.cuh"
+
+namespace ffemb {
+
+static constexpr int kThreads = 256;
+static constexpr int CH1 = 64;  // level-1 tile (sorted lookups per slot)
+static constexpr int CH2 = 32;  // level-k tile (partial rows per slot)
+static constexpr int kSmallLevel = 1 << 15;  // <= this many partial slots: finish in one CTA
+
+__device__ __forceinline__ void f4_add(float4 &a, const float4 &b) {
+  a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+}
+__device__ __forceinline__ float4 f4_div(float4 a, float d) {
+  return make_float4(a.x / d, a.y / d, a.z / d, a.w / d);
+}
+__device__ __forceinline__ float4 ld_f4(const float *p) { return *reinterpret_cast<const float4 *>(p); }
+__device__ __forceinline__ void st_f4(float *p, float4 v) { *reinterpret_cast<float4 *>(p) = v; }
+
+template <typename K> struct KeyTraits;
+template <> struct KeyTraits<uint32_t> { static constexpr uint32_t INV = 0xffffffffu; };
+template <> struct KeyTraits<uint64_t> { static constexpr uint64_t INV = ~0ull; };
+
+template <typename K> __device__ __forceinline__ K shfl_key(K v, int src);
+template <> __device__ __forceinline__ uint32_t shfl_key<uint32_t>(uint32_t v, int src) {
+  return __shfl_sync(0xffffffffu, v, src);
+}
+template <> __device__ __forceinline__ uint64_t shfl_key<uint64_t>(uint64_t v, int src) {
+  return (uint64_t)shfl_i64((int64_t)v, src);
+}
+
+// ---- 1. keygen -----------------------------------------------------------------------------
+template <typename K>
+__global__ void __launch_bounds__(kThreads)
+keygen_kernel(const __grid_constant__ TableBatch tb, int64_t B, K *keys, uint32_t *vals) {
+  const TableDesc &td = tb.t[blockIdx.y];
+  const int L = td.L;
+  const int64_t n = B * (int64_t)L;
+  const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  if (i >= n) return;
+  const int64_t b = i / L;
+  const int64_t row = __ldg(td.idx + i);
+  keys[td.lookup_base + i] = (K)(tb.row_base[blockIdx.y] + (uint64_t)row);
+  vals[td.lookup_base + i] = (uint32_t)(blockIdx.y * B + b);
+}
+
+// table of a global row id: row_base is ascending, <= 65 entries
+__device__ __forceinline__ int find_table(const TableBatch &tb, uint64_t key) {
+  int lo = 0, hi = tb.num_tables - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (tb.row_base[mid] <= key) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+// ---- 3/4. one tile of the segmented sum -----------------------------------------------------
+// LEVEL1: entries are sorted lookups; the row of entry p is outgrad[vals[p]] (scaled by 1/L for
+//         AVG/MEAN, per element, like embedding.cu:210).  No invalid keys inside [0, n).
+// else  : entries are the previous level's partial rows rows_in[p]; keys may be INV
+//         (transparent: skipped, and runs continue across ONE invalid slot — by construction two
+//         partials of the same run are never separated by more than one, see header).
+template <typename K, int G, int C, bool LEVEL1, int MODE>
+__device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
+                                            const uint32_t *vals,
+                                            const float *rows_in, int64_t n, int64_t tile, int CH,
+                                            bool active, int D, uint32_t B, int aggr, float lr,
+                                            K *keys_out, float *rows_out, int sub, int sl) {
+  constexpr K INV = KeyTraits<K>::INV;
+  constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
+  const int D4 = D >> 2;
+  const int64_t t0 = tile * CH;
+  const int64_t t1 = active ? min(n, t0 + CH) : t0;
+
+  float4 acc[C];
+#pragma unroll
+  for (int c = 0; c < C; c++) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  bool seen = false;        // a valid entry was met in this tile
+  bool first_open = false;  // the tile's first run continues a run of the previous tile
+  bool pending = false;     // acc holds an unflushed run
+  K pend_key = INV;
+  bool wrote_head = false;
+
+  for (int64_t p0 = t0; p0 < t0 + CH; p0 += G) {  // trip count uniform across the warp
+    const int64_t p = p0 + sl;
+    K k = INV, kn = INV, kn2 = INV;
+    uint32_t v = 0;
+    if (p < t1) {
+      k = keys[p];
+      if (p + 1 < n) kn = keys[p + 1];
+      if (!LEVEL1 && p + 2 < n) kn2 = keys[p + 2];
+      if (LEVEL1) v = vals[p];
+    }
+    // does the run of entry p stop at p?  (lookahead crosses the tile edge on purpose)
+    const bool is_end = (k != INV) && !(kn == k || (!LEVEL1 && kn == INV && kn2 == k));
+
+    for (int jj = 0; jj < G; jj += UNR) {
+      if (p0 + jj >= t0 + CH) break;  // uniform
+      float4 g[UNR][C], w[UNR][C];
+      K ek[UNR];
+      bool eend[UNR];
+      float *wp[UNR];
+      float scale[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; u++) {
+        const int src = sub * G + jj + u;
+        ek[u] = shfl_key<K>(k, src);
+        const uint32_t ev = __shfl_sync(0xffffffffu, v, src);
+        eend[u] = __shfl_sync(0xffffffffu, (int)is_end, src) != 0;
+        wp[u] = nullptr;
+        scale[u] = 1.0f;
+        if (jj + u < G && ek[u] != INV) {
+          const float *gp;
+          if (LEVEL1) {
+            const uint32_t t = ev / B;
+            const uint32_t b = ev - t * B;
+            gp = tb.t[t].out + (int64_t)b * D;
+            if (aggr != FFEMB_AGGR_SUM) scale[u] = (float)tb.t[t].L;
+            if (eend[u]) wp[u] = tb.t[t].table + (int64_t)(ek[u] - tb.row_base[t]) * D;
+          } else {
+            gp = rows_in + (p0 + jj + u) * (int64_t)D;
+            if (eend[u]) {
+              const int t = find_table(tb, (uint64_t)ek[u]);
+              wp[u] = tb.t[t].table + (int64_t)((uint64_t)ek[u] - tb.row_base[t]) * D;
+            }
+          }
+#pragma unroll
+          for (int c = 0; c < C; c++) {
+            if (sl + c * G < D4) {
+              g[u][c] = LEVEL1 ? ldg_row(gp + 4 * (sl + c * G)) : ld_f4(gp + 4 * (sl + c * G));
+              if (wp[u]) w[u][c] = ld_f4(wp[u] + 4 * (sl + c * G));
+            }
+          }
+        } else {
+          ek[u] = INV;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; u++) {
+        if (ek[u] == INV) continue;
+        if (!seen) {  // first valid entry of the tile: does it continue the previous tile's run?
+          seen = true;
+          const int64_t q = p0 + jj + u;
+          K km1 = INV, km2 = INV;
+          if (q >= 1) km1 = keys[q - 1];
+          if (!LEVEL1 && q >= 2) km2 = keys[q - 2];
+          first_open = (km1 == ek[u]) || (!LEVEL1 && km1 == INV && km2 == ek[u]);
+        }
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+          if (sl + c * G < D4) {
+            float4 x = g[u][c];
+            if (LEVEL1 && aggr != FFEMB_AGGR_SUM) x = f4_div(x, scale[u]);
+            f4_add(acc[c], x);
+          }
+        }
+        pending = true;
+        pend_key = ek[u];
+        if (eend[u]) {
+          if (first_open) {  // head partial: the run began in an earlier tile
+            if (sl == 0) keys_out[2 * tile] = ek[u];
+#pragma unroll
+            for (int c = 0; c < C; c++)
+              if (sl + c * G < D4) st_f4(rows_out + (2 * tile) * (int64_t)D + 4 * (sl + c * G), acc[c]);
+            wrote_head = true;
+          } else {  // complete run: the one read-modify-write of this table row
+#pragma unroll
+            for (int c = 0; c < C; c++) {
+              if (sl + c * G < D4) {
+                float4 o = w[u][c];
+                if (MODE == APPLY_SGD) {  // W -= lr*gt, contracted like the reference's FFMA
+                  o.x = fmaf(-acc[c].x, lr, o.x); o.y = fmaf(-acc[c].y, lr, o.y);
+                  o.z = fmaf(-acc[c].z, lr, o.z); o.w = fmaf(-acc[c].w, lr, o.w);
+                } else {
+                  f4_add(o, acc[c]);
+                }
+                st_f4(wp[u] + 4 * (sl + c * G), o);
+              }
+            }
+          }
+          first_open = false;
+          pending = false;
+#pragma unroll
+          for (int c = 0; c < C; c++) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+    }
+  }
+  if (active) {
+    if (pending) {  // tail partial: the run goes on in a later tile
+#pragma unroll
+      for (int c = 0; c < C; c++)
+        if (sl + c * G < D4) st_f4(rows_out + (2 * tile + 1) * (int64_t)D + 4 * (sl + c * G), acc[c]);
+    }
+    if (sl == 0) {
+      if (!wrote_head) keys_out[2 * tile] = INV;
+      keys_out[2 * tile + 1] = pending ? pend_key : INV;
+    }
+  }
+}
+
+template <typename K, int G, int C, bool LEVEL1, int MODE>
+__global__ void __launch_bounds__(kThreads)
+reduce_level_kernel(const __grid_constant__ TableBatch tb, const K *keys, const uint32_t *vals,
+                    const float *rows_in, int64_t n, int CH, int D, uint32_t B, int aggr, float lr,
+                    K *keys_out, float *rows_out) {
+  constexpr int SLOTS = 32 / G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane / G, sl = lane % G;
+  const int64_t tile = ((int64_t)blockIdx.x * (kThreads / 32) + warp) * SLOTS + sub;
+  const int64_t ntiles = (n + CH - 1) / CH;
+  reduce_tile<K, G, C, LEVEL1, MODE>(tb, keys, vals, rows_in, n, tile, CH, tile < ntiles, D, B,
+                                     aggr, lr, keys_out, rows_out, sub, sl);
+}
+
+// All remaining levels in ONE CTA: level i reads buffer (i&1), writes buffer ((i+1)&1).
+template <typename K, int G, int C, int MODE>
+__global__ void __launch_bounds__(kThreads)
+reduce_tail_kernel(const __grid_constant__ TableBatch tb, K *keys_a, float *rows_a, K *keys_b,
+                   float *rows_b, int64_t n, int CH, int D, float lr) {
+  constexpr int SLOTS = 32 / G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane / G, sl = lane % G;
+  const int nslots = (kThreads / 32) * SLOTS;
+  const int slot = warp * SLOTS + sub;
+  K *kin = keys_a, *kout = keys_b;
+  float *rin = rows_a, *rout = rows_b;
+  while (true) {
+    const int64_t ntiles = (n + CH - 1) / CH;
+    for (int64_t base = 0; base < ntiles; base += nslots) {
+      const int64_t tile = base + slot;
+      reduce_tile<K, G, C, false, MODE>(tb, kin, nullptr, rin, n, tile, CH, tile < ntiles, D, 1u,
+                                        FFEMB_AGGR_SUM, lr, kout, rout, sub, sl);
+    }
+    if (ntiles <= 1) break;
+    __syncthreads();  // partial rows written by this CTA are visible to it after the barrier
+    n = 2 * ntiles;
+    K *tk = kin; kin = kout; kout = tk;
+    float *tr = rin; rin = rout; rout = tr;
+  }
+}
+
+// ---- workspace carving -----------------------------------------------------------------------
+static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+static inline bool wide_keys(int64_t total_rows) { return (uint64_t)total_rows >= 0xffffffffull; }
+
+struct Levels {
+  int count;            // number of partial buffers
+  int64_t slots[8];     // partial slots of level i output (2 * tiles)
+};
+static Levels plan_levels(int64_t n) {
+  Levels lv;
+  lv.count = 0;
+  int64_t m = 2 * ((n + CH1 - 1) / CH1);
+  lv.slots[lv.count++] = m;
+  while (m > 2 && lv.count < 8) {  // more than one tile at the previous level
+    const int64_t tiles = (m + CH2 - 1) / CH2;
+    m = 2 * tiles;
+    lv.slots[lv.count++] = m;
+    if (tiles <= 1) break;
+  }
+  return lv;
+}
+
+struct Carve {
+  char *keys_a, *keys_b;
+  uint32_t *vals_a, *vals_b;
+  void *cub_tmp;
+  size_t cub_bytes;
+  char *pkeys[2];
+  float *prows[2];
+  size_t total;
+};
+static Carve carve(char *base, int64_t n, int64_t total_rows, int64_t D) {
+  Carve c;
+  const size_t ksz = wide_keys(total_rows) ? 8 : 4;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char *p = base ? base + off : nullptr; off += align_up(bytes); return p; };
+  c.keys_a = take((size_t)n * ksz);
+  c.keys_b = take((size_t)n * ksz);
+  c.vals_a = (uint32_t *)take((size_t)n * 4);
+  c.vals_b = (uint32_t *)take((size_t)n * 4);
+  size_t tmp = 0;
+  if (ksz == 4)
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp, (uint32_t *)nullptr, (uint32_t *)nullptr,
+                                    (uint32_t *)nullptr, (uint32_t *)nullptr, (int)n, 0, 32);
+  else
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp, (uint64_t *)nullptr, (uint64_t *)nullptr,
+                                    (uint32_t *)nullptr, (uint32_t *)nullptr, (int)n, 0, 64);
+  c.cub_bytes = tmp;
+  c.cub_tmp = take(tmp);
+  // partial buffers ping-pong: level 1 output is the largest; level 2 output the second largest
+  const Levels lv = plan_levels(n);
+  const int64_t s0 = lv.slots[0], s1 = lv.count > 1 ? lv.slots[1] : 2;
+  c.pkeys[0] = take((size_t)s0 * ksz);
+  c.prows[0] = (float *)take((size_t)s0 * D * 4);
+  c.pkeys[1] = take((size_t)s1 * ksz);
+  c.prows[1] = (float *)take((size_t)s1 * D * 4);
+  c.total = off;
+  return c;
+}
+
+size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t D) {
+  if (num_lookups <= 0 || total_rows <= 0 || D <= 0 || num_lookups >= (1ll << 31)) return 0;
+  return carve(nullptr, num_lookups, total_rows, D).total;
+}
+
+// ---- host driver -----------------------------------------------------------------------------
+template <typename K, int G, int C, int MODE>
+static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr, int64_t n,
+                      int64_t total_rows, const Carve &c, cudaStream_t s) {
+  K *keys_a = (K *)c.keys_a, *keys_b = (K *)c.keys_b;
+  int max_l = 1;
+  for (int t = 0; t < tb.num_tables; t++) max_l = tb.t[t].L > max_l ? tb.t[t].L : max_l;
+  {
+    ProfScope prof(FFEMB_PHASE_KEYGEN, 1, s);
+    dim3 grid((unsigned)((B * max_l + kThreads - 1) / kThreads), tb.num_tables);
+    keygen_kernel<K><<<grid, kThreads, 0, s>>>(tb, B, keys_a, c.vals_a);
+  }
+  int end_bit = 1;
+  while (end_bit < (int)sizeof(K) * 8 && ((uint64_t)(total_rows - 1) >> end_bit) != 0) end_bit++;
+  {
+    // onesweep: histogram + scan + one pass per 8 key bits
+    ProfScope prof(FFEMB_PHASE_SORT, 2 + (end_bit + 7) / 8, s);
+    size_t tmp = c.cub_bytes;
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(c.cub_tmp, tmp, keys_a, keys_b, c.vals_a,
+                                                    c.vals_b, (int)n, 0, end_bit, s);
+    if (e != cudaSuccess) return cuda_fail(e, "radix sort");
+  }
+
+  constexpr int SLOTS = 32 / G;
+  const int64_t slots_per_cta = (int64_t)(kThreads / 32) * SLOTS;
+  const int64_t ntiles1 = (n + CH1 - 1) / CH1;
+  K *pk0 = (K *)c.pkeys[0], *pk1 = (K *)c.pkeys[1];
+  {
+    ProfScope prof(FFEMB_PHASE_REDUCE1, 1, s);
+    reduce_level_kernel<K, G, C, true, MODE>
+        <<<(unsigned)((ntiles1 + slots_per_cta - 1) / slots_per_cta), kThreads, 0, s>>>(
+            tb, keys_b, c.vals_b, nullptr, n, CH1, D, (uint32_t)B, aggr, lr, pk0, c.prows[0]);
+  }
+  int64_t m = 2 * ntiles1;
+  if (ntiles1 > 1) {
+    int ups = 1;
+    for (int64_t mm = m; mm > kSmallLevel; mm = 2 * ((mm + CH2 - 1) / CH2)) ups++;
+    ProfScope prof(FFEMB_PHASE_REDUCE_UP, ups, s);
+    int cur = 0;
+    K *pk[2] = {pk0, pk1};
+    while (m > kSmallLevel) {  // grid-wide levels while the partial array is large
+      const int64_t tiles = (m + CH2 - 1) / CH2;
+      reduce_level_kernel<K, G, C, false, MODE>
+          <<<(unsigned)((tiles + slots_per_cta - 1) / slots_per_cta), kThreads, 0, s>>>(
+              tb, pk[cur], nullptr, c.prows[cur], m, CH2, D, 1u, FFEMB_AGGR_SUM, lr, pk[cur ^ 1],
+              c.prows[cur ^ 1]);
+      m = 2 * tiles;
+      cur ^= 1;
+    }
+    reduce_tail_kernel<K, G, C, MODE><<<1, kThreads, 0, s>>>(tb, pk[cur], c.prows[cur], pk[cur ^ 1],
+                                                            c.prows[cur ^ 1], m, CH2, D, lr);
+  }
+  return cuda_fail(cudaGetLastError(), "sorted backward launch");
+}
+
+template <typename K, int MODE>
+static int dispatch_g(const TableBatch &tb, int D, int64_t B, int aggr, float lr, int64_t n,
+                      int64_t rows, const Carve &c, cudaStream_t s) {
+  const int D4 = D / 4;
+  if (D4 <= 1) return run_sorted<K, 1, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
+  if (D4 <= 2) return run_sorted<K, 2, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
+  if (D4 <= 4) return run_sorted<K, 4, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
+  if (D4 <= 8) return run_sorted<K, 8, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
+  if (D4 <= 16) return run_sorted<K, 16, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
+  if (D4 <= 32) return run_sorted<K, 32, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
+  if (D4 <= 64) return run_sorted<K, 32, 2, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
+  return run_sorted<K, 32, 4, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
+}
+
+int launch_backward_sorted(const TableBatch &tb, int64_t D, int64_t B, int aggr, float lr,
+                           ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s) {
+  int64_t n = 0;
+  for (int t = 0; t < tb.num_tables; t++) n += B * tb.t[t].L;
+  const int64_t rows = (int64_t)tb.row_base[tb.num_tables];
+  if (n == 0) return FFEMB_OK;
+  if (D % 4 != 0 || D > 512) {
+    set_error("sorted backward needs D %% 4 == 0 and D <= 512 (got %lld)", (long long)D);
+    return FFEMB_EINVAL;
+  }
+  if (n >= (1ll << 31) || (int64_t)tb.num_tables * B >= (1ll << 32)) {
+    set_error("sorted backward: too many lookups for one call (%lld)", (long long)n);
+    return FFEMB_EINVAL;
+  }
+  const size_t need = backward_workspace_bytes(n, rows, D);
+  if (!ws || ((uintptr_t)ws & 255) || ws_bytes < need) {
+    set_error("workspace: need %zu bytes, 256-byte aligned (got %zu at %p)", need, ws_bytes, ws);
+    return FFEMB_EWORKSPACE;
+  }
+  const Carve c = carve((char *)ws, n, rows, D);
+  if (wide_keys(rows)) {
+    return mode == APPLY_SGD
+               ? dispatch_g<uint64_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s)
+               : dispatch_g<uint64_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s);
+  }
+  return mode == APPLY_SGD ? dispatch_g<uint32_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s)
+                           : dispatch_g<uint32_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s);
+}
+
+// ---- the atomic comparison: reference-equivalent unordered scatter ---------------------------
+template <int G, int C>
+__global__ void __launch_bounds__(kThreads)
+bwd_atomic_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int aggr) {
+  constexpr int SLOTS = 32 / G;
+  const TableDesc &td = tb.t[blockIdx.y];
+  const int L = td.L;
+  const int D4 = D >> 2;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane / G, sl = lane % G;
+  const int64_t bag = ((int64_t)blockIdx.x * (kThreads / 32) + warp) * SLOTS + sub;
+  const bool valid = bag < B;
+  const int64_t b = valid ? bag : (B - 1);
+  const int64_t *ip = td.idx + b * (int64_t)L;
+  float4 g[C];
+#pragma unroll
+  for (int c = 0; c < C; c++) {
+    g[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (sl + c * G < D4) {
+      g[c] = ldg_row(td.out + b * (int64_t)D + 4 * (sl + c * G));
+      if (aggr != FFEMB_AGGR_SUM) g[c] = f4_div(g[c], (float)L);
+    }
+  }
+  for (int j0 = 0; j0 < L; j0 += G) {
+    const int64_t mine = (j0 + sl < L) ? __ldg(ip + j0 + sl) : 0;
+    const int cnt = min(G, L - j0);
+    for (int jj = 0; jj < cnt; jj++) {
+      const int64_t r = shfl_i64(mine, sub * G + jj);
+      if (valid) {
+        float *wp = td.table + r * (int64_t)D;
+#pragma unroll
+        for (int c = 0; c < C; c++)
+          if (sl + c * G < D4) atomicAdd(reinterpret_cast<float4 *>(wp + 4 * (sl + c * G)), g[c]);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+bwd_atomic_generic_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int aggr) {
+  const TableDesc &td = tb.t[blockIdx.y];
+  const int L = td.L;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t bag = (int64_t)blockIdx.x * (kThreads / 32) + warp;
+  if (bag >= B) return;
+  for (int d = lane; d < D; d += 32) {
+    float g = td.out[bag * (int64_t)D + d];
+    if (aggr != FFEMB_AGGR_SUM) g = g / (float)L;
+    for (int j = 0; j < L; j++)
+      atomicAdd(td.table + __ldg(td.idx + bag * (int64_t)L + j) * (int64_t)D + d, g);
+  }
+}
+
+template <int G, int C>
+static void launch_atomic(const TableBatch &tb, int D, int64_t B, int aggr, cudaStream_t s) {
+  const int64_t per_cta = (int64_t)(kThreads / 32) * (32 / G);
+  dim3 grid((unsigned)((B + per_cta - 1) / per_cta), tb.num_tables);
+  bwd_atomic_kernel<G, C><<<grid, kThreads, 0, s>>>(tb, D, B, aggr);
+}
+
+int launch_backward_atomic(const TableBatch &tb, int64_t D64, int64_t B, int aggr, cudaStream_t s) {
+  const int D = (int)D64;
+  if (B == 0 || tb.num_tables == 0) return FFEMB_OK;
+  ProfScope prof(FFEMB_PHASE_ATOMIC, 1, s);
+  bool vec = (D % 4 == 0) && D <= 512;
+  for (int t = 0; t < tb.num_tables; t++)
+    vec = vec && (((uintptr_t)tb.t[t].table | (uintptr_t)tb.t[t].out) % 16 == 0);
+  if (!vec) {
+    dim3 grid((unsigned)((B + kThreads / 32 - 1) / (kThreads / 32)), tb.num_tables);
+    bwd_atomic_generic_kernel<<<grid, kThreads, 0, s>>>(tb, D, B, aggr);
+  } else {
+    const int D4 = D / 4;
+    if (D4 <= 1) launch_atomic<1, 1>(tb, D, B, aggr, s);
+    else if (D4 <= 2) launch_atomic<2, 1>(tb, D, B, aggr, s);
+    else if (D4 <= 4) launch_atomic<4, 1>(tb, D, B, aggr, s);
+    else if (D4 <= 8) launch_atomic<8, 1>(tb, D, B, aggr, s);
+    else if (D4 <= 16) launch_atomic<16, 1>(tb, D, B, aggr, s);
+    else if (D4 <= 32) launch_atomic<32, 1>(tb, D, B, aggr, s);
+    else if (D4 <= 64) launch_atomic<32, 2>(tb, D, B, aggr, s);
+    else launch_atomic<32, 4>(tb, D, B, aggr, s);
+  }
+  return cuda_fail(cudaGetLastError(), "atomic backward launch");
+}
+
+}  // namespace ffemb

@@ -1,0 +1,78 @@
+// ffemb_internal.cuh — shared declarations of libffemb.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "ffemb.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libffemb is written for sm_100a (B200) only"
+#endif
+
+namespace ffemb {
+
+// Descriptor array passed BY VALUE as a kernel parameter (64 x 40 B = 2.5 KB of the 4 KB
+// parameter space): no per-step H2D copy, no device-side descriptor allocation.
+struct TableDesc {
+  const int64_t *idx;
+  float *out;     // pooled output (fwd) / output-grad (bwd)
+  float *table;   // weights or dense weight-grad
+  int64_t R;
+  int32_t L;
+  uint32_t lookup_base;  // first lookup number of this table: sum_{s<t} B*L_s (bwd only)
+};
+struct TableBatch {
+  TableDesc t[FFEMB_MAX_TABLES];
+  uint64_t row_base[FFEMB_MAX_TABLES + 1];  // first global row id of each table (bwd keys)
+  int32_t num_tables;
+};
+
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what);
+
+// profiling hooks (ffemb_api.cu): no-ops unless ffemb_profile_enable(1)
+void prof_begin(int phase, cudaStream_t s);
+void prof_end(int phase, int launches, cudaStream_t s);
+struct ProfScope {
+  int phase, launches;
+  cudaStream_t s;
+  ProfScope(int p, int n, cudaStream_t st) : phase(p), launches(n), s(st) { prof_begin(p, st); }
+  ~ProfScope() { prof_end(phase, launches, s); }
+};
+
+static inline bool aggr_valid(int aggr) {
+  return aggr == FFEMB_AGGR_SUM || aggr == FFEMB_AGGR_AVG || aggr == FFEMB_AGGR_MEAN;
+}
+
+// launchers (defined in the .cu files)
+int launch_forward(const TableBatch &tb, int64_t D, int64_t B, int aggr, cudaStream_t s);
+int launch_backward_atomic(const TableBatch &tb, int64_t D, int64_t B, int aggr, cudaStream_t s);
+enum ApplyMode { APPLY_SGD = 0, APPLY_GRAD = 1 };
+int launch_backward_sorted(const TableBatch &tb, int64_t D, int64_t B, int aggr, float lr,
+                           ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s);
+size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t D);
+
+// ---- device helpers --------------------------------------------------------------------
+// 16-byte read-only load of a table row fragment.  Rows are touched once per lookup, so keep
+// them out of L1 (L1::no_allocate) and let L2 hold the hot ones.
+__device__ __forceinline__ float4 ldg_row(const float *p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p));
+  return v;
+}
+// streaming 16-byte store (pooled outputs are consumed by another kernel / another GPU)
+__device__ __forceinline__ void st_stream(float *p, float4 v) {
+  asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x),
+               "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ int64_t shfl_i64(int64_t v, int src) {
+  int lo = __shfl_sync(0xffffffffu, (int)(v & 0xffffffffll), src);
+  int hi = __shfl_sync(0xffffffffu, (int)(v >> 32), src);
+  return ((int64_t)hi << 32) | (uint32_t)lo;
+}
+
+}  // namespace ffemb

@@ -1,0 +1,195 @@
+"""Host-side mirror of the reference Embedding operator for this path.
+
+Names and argument meaning follow /root/reference/include/model.h:1136-1202:
+  Embedding.forward_kernel / backward_kernel  — the static raw-pointer wrappers (the seam);
+  EmbeddingMeta                                — per-shard state made once by init_task
+                                                 (src/ops/embedding.cu:104-113), here it also
+                                                 owns the backward workspace;
+  Embedding(num_entries, out_dim, aggr)        — the op: init / forward / backward.
+EmbeddingCollection is the table-batched form (all tables of one GPU per launch).
+Everything computes in libffemb.so; tensors are torch CUDA tensors used as device buffers.
+"""
+import ctypes as C
+
+import torch
+
+from . import binding as B
+from .binding import AGGR_MODE_SUM, check, ffemb_table_t, lib
+
+
+def _stream_ptr(stream=None):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+def _req(t, dtype, name):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == dtype and t.is_contiguous()):
+        raise TypeError(f"{name}: expected a contiguous CUDA tensor of {dtype}")
+    return t
+
+
+class EmbeddingMeta:
+    """OpMeta analogue: aggr + a persistent workspace (no allocation on the hot path)."""
+
+    def __init__(self, aggr, profiling=False):
+        self.aggr = int(aggr)
+        self.profiling = bool(profiling)
+        self.workspace = None
+
+    def ensure_workspace(self, num_lookups, total_rows, dim, device):
+        need = lib().ffemb_backward_workspace(int(num_lookups), int(total_rows), int(dim))
+        if need == 0 and num_lookups > 0:
+            raise B.FFEmbError(B.FFEMB_EINVAL, "invalid workspace query")
+        if self.workspace is None or self.workspace.numel() < need or self.workspace.device != device:
+            self.workspace = torch.empty(max(need, 256), dtype=torch.uint8, device=device)
+        return self.workspace
+
+
+class Embedding:
+    """One table.  Mirrors class Embedding (include/model.h:1136-1196)."""
+
+    def __init__(self, num_entries, out_dim, aggr=AGGR_MODE_SUM, name=None):
+        self.num_entries, self.out_channels, self.aggr = int(num_entries), int(out_dim), int(aggr)
+        self.name = name
+        self.meta = None
+
+    # -- the seam: same argument order as the reference's static wrappers --------------------
+    @staticmethod
+    def forward_kernel(input_ptr, output_ptr, weight_ptr, in_dim, out_dim, batch_size, aggr,
+                       outputSize=None, stream=None):
+        """Embedding::forward_kernel (src/ops/embedding.cu:219-231). Pointers are ints."""
+        if outputSize is not None and outputSize != batch_size * out_dim:
+            raise ValueError("outputSize must equal batch_size * out_dim")
+        check(lib().ffemb_forward(input_ptr, output_ptr, weight_ptr, in_dim, out_dim, batch_size,
+                                  int(aggr), _stream_ptr(stream)))
+
+    @staticmethod
+    def backward_kernel(input_ptr, output_ptr, weight_grad_ptr, in_dim, out_dim, batch_size, aggr,
+                        outputSize=None, stream=None):
+        """Embedding::backward_kernel (src/ops/embedding.cu:308-320): unordered atomic scatter
+        into the dense, pre-zeroed weight-grad — the API-exact comparison variant."""
+        if outputSize is not None and outputSize != batch_size * out_dim:
+            raise ValueError("outputSize must equal batch_size * out_dim")
+        check(lib().ffemb_backward_dense_atomic(input_ptr, output_ptr, weight_grad_ptr, in_dim,
+                                                out_dim, batch_size, int(aggr), _stream_ptr(stream)))
+
+    # -- op-level API --------------------------------------------------------------------------
+    def init(self):
+        """Embedding::init -> init_task: make the per-shard meta."""
+        self.meta = EmbeddingMeta(self.aggr)
+        return self.meta
+
+    def _shapes(self, input, weight):
+        _req(input, torch.int64, "input")
+        _req(weight, torch.float32, "weight")
+        if input.dim() != 2 or weight.dim() != 2:
+            raise ValueError("input must be [B][L], weight [R][D]")
+        if weight.shape[0] != self.num_entries or weight.shape[1] != self.out_channels:
+            raise ValueError("weight shape does not match (num_entries, out_dim)")
+        return input.shape[0], input.shape[1]
+
+    def forward(self, input, weight, output=None, stream=None):
+        Bsz, L = self._shapes(input, weight)
+        if output is None:
+            output = torch.empty((Bsz, self.out_channels), dtype=torch.float32, device=weight.device)
+        _req(output, torch.float32, "output")
+        if tuple(output.shape) != (Bsz, self.out_channels):
+            raise ValueError("output shape must be [B][D]")  # the task body's asserts
+        self.forward_kernel(input.data_ptr(), output.data_ptr(), weight.data_ptr(), L,
+                            self.out_channels, Bsz, self.aggr, stream=stream)
+        return output
+
+    def backward(self, input, output_grad, weight_grad, deterministic=True, stream=None):
+        """Unfused, API-exact: accumulate into the dense weight-grad."""
+        Bsz, L = self._shapes(input, weight_grad)
+        _req(output_grad, torch.float32, "output_grad")
+        if not deterministic:
+            self.backward_kernel(input.data_ptr(), output_grad.data_ptr(), weight_grad.data_ptr(),
+                                 L, self.out_channels, Bsz, self.aggr, stream=stream)
+            return weight_grad
+        if self.meta is None:
+            self.init()
+        ws = self.meta.ensure_workspace(Bsz * L, self.num_entries, self.out_channels, weight_grad.device)
+        check(lib().ffemb_backward_dense(input.data_ptr(), output_grad.data_ptr(),
+                                         weight_grad.data_ptr(), L, self.out_channels, Bsz,
+                                         self.num_entries, self.aggr, ws.data_ptr(), ws.numel(),
+                                         _stream_ptr(stream)))
+        return weight_grad
+
+    def backward_sgd(self, input, output_grad, weight, lr, stream=None):
+        """Fused backward + sparse SGD row update (momentum = weight_decay = 0)."""
+        Bsz, L = self._shapes(input, weight)
+        _req(output_grad, torch.float32, "output_grad")
+        if self.meta is None:
+            self.init()
+        ws = self.meta.ensure_workspace(Bsz * L, self.num_entries, self.out_channels, weight.device)
+        check(lib().ffemb_backward_sgd(input.data_ptr(), output_grad.data_ptr(), weight.data_ptr(),
+                                       L, self.out_channels, Bsz, self.num_entries, self.aggr,
+                                       float(lr), ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
+        return weight
+
+
+class EmbeddingCollection:
+    """All tables that live on one GPU, driven through the table-batched entry points."""
+
+    def __init__(self, weights, bags, aggr=AGGR_MODE_SUM):
+        if len(weights) == 0 or len(weights) != len(bags):
+            raise ValueError("need one bag width per table")
+        self.weights = [_req(w, torch.float32, "weight") for w in weights]
+        self.dim = int(weights[0].shape[1])
+        if any(w.dim() != 2 or w.shape[1] != self.dim for w in weights):
+            raise ValueError("all tables of a collection share the embedding dim")
+        self.bags = [int(l) for l in bags]
+        self.aggr = int(aggr)
+        self.device = weights[0].device
+        self.meta = EmbeddingMeta(aggr)
+        self.total_rows = sum(int(w.shape[0]) for w in weights)
+
+    def _descs(self, indices, outs, tables, batch):
+        T = len(self.weights)
+        arr = (ffemb_table_t * T)()
+        for t in range(T):
+            _req(indices[t], torch.int64, "indices")
+            _req(outs[t], torch.float32, "out")
+            if tuple(indices[t].shape) != (batch, self.bags[t]) or tuple(outs[t].shape) != (batch, self.dim):
+                raise ValueError(f"table {t}: expected indices [{batch}][{self.bags[t]}] and out [{batch}][{self.dim}]")
+            arr[t].idx, arr[t].out, arr[t].table = indices[t].data_ptr(), outs[t].data_ptr(), tables[t].data_ptr()
+            arr[t].R, arr[t].L = int(tables[t].shape[0]), self.bags[t]
+        return arr
+
+    def _chunks(self):
+        T = len(self.weights)
+        return [(s, min(T, s + B.FFEMB_MAX_TABLES)) for s in range(0, T, B.FFEMB_MAX_TABLES)]
+
+    def forward(self, indices, outs=None, stream=None):
+        batch = int(indices[0].shape[0])
+        if outs is None:
+            outs = [torch.empty((batch, self.dim), dtype=torch.float32, device=self.device)
+                    for _ in self.weights]
+        arr = self._descs(indices, outs, self.weights, batch)
+        for s, e in self._chunks():
+            sub = C.cast(C.byref(arr, s * C.sizeof(ffemb_table_t)), C.POINTER(ffemb_table_t))
+            check(lib().ffemb_forward_batched(sub, e - s, self.dim, batch, self.aggr, _stream_ptr(stream)))
+        return outs
+
+    def backward_sgd(self, indices, out_grads, lr, stream=None):
+        batch = int(indices[0].shape[0])
+        arr = self._descs(indices, out_grads, self.weights, batch)
+        for s, e in self._chunks():
+            n = batch * sum(self.bags[s:e])
+            rows = sum(int(w.shape[0]) for w in self.weights[s:e])
+            ws = self.meta.ensure_workspace(n, rows, self.dim, self.device)
+            sub = C.cast(C.byref(arr, s * C.sizeof(ffemb_table_t)), C.POINTER(ffemb_table_t))
+            check(lib().ffemb_backward_sgd_batched(sub, e - s, self.dim, batch, self.aggr, float(lr),
+                                                   ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
+
+    def backward_dense(self, indices, out_grads, weight_grads, stream=None):
+        batch = int(indices[0].shape[0])
+        arr = self._descs(indices, out_grads, weight_grads, batch)
+        for s, e in self._chunks():
+            n = batch * sum(self.bags[s:e])
+            rows = sum(int(w.shape[0]) for w in weight_grads[s:e])
+            ws = self.meta.ensure_workspace(n, rows, self.dim, self.device)
+            sub = C.cast(C.byref(arr, s * C.sizeof(ffemb_table_t)), C.POINTER(ffemb_table_t))
+            check(lib().ffemb_backward_dense_batched(sub, e - s, self.dim, batch, self.aggr,
+                                                     ws.data_ptr(), ws.numel(), _stream_ptr(stream)))

@@ -1,0 +1,150 @@
+/* ffemb.h — C ABI of libffemb.so: the B200 (sm_100a) embedding hot path for DLRM-FlexFlow.
+ *
+ * This is the drop-in boundary for ONE path of the reference (/root/reference, cited as
+ * file:line): the FlexFlow Embedding operator.  Legion task bodies keep their reference
+ * signatures (Embedding::forward_task / backward_task, src/ops/embedding.cu:238-272,322-354)
+ * and call these entry points where they used to call the static raw-pointer wrappers
+ *     Embedding::forward_kernel   include/model.h:1169-1177, src/ops/embedding.cu:219-231
+ *     Embedding::backward_kernel  include/model.h:1178-1186, src/ops/embedding.cu:308-320
+ * The reference-side binding is shown in INTEGRATION.md; dlrm-flexflow_b200/csrc/flexflow/
+ * embedding.cu is that binding written out.
+ *
+ * Conventions:
+ *   - plain C: pointers, int64 sizes, an opaque CUDA stream; no C++/torch types;
+ *   - every pointer is a DEVICE-accessible pointer borrowed from the caller (Legion owns all
+ *     regions); nothing is allocated or freed per call; scratch comes from the caller
+ *     (FFHandler::workSpace or an EmbeddingMeta-owned buffer) and is sized by the *_workspace
+ *     queries;
+ *   - all work is enqueued on `stream`; no host synchronisation, no device selection (the
+ *     caller's current device is used), re-entrant across devices and threads;
+ *   - returns FFEMB_OK or an error code and never throws / exits; ffemb_last_error() gives the
+ *     text for the calling thread.  (The reference asserts / exit(1)s instead,
+ *     include/cuda_helper.h:6-46; the drop-in task bodies turn non-zero into that.)
+ *   - layouts are the flat row-major buffers the reference kernels see:
+ *     idx int64 [B][L], table float [R][D], pooled output / output-grad float [B][D].
+ *   - indices are NOT range-checked on the hot entry points (the reference GPU kernels do not
+ *     either); ffemb_check_indices is the debug aid.
+ */
+#ifndef FFEMB_H
+#define FFEMB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FFEMB_VERSION 100
+#if defined(__GNUC__)
+#define FFEMB_API __attribute__((visibility("default")))
+#else
+#define FFEMB_API
+#endif
+
+/* status codes */
+#define FFEMB_OK 0
+#define FFEMB_EINVAL 1     /* bad argument (NULL pointer, negative size, AGGR_MODE_NONE, ...) */
+#define FFEMB_ECUDA 2      /* a CUDA call or launch failed */
+#define FFEMB_EWORKSPACE 3 /* workspace missing, misaligned or smaller than *_workspace said */
+#define FFEMB_ERANGE 4     /* ffemb_check_indices found an index outside [0, R) */
+
+/* AggrMode values of include/ffconst.h:12-16, passed through as ints */
+#define FFEMB_AGGR_NONE 20 /* accepted by FFModel::embedding but asserts in the kernels -> EINVAL */
+#define FFEMB_AGGR_SUM 21
+#define FFEMB_AGGR_AVG 22   /* REF_LITERAL: divide inside the bag loop, src/ops/embedding.cu:180-188 */
+#define FFEMB_AGGR_MEAN 122 /* opt-in true mean (sum * (1/L)); not a reference enum value */
+
+#define FFEMB_MAX_TABLES 64 /* tables per batched call */
+
+/* ABI-compatible with cudaStream_t */
+typedef struct CUstream_st *ffemb_stream_t;
+
+/* One table of a batched call.  All tables of a call share B and D; L (bag width) and R
+ * (rows) are per table.  `out` is the pooled output in forward and the output-grad in
+ * backward.  `table` is the weight (forward: read; backward_sgd: read-write) or the dense
+ * weight-grad (backward_dense*).                                                           */
+typedef struct ffemb_table {
+  const int64_t *idx; /* [B][L] */
+  float *out;         /* [B][D] */
+  float *table;       /* [R][D] */
+  int64_t R;
+  int32_t L;
+  int32_t reserved;
+} ffemb_table_t;
+
+FFEMB_API const char *ffemb_last_error(void);
+FFEMB_API int ffemb_version(void);
+
+/* ---- forward: replaces Embedding::forward_kernel ------------------------------------------
+ * out[b][d] = pool_j table[idx[b][j]][d]; every element of out is written (region is
+ * WRITE_ONLY in the reference).  Accumulation is sequential in j per output element, so SUM
+ * and AVG(REF_LITERAL) are bit-identical to embed_forward.                                   */
+FFEMB_API int ffemb_forward(const int64_t *idx, float *out, const float *table, int64_t L, int64_t D,
+                  int64_t B, int aggr, ffemb_stream_t stream);
+
+/* all tables of one GPU in one launch */
+FFEMB_API int ffemb_forward_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                          int aggr, ffemb_stream_t stream);
+
+/* ---- backward, API-exact (unfused): replaces Embedding::backward_kernel -------------------
+ * Accumulates into the dense, caller-zeroed weight-grad like embed_backward
+ * (src/ops/embedding.cu:192-217).
+ *   _atomic : red.global.add scatter (unordered, like the reference; the measured comparison)
+ *   (plain) : deterministic sort + segmented reduce, needs workspace                         */
+FFEMB_API int ffemb_backward_dense_atomic(const int64_t *idx, const float *outgrad, float *wgrad, int64_t L,
+                                int64_t D, int64_t B, int aggr, ffemb_stream_t stream);
+FFEMB_API int ffemb_backward_dense(const int64_t *idx, const float *outgrad, float *wgrad, int64_t L,
+                         int64_t D, int64_t B, int64_t R, int aggr, void *workspace,
+                         size_t workspace_bytes, ffemb_stream_t stream);
+
+/* ---- backward fused with the sparse SGD row update ----------------------------------------
+ * Replaces, for one table and momentum == weight_decay == 0:
+ *   Op::zero_grad on the weight-grad   src/runtime/model.cc:466-490
+ *   Embedding::backward_kernel          src/ops/embedding.cu:308-320
+ *   SGDOptimizer::update -> sgd_update  src/runtime/optimizer_kernel.cu:23-41
+ * table[r] = fma(-lr, sum_of_grads(r), table[r]) for every touched row r, once; untouched
+ * rows are not read or written.  Deterministic: radix sort of (row, bag) pairs, then a
+ * fixed-shape segmented sum.                                                                 */
+FFEMB_API int ffemb_backward_sgd(const int64_t *idx, const float *outgrad, float *table, int64_t L,
+                       int64_t D, int64_t B, int64_t R, int aggr, float lr, void *workspace,
+                       size_t workspace_bytes, ffemb_stream_t stream);
+
+FFEMB_API int ffemb_backward_sgd_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                               int aggr, float lr, void *workspace, size_t workspace_bytes,
+                               ffemb_stream_t stream);
+FFEMB_API int ffemb_backward_dense_batched(const ffemb_table_t *tables, int num_tables, int64_t D,
+                                 int64_t B, int aggr, void *workspace, size_t workspace_bytes,
+                                 ffemb_stream_t stream);
+
+/* Bytes of scratch the sorted backward needs for `num_lookups` = sum_t B*L_t lookups over
+ * tables holding `total_rows` = sum_t R_t rows of D floats.  0 on invalid arguments.         */
+FFEMB_API size_t ffemb_backward_workspace(int64_t num_lookups, int64_t total_rows, int64_t D);
+
+/* ---- debug aid (not on the timed path) -----------------------------------------------------
+ * Writes the number of indices outside [0, R) to *bad_count (device int64).                   */
+FFEMB_API int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int64_t *bad_count,
+                        ffemb_stream_t stream);
+
+/* ---- profiling (the OpMeta::profiling analogue, src/ops/embedding.cu:266-271) -------------
+ * When enabled, every entry point brackets its internal phases with CUDA events on the
+ * caller's stream.  ffemb_profile_collect synchronises on those events, adds the elapsed
+ * milliseconds and the number of kernel launches per phase into the two arrays
+ * (FFEMB_NUM_PHASES entries each, either may be NULL) and resets.  Off by default; the hot
+ * path then records nothing.  ffemb_launch_count is the running number of kernels this
+ * library has launched in this process (its own kernels and the radix-sort passes).          */
+#define FFEMB_PHASE_FORWARD 0
+#define FFEMB_PHASE_KEYGEN 1
+#define FFEMB_PHASE_SORT 2
+#define FFEMB_PHASE_REDUCE1 3   /* level-1 segmented sum + row update */
+#define FFEMB_PHASE_REDUCE_UP 4 /* upper levels */
+#define FFEMB_PHASE_ATOMIC 5    /* atomic comparison backward */
+#define FFEMB_NUM_PHASES 6
+FFEMB_API int ffemb_profile_enable(int on);
+FFEMB_API int ffemb_profile_collect(float *ms_per_phase, int64_t *launches_per_phase);
+FFEMB_API int64_t ffemb_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FFEMB_H */

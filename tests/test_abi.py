@@ -1,0 +1,56 @@
+"""CPU tests of the drop-in boundary: libffemb.so loads, exports every symbol include/ffemb.h
+declares, and rejects bad arguments before touching a device (no compute without a GPU)."""
+import ctypes as C
+import os
+
+import pytest
+
+
+def test_library_built_and_exports_every_declared_symbol(ffemb):
+    assert os.path.exists(ffemb.library_path()), "run __graft_entry__.build() first"
+    declared = ffemb.declared_symbols()
+    assert "ffemb_forward" in declared and "ffemb_backward_sgd_batched" in declared
+    exported = set(ffemb.exported_symbols())
+    missing = [s for s in declared if s not in exported]
+    assert not missing, f"declared in ffemb.h but not exported: {missing}"
+    # nothing but the C ABI leaks out of the library
+    assert all(s.startswith("ffemb_") for s in exported), sorted(exported)
+    L = ffemb.lib()
+    assert L.ffemb_version() == 100
+
+
+def test_argument_validation_returns_codes_without_a_device(ffemb):
+    L = ffemb.lib()
+    # AGGR_MODE_NONE (20) hits assert(aggr == AGGR_MODE_AVG) in the reference kernels
+    assert L.ffemb_forward(8, 8, 8, 1, 16, 4, ffemb.AGGR_MODE_NONE, None) == 1
+    assert b"aggr" in L.ffemb_last_error()
+    assert L.ffemb_forward(8, 8, 8, 1, 0, 4, ffemb.AGGR_MODE_SUM, None) == 1      # D = 0
+    assert L.ffemb_forward(8, 8, 8, 1, 16, -1, ffemb.AGGR_MODE_SUM, None) == 1    # B < 0
+    assert L.ffemb_forward(8, None, 8, 1, 16, 4, ffemb.AGGR_MODE_SUM, None) == 1  # NULL out
+    assert L.ffemb_forward(8, 8, 8, -1, 16, 4, ffemb.AGGR_MODE_SUM, None) == 1    # L < 0
+    assert L.ffemb_forward_batched(None, 1, 16, 4, ffemb.AGGR_MODE_SUM, None) == 1
+    # empty work is a no-op, not an error (and launches nothing)
+    assert L.ffemb_forward(None, None, None, 1, 16, 0, ffemb.AGGR_MODE_SUM, None) == 0
+
+
+def test_workspace_query(ffemb):
+    L = ffemb.lib()
+    assert L.ffemb_backward_workspace(0, 10, 16) == 0
+    assert L.ffemb_backward_workspace(10, 10, 0) == 0
+    small = L.ffemb_backward_workspace(1000, 1000, 16)
+    big = L.ffemb_backward_workspace(100000, 1000, 16)
+    assert 0 < small < big
+    # keys widen to 64 bits once the global row id no longer fits 32
+    assert L.ffemb_backward_workspace(100000, 1 << 33, 16) > big
+    # missing workspace is reported, not dereferenced
+    rc = L.ffemb_backward_sgd(8, 8, 8, 1, 16, 4, 100, ffemb.AGGR_MODE_SUM, 0.01, None, 0, None)
+    assert rc == 3 and b"workspace" in L.ffemb_last_error()
+
+
+def test_compute_fails_loudly_without_library(ffemb, monkeypatch):
+    from importlib import import_module
+    b = import_module("dlrm-flexflow_b200.binding")
+    monkeypatch.setattr(b, "_lib", None)
+    monkeypatch.setattr(b, "library_path", lambda: "/nonexistent/libffemb.so")
+    with pytest.raises(ffemb.FFEmbError):
+        b.lib()

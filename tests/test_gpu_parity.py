@@ -1,0 +1,252 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the C ABI, against the
+oracle on the same seeded inputs, against the committed golden vectors of the reference's own
+code, and — at full size — through size-independent properties.
+
+Bars (north_star): gathered rows / forward sums are BIT-EXACT (sequential accumulation in j);
+updated tables and gradients agree within 1e-6 relative error where rows repeat (summation
+order), bit-exact where they do not; untouched rows are bit-identical.
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
+from conftest import golden_path  # noqa: E402
+from make_golden import CPU_CASES, GPU_CASES, make_inputs  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 1e-6  # north_star: pooled outputs / updated tables within 1e-6 relative
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    torch.cuda.set_device(0)
+    return torch
+
+
+def dev(torch, x):
+    return torch.from_numpy(np.ascontiguousarray(x)).cuda()
+
+
+def rel_err(a, b):
+    return np.max(np.abs(a.astype(np.float64) - b) / np.maximum(np.abs(b), 1e-30))
+
+
+def table_tol(W, n_dup=1):
+    """1e-6 relative on the updated table; absolute floor = 1e-6 * scale of the table."""
+    return REL_TOL * np.maximum(np.abs(W), np.abs(W).max())
+
+
+# ---------------------------------------------------------------------------------------------
+# forward
+# ---------------------------------------------------------------------------------------------
+FWD_SHAPES = [  # R, D, L, B
+    (1000, 16, 1, 4097), (1000, 64, 1, 2048), (1000, 128, 1, 513), (50, 4, 1, 100),
+    (50, 8, 1, 100), (777, 32, 1, 1000), (300, 256, 1, 64), (300, 512, 1, 33),
+    (1000, 16, 7, 1000), (1000, 64, 20, 257), (1000, 128, 20, 129), (1000, 128, 64, 65),
+    (100, 48, 5, 99), (100, 20, 3, 77), (100, 100, 9, 41), (64, 256, 33, 17), (64, 512, 3, 9),
+    (100, 18, 4, 55), (100, 7, 2, 31), (100, 1, 5, 31), (40, 130, 3, 20),  # generic (D % 4 != 0)
+    (4, 16, 1, 5000), (3, 128, 20, 300),  # tiny tables: every row hot
+]
+
+
+@pytest.mark.parametrize("R,D,L,B", FWD_SHAPES)
+@pytest.mark.parametrize("aggr", [21, 22, 122])
+def test_forward_bit_exact_vs_oracle(ffemb, oracle, torch_cuda, R, D, L, B, aggr):
+    torch = torch_cuda
+    W, idx, _ = make_inputs(R, D, L, B, seed=R + D + L + B)
+    W[0, 0] = -0.0  # out = 0 + w must give +0
+    op = ffemb.Embedding(R, D, aggr)
+    out = op.forward(dev(torch, idx), dev(torch, W))
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), oracle.forward(idx, W, aggr))
+
+
+def test_forward_golden_reference_cpu(ffemb, torch_cuda):
+    """Against the reference's own CPU tasks (tests/golden/ref_cpu.npz)."""
+    torch = torch_cuda
+    z = np.load(golden_path("ref_cpu.npz"))
+    for name, R, D, L, B, aggr, seed in CPU_CASES:
+        W, idx, _ = make_inputs(R, D, L, B, seed)
+        out = ffemb.Embedding(R, D, aggr).forward(dev(torch, idx), dev(torch, W))
+        assert np.array_equal(out.cpu().numpy(), z[name + ".fwd"]), name
+
+
+@pytest.mark.skipif(not os.path.exists(golden_path("ref_gpu.npz")), reason="GPU goldens not generated yet")
+def test_forward_and_step_golden_reference_gpu(ffemb, torch_cuda):
+    """Against the reference's own GPU kernels run on a B200 (tests/golden/ref_gpu.npz)."""
+    torch = torch_cuda
+    z = np.load(golden_path("ref_gpu.npz"))
+    for name, R, D, L, B, aggr, seed in GPU_CASES:
+        W, idx, g = make_inputs(R, D, L, B, seed)
+        op = ffemb.Embedding(R, D, aggr)
+        dW = dev(torch, W)
+        out = op.forward(dev(torch, idx), dW)
+        assert np.array_equal(out.cpu().numpy(), z[name + ".fwd"]), name
+        if D % 4 == 0:
+            op.backward_sgd(dev(torch, idx), dev(torch, g), dW, 0.01)
+            got, want = dW.cpu().numpy(), z[name + ".wnew"]
+            cnt = np.bincount(idx.reshape(-1), minlength=R)
+            assert np.array_equal(got[cnt <= 1], want[cnt <= 1]), name
+            assert np.all(np.abs(got - want) <= table_tol(W)), name
+
+
+def test_forward_batched_ragged_tables(ffemb, oracle, torch_cuda):
+    torch = torch_cuda
+    rows, bags, D, B = [5, 1000, 33, 20000, 4], [1, 3, 20, 2, 7], 32, 777
+    Ws, idxs = [], []
+    for t, (R, L) in enumerate(zip(rows, bags)):
+        W, idx, _ = make_inputs(R, D, L, B, seed=100 + t)
+        Ws.append(W), idxs.append(idx)
+    for aggr in (21, 22):
+        coll = ffemb.EmbeddingCollection([dev(torch, w) for w in Ws], bags, aggr)
+        outs = coll.forward([dev(torch, i) for i in idxs])
+        for t in range(len(rows)):
+            assert np.array_equal(outs[t].cpu().numpy(), oracle.forward(idxs[t], Ws[t], aggr)), t
+
+
+def test_forward_empty_and_unaligned(ffemb, oracle, torch_cuda):
+    torch = torch_cuda
+    W, idx, _ = make_inputs(100, 16, 2, 10, seed=1)
+    op = ffemb.Embedding(100, 16, 21)
+    out = op.forward(dev(torch, idx[:0]), dev(torch, W))  # empty batch
+    assert out.shape == (0, 16)
+    out = op.forward(dev(torch, np.zeros((6, 0), np.int64)), dev(torch, W))  # empty bags pool to 0
+    assert not out.cpu().numpy().any()
+    # a table view that is only 4-byte aligned takes the generic path and stays exact
+    buf = torch.zeros(100 * 16 + 1, device="cuda")
+    Wd = buf[1:].view(100, 16)
+    Wd.copy_(dev(torch, W))
+    out = ffemb.Embedding(100, 16, 21).forward(dev(torch, idx), Wd)
+    assert np.array_equal(out.cpu().numpy(), oracle.forward(idx, W))
+
+
+def test_error_behaviour(ffemb, torch_cuda):
+    torch = torch_cuda
+    W, idx, _ = make_inputs(10, 16, 1, 4, seed=2)
+    with pytest.raises(ffemb.FFEmbError) as e:  # A.2: AGGR_MODE_NONE is invalid
+        ffemb.Embedding(10, 16, ffemb.AGGR_MODE_NONE).forward(dev(torch, idx), dev(torch, W))
+    assert e.value.code == 1
+    with pytest.raises(ValueError):  # the task body's shape asserts
+        ffemb.Embedding(10, 16).forward(dev(torch, idx), dev(torch, W), output=torch.empty(3, 16, device="cuda"))
+    bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+    import ctypes as C
+    i = dev(torch, np.array([0, 5, 10, -1, 9], np.int64))
+    assert ffemb.lib().ffemb_check_indices(i.data_ptr(), 5, 10, bad.data_ptr(), None) == 0
+    assert bad.item() == 2
+
+
+# ---------------------------------------------------------------------------------------------
+# backward
+# ---------------------------------------------------------------------------------------------
+BWD_SHAPES = [  # R, D, L, B   (D % 4 == 0 for the sorted path)
+    (100000, 16, 1, 4097), (100000, 64, 1, 2048), (100000, 128, 1, 1000), (5000, 32, 1, 3000),
+    (1000, 16, 7, 1000), (1000, 64, 20, 257), (1000, 128, 20, 300), (2000, 128, 64, 130),
+    (4, 16, 1, 20000), (3, 128, 20, 700), (1, 64, 1, 5000), (11, 8, 3, 9999), (50, 4, 1, 100),
+    (100, 48, 5, 99), (100, 20, 3, 77), (64, 256, 9, 70), (64, 512, 3, 40), (7, 16, 64, 3000),
+]
+
+
+@pytest.mark.parametrize("R,D,L,B", BWD_SHAPES)
+@pytest.mark.parametrize("aggr", [21, 22])
+def test_backward_sgd_vs_reference_step(ffemb, oracle, torch_cuda, R, D, L, B, aggr):
+    torch = torch_cuda
+    W, idx, g = make_inputs(R, D, L, B, seed=7 * R + D + L + B)
+    want = oracle.reference_step(idx, g, W, aggr, lr=0.01)  # zero-fill -> embed_backward -> sgd_update
+    dW = dev(torch, W)
+    ffemb.Embedding(R, D, aggr).backward_sgd(dev(torch, idx), dev(torch, g), dW, 0.01)
+    torch.cuda.synchronize()
+    got = dW.cpu().numpy()
+    cnt = np.bincount(idx.reshape(-1), minlength=R)
+    assert np.array_equal(got[cnt == 0], W[cnt == 0])            # untouched rows bit-identical
+    assert np.array_equal(got[cnt == 1], want[cnt == 1])         # single lookups: same arithmetic
+    # repeated rows: summation order differs; compare against the fp64 sum
+    exact = W.astype(np.float64) - 0.01 * oracle.backward_dense_f64(idx, g, R, aggr)
+    assert np.all(np.abs(got - exact) <= table_tol(W) * np.maximum(1, np.sqrt(cnt))[:, None])
+    assert np.all(np.abs(got - want) <= 2 * table_tol(W) * np.maximum(1, np.sqrt(cnt))[:, None])
+
+
+@pytest.mark.parametrize("R,D,L,B", [(100000, 16, 1, 4097), (1000, 64, 20, 257), (4, 16, 1, 20000), (40, 18, 3, 50)])
+@pytest.mark.parametrize("aggr", [21, 22])
+def test_backward_dense_variants(ffemb, oracle, torch_cuda, R, D, L, B, aggr):
+    """API-exact unfused mode: accumulate into a dense grad (atomic and deterministic)."""
+    torch = torch_cuda
+    W, idx, g = make_inputs(R, D, L, B, seed=R + B)
+    pre = np.random.default_rng(0).uniform(-1, 1, (R, D)).astype(np.float32)  # A.5: accumulated into
+    exact = pre.astype(np.float64) + oracle.backward_dense_f64(idx, g, R, aggr)
+    cnt = np.bincount(idx.reshape(-1), minlength=R)
+    tol = REL_TOL * np.maximum(np.abs(exact), 1.0) * np.maximum(1, cnt)[:, None]
+    op = ffemb.Embedding(R, D, aggr)
+    variants = [False] if D % 4 else [False, True]
+    for det in variants:
+        dG = dev(torch, pre)
+        op.backward(dev(torch, idx), dev(torch, g), dG, deterministic=det)
+        got = dG.cpu().numpy()
+        assert np.all(np.abs(got - exact) <= tol), det
+        assert np.array_equal(got[cnt == 0], pre[cnt == 0])
+
+
+def test_backward_is_deterministic_and_atomic_is_the_comparison(ffemb, torch_cuda):
+    """Two runs of the sorted backward are bit-identical (the reference's atomics are not
+    required to be)."""
+    torch = torch_cuda
+    W, idx, g = make_inputs(37, 64, 8, 20000, seed=5)  # every row ~4300 duplicates
+    outs = []
+    for _ in range(3):
+        dW = dev(torch, W)
+        ffemb.Embedding(37, 64, 21).backward_sgd(dev(torch, idx), dev(torch, g), dW, 0.01)
+        outs.append(dW.cpu().numpy())
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+
+
+def test_backward_batched_ragged_tables(ffemb, oracle, torch_cuda):
+    torch = torch_cuda
+    rows, bags, D, B = [5, 100000, 33, 20000, 4, 1], [1, 3, 20, 2, 7, 1], 16, 2500
+    Ws, idxs, gs = [], [], []
+    for t, (R, L) in enumerate(zip(rows, bags)):
+        W, idx, g = make_inputs(R, D, L, B, seed=200 + t)
+        Ws.append(W), idxs.append(idx), gs.append(g)
+    for aggr in (21, 22):
+        dWs = [dev(torch, w) for w in Ws]
+        coll = ffemb.EmbeddingCollection(dWs, bags, aggr)
+        coll.backward_sgd([dev(torch, i) for i in idxs], [dev(torch, g) for g in gs], 0.01)
+        for t, R in enumerate(rows):
+            got = dWs[t].cpu().numpy()
+            cnt = np.bincount(idxs[t].reshape(-1), minlength=R)
+            want = oracle.reference_step(idxs[t], gs[t], Ws[t], aggr, lr=0.01)
+            exact = Ws[t].astype(np.float64) - 0.01 * oracle.backward_dense_f64(idxs[t], gs[t], R, aggr)
+            assert np.array_equal(got[cnt <= 1], want[cnt <= 1]), t
+            assert np.all(np.abs(got - exact) <= table_tol(Ws[t]) * np.maximum(1, np.sqrt(cnt))[:, None]), t
+
+
+def test_linearity_and_roundtrip_at_full_size(ffemb, torch_cuda):
+    """Size-independent properties at BASELINE config-2 scale (26 tables, D=16, B=16384) without
+    the CPU oracle: (1) forward of bag-1 indices is a pure gather; (2) with lr = 1 and
+    outgrad = forward output on distinct rows, the update zeroes exactly those rows
+    (W - 1*W == 0) and leaves the checksum of the others unchanged."""
+    torch = torch_cuda
+    wl = ffemb.synth.config(2)
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    Ws = [torch.rand((r, wl.dim), device="cuda", generator=g) + 0.5 for r in wl.rows]
+    idx = [torch.from_numpy(ffemb.synth.gen_indices(wl, t)).cuda() for t in range(wl.num_tables)]
+    coll = ffemb.EmbeddingCollection(Ws, wl.bags)
+    outs = coll.forward(idx)
+    for t in range(wl.num_tables):
+        assert torch.equal(outs[t], Ws[t][idx[t][:, 0]])
+    # distinct rows only: make the batch a permutation prefix per table where possible
+    big = [t for t in range(wl.num_tables) if wl.rows[t] >= wl.batch]
+    Wb = [Ws[t] for t in big]
+    idxb = [torch.randperm(wl.rows[t], device="cuda", generator=g)[:wl.batch].view(-1, 1).contiguous() for t in big]
+    sums_before = [w.double().sum().item() for w in Wb]
+    collb = ffemb.EmbeddingCollection(Wb, [1] * len(big))
+    outb = collb.forward(idxb)
+    gathered = [o.double().sum().item() for o in outb]
+    collb.backward_sgd(idxb, outb, 1.0)
+    torch.cuda.synchronize()
+    for k in range(len(big)):
+        assert torch.count_nonzero(Wb[k][idxb[k][:, 0]]).item() == 0
+        assert abs(Wb[k].double().sum().item() - (sums_before[k] - gathered[k])) <= 1e-6 * sums_before[k]
