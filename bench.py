@@ -1,0 +1,492 @@
+#!/usr/bin/env python
+"""bench.py — embedding lookups/s (forward + backward fused with the SGD row update) on N B200s.
+
+Contract (one JSON line on rank 0):
+  python bench.py --gpus N --steps K --warmup W            # product arm (libffemb.so, sm_100a)
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU tasks on host cores
+A "step" is one pass of the hot path over one batch of synthetic input:
+  forward gather-pool of every table  ->  [N>1: exchange of pooled rows / output-grads]
+  ->  backward sort + segmented reduce + SGD row update.
+Default workload = BASELINE.json configs[2] (MLPerf Criteo-Terabyte shape: 26 tables up to 40M
+rows x 128, multi-hot 1..20, batch 64K) — the config the north star's roofline and scaling
+targets are quoted on; it fits one B200 (96 GB of tables).  --workload 1|2|4|5 selects the
+others.  The table set and the global batch are fixed as N grows ("scaling": "strong"), tables
+placed t % N like the reference's strategy generator.
+
+value   : device-resident inputs, CUDA events on the launch stream, max over ranks.
+e2e     : the same step through the host-side operator mirror with HOST (pinned) buffers:
+          indices + output-grads copied H2D, pooled outputs copied D2H inside the timed region.
+roofline: the dominant kernel phase (per-phase CUDA events recorded inside the same timed region
+          by libffemb's profiling hooks), algorithmic bytes / duration vs MEASURED_PEAKS.json.
+cpu_baseline / --impl reference: oracle/_ref (the reference's own embedding.cc, AVX2) where it
+          can run the workload, else the oracle port, on a bounded sample, all host cores.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "embedding_lookups_per_sec_fwd_bwd"
+UNIT = "lookups/s"
+FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md fallback
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", type=int, default=3, help="BASELINE config number 1..5")
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink rows/batch (debug only)")
+    ap.add_argument("--pool", type=int, default=4, help="distinct index batches cycled")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--placement", default="modulo", choices=["modulo", "balanced"])
+    ap.add_argument("--backward", default="sorted", choices=["sorted", "atomic"],
+                    help="atomic = dense-grad atomicAdd comparison (not the product path)")
+    ap.add_argument("--rows-cap", type=int, default=0, help="cap rows per table (profiling under ncu only)")
+    ap.add_argument("--cpu-batch", type=int, default=16384)
+    ap.add_argument("--cpu-rows-cap", type=int, default=2_000_000)
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled DURING the timed region
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])), mx.append(float(f[1])), pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------
+# workload on the device
+# ---------------------------------------------------------------------------------------------
+def placement(wl, world, kind):
+    """table -> rank.  modulo = the reference's strategy generator (t % G,
+    examples/cpp/DLRM/strategies/dlrm_strategy.cc:252-256); balanced = greedy by lookups."""
+    T = wl.num_tables
+    if kind == "modulo" or world == 1:
+        return [t % world for t in range(T)]
+    load, mem, own = [0.0] * world, [0.0] * world, [0] * T
+    for t in sorted(range(T), key=lambda t: -(wl.bags[t] + 1)):
+        cands = sorted(range(world), key=lambda g: (load[g], mem[g]))
+        g = next((g for g in cands if mem[g] + wl.rows[t] * wl.dim * 4 < 150e9), cands[0])
+        own[t], load[g], mem[g] = g, load[g] + wl.bags[t] + 1, mem[g] + wl.rows[t] * wl.dim * 4
+    return own
+
+
+def zipf_indices(torch, gen, rows, shape, alpha, table_id, dev):
+    """Zipf(alpha) ranks via inverse CDF (exact head of 2^20 ranks, continuous tail), then a fixed
+    affine rank->row bijection so hot rows are not address-adjacent (synth.gen_indices)."""
+    import math
+    n = shape[0] * shape[1]
+    head = min(rows, 1 << 20)
+    w = 1.0 / torch.arange(1, head + 1, dtype=torch.float64, device=dev).pow(alpha)
+    cdf = torch.cumsum(w, 0)
+    tail = 0.0
+    if rows > head:
+        tail = ((head + 0.5) ** (1 - alpha) - (rows + 0.5) ** (1 - alpha)) / (alpha - 1)
+    total = cdf[-1].item() + tail
+    u = torch.rand(n, dtype=torch.float64, device=dev, generator=gen) * total
+    r = torch.searchsorted(cdf, u, right=True)
+    if tail > 0:
+        m = u >= cdf[-1]
+        x = ((head + 0.5) ** (1 - alpha) - (u[m] - cdf[-1]) * (alpha - 1)).pow(1.0 / (1 - alpha)) - 0.5
+        r[m] = x.long().clamp(head, rows - 1)
+    r = r.clamp_(max=rows - 1)
+    a = (1234567 + 2 * table_id * 7919) | 1
+    while math.gcd(a, rows) != 1:
+        a += 2
+    a %= rows
+    return ((r * a + 977 * (table_id + 1)) % rows).view(shape).contiguous()
+
+
+class DeviceWorkload:
+    def __init__(self, torch, pkg, wl, owned, dev, pool, seed):
+        self.torch, self.wl, self.owned, self.dev = torch, wl, owned, dev
+        g = torch.Generator(device=dev)
+        self.W, self.idx, self.outgrad, self.out, self.uniq = [], [], [], [], []
+        for t in owned:
+            g.manual_seed(seed + t)
+            R, L = wl.rows[t], wl.bags[t]
+            a = (1.0 / R) ** 0.5  # examples/cpp/DLRM/dlrm.cc:44-45
+            self.W.append(torch.empty((R, wl.dim), dtype=torch.float32, device=dev).uniform_(-a, a, generator=g))
+            batches = []
+            for k in range(pool):
+                if wl.dist == "zipf":
+                    batches.append(zipf_indices(torch, g, R, (wl.batch, L), wl.zipf_alpha, t, dev))
+                else:
+                    batches.append(torch.randint(0, R, (wl.batch, L), dtype=torch.int64, device=dev, generator=g))
+            self.idx.append(batches)
+            self.uniq.append([int(torch.unique(b).numel()) for b in batches])
+            self.outgrad.append(torch.empty((wl.batch, wl.dim), dtype=torch.float32, device=dev).uniform_(-1, 1, generator=g))
+            self.out.append(torch.empty((wl.batch, wl.dim), dtype=torch.float32, device=dev))
+        self.pool = pool
+        self.coll = pkg.EmbeddingCollection(self.W, [wl.bags[t] for t in owned], wl.aggr) if owned else None
+
+    def lookups(self):
+        return sum(self.wl.batch * self.wl.bags[t] for t in self.owned)
+
+    def bytes_per_step(self):
+        """SURVEY §8d algorithmic bytes for the owned tables, averaged over the pool:
+        fwd = 8N + 4DN + 4D*T*B ; bwd = 8N + 4D*T*B + 8D*U."""
+        D, B = self.wl.dim, self.wl.batch
+        n, T = self.lookups(), len(self.owned)
+        U = sum(sum(u) / len(u) for u in self.uniq)
+        fwd = 8 * n + 4 * D * n + 4 * D * T * B
+        bwd = 8 * n + 4 * D * T * B + 8 * D * U
+        return fwd, bwd, U
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        if rank == 0:
+            print(json.dumps(reference_arm(args, max(world, args.gpus))), flush=True)
+        return 0
+
+    import torch
+    pkg = importlib.import_module("dlrm-flexflow_b200")
+    pkg.lib()  # fails loudly when libffemb.so is missing: there is no fallback
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    wl = pkg.synth.config(args.workload, args.scale)
+    if args.rows_cap:
+        wl.rows = [min(r, args.rows_cap) for r in wl.rows]
+        wl.name += f"-rowscap{args.rows_cap}"
+    own = placement(wl, world, args.placement)
+    owned = [t for t in range(wl.num_tables) if own[t] == rank]
+    dw = DeviceWorkload(torch, pkg, wl, owned, dev, args.pool, seed=1234)
+    ex = pkg.exchange.TableWiseExchange(wl.num_tables, own, wl.batch, wl.dim, rank, world, dev) if world > 1 else None
+    stream = torch.cuda.current_stream()
+
+    wgrads = None
+    if args.backward == "atomic":  # the measured comparison: dense grad + atomics + dense update
+        wgrads = [torch.zeros_like(w) for w in dw.W]
+
+    def step(k):
+        p = k % dw.pool
+        idx = [b[p] for b in dw.idx]
+        if dw.coll is not None:
+            dw.coll.forward(idx, dw.out)
+        if ex is not None:
+            ex.forward(dw.out)            # pooled rows -> interaction input of each sample's rank
+            ex.backward(dw.outgrad)       # output-grads back to the table owners
+        if dw.coll is None:
+            return
+        if wgrads is None:
+            dw.coll.backward_sgd(idx, dw.outgrad, wl.lr)
+        else:
+            for t, w in enumerate(dw.W):
+                wgrads[t].zero_()
+                pkg.Embedding.backward_kernel(idx[t].data_ptr(), dw.outgrad[t].data_ptr(), wgrads[t].data_ptr(),
+                                              wl.bags[owned[t]], wl.dim, wl.batch, wl.aggr)
+                w.add_(wgrads[t], alpha=-wl.lr)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for k in range(args.warmup):
+        step(k)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    pkg.profile_enable(True)
+    pkg.profile_collect()
+    l0 = pkg.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for k in range(args.steps):
+        step(args.warmup + k)
+    e1.record(stream)
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    launches = pkg.launch_count() - l0
+    phase_ms, phase_launch = pkg.profile_collect()
+    pkg.profile_enable(False)
+    clocks = sampler.stop() if sampler else None
+    if dist is not None:
+        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = t.item()
+    ms_step = ms_total / args.steps
+    total_lookups = wl.lookups
+
+    # ---- e2e: host buffers, copies inside the timed region ----------------------------------
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(torch, pkg, args, wl, dw, ex, dist, dev, barrier, total_lookups)
+
+    # ---- roofline of the dominant kernel phase ----------------------------------------------
+    peak, peak_src = peaks()
+    fwd_b, bwd_b, U = dw.bytes_per_step()
+    kernel_phases = {k: v / args.steps for k, v in phase_ms.items() if v > 0}
+    D, B = wl.dim, wl.batch
+    n_own, T_own = dw.lookups(), len(owned)
+    alg = {"forward": fwd_b, "reduce1": 4 * D * T_own * B + 8 * D * U + 8 * n_own,
+           "keygen": 8 * n_own, "sort": 0, "reduce_up": 0, "atomic": bwd_b}
+    dom = max(kernel_phases, key=kernel_phases.get) if kernel_phases else "forward"
+    dom_ms = kernel_phases.get(dom, ms_step)
+    achieved = alg.get(dom, 0) / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    roof = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+            "frac": round(achieved / peak, 4), "traffic": load_traffic(dom),
+            "peak_source": peak_src, "ms_per_launch": round(dom_ms, 4),
+            "algorithmic_bytes_per_launch": int(alg.get(dom, 0)),
+            "phases_ms_per_step": {k: round(v, 4) for k, v in kernel_phases.items()},
+            "step_algorithmic_bytes": int(fwd_b + bwd_b),
+            "step_achieved_gbs": round((fwd_b + bwd_b) / (ms_step * 1e-3) / 1e9, 1),
+            "step_frac_of_peak": round((fwd_b + bwd_b) / (ms_step * 1e-3) / 1e9 / peak, 4),
+            "step_frac_of_8000": round((fwd_b + bwd_b) / (ms_step * 1e-3) / 1e9 / 8000.0, 4)}
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
+    line = {
+        "metric": METRIC, "value": total_lookups / (ms_step * 1e-3), "unit": UNIT,
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl.name, "tables": wl.num_tables, "dim": wl.dim, "batch": wl.batch,
+                   "bags": wl.bags, "rows_total": int(sum(wl.rows)), "lookups_per_step": total_lookups,
+                   "aggr": wl.aggr, "index_dist": wl.dist, "lr": wl.lr,
+                   "parallelism": ("single" if world == 1 else f"table-wise x{world} ({args.placement}) + all-to-all"),
+                   "backward": args.backward,
+                   "cache": f"inputs larger than L2: {args.pool} index batches cycled, "
+                            f"{sum(wl.rows) * wl.dim * 4 / 1e9:.1f} GB of tables, random rows",
+                   "unique_rows_per_step": int(U)},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roof,
+    }
+    if e2e is not None:
+        line["e2e"] = e2e
+    if world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(args, wl, steps=3, warmup=1)
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def load_traffic(phase):
+    """dram bytes per launch of the dominant kernel from the committed ncu summary, or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        return json.load(open(p)).get(phase)
+    except Exception:
+        return None
+
+
+def run_e2e(torch, pkg, args, wl, dw, ex, dist, dev, barrier, total_lookups):
+    """Same step, HOST buffers: per step H2D of that step's indices and output-grads from
+    pinned memory, D2H of the pooled outputs; the step ends when the D2H has landed."""
+    if dw.coll is None:
+        h_idx = h_g = h_out = []
+    else:
+        h_idx = [[b.cpu().pin_memory() for b in bs[:2]] for bs in dw.idx]
+        h_g = [g.cpu().pin_memory() for g in dw.outgrad]
+        h_out = [torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in dw.out]
+    d_idx = [bs[0].clone() for bs in dw.idx]
+    h2d = sum(x[0].numel() * 8 for x in h_idx) + sum(x.numel() * 4 for x in h_g)
+    d2h = sum(x.numel() * 4 for x in h_out)
+    stream = torch.cuda.current_stream()
+
+    def step(k):
+        p = k % 2
+        for t in range(len(d_idx)):
+            d_idx[t].copy_(h_idx[t][p], non_blocking=True)
+            dw.outgrad[t].copy_(h_g[t], non_blocking=True)
+        if dw.coll is not None:
+            dw.coll.forward(d_idx, dw.out)
+            for t in range(len(d_idx)):
+                h_out[t].copy_(dw.out[t], non_blocking=True)
+        if ex is not None:
+            ex.forward(dw.out)
+            ex.backward(dw.outgrad)
+        if dw.coll is not None:
+            dw.coll.backward_sgd(d_idx, dw.outgrad, wl.lr)
+        torch.cuda.current_stream().synchronize()  # the caller consumes the result every step
+
+    steps = max(3, min(args.steps, 10))
+    for k in range(2):
+        step(k)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for k in range(steps):
+        step(k)
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms, h2d, d2h], dtype=torch.float64, device=dev)
+        dist.all_reduce(t[:1], op=dist.ReduceOp.MAX)
+        dist.all_reduce(t[1:], op=dist.ReduceOp.SUM)
+        ms, h2d, d2h = t[0].item(), t[1].item(), t[2].item()
+    return {"value": total_lookups / (ms / steps * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
+            "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the reference's own CPU embedding tasks on the box's host cores
+# ---------------------------------------------------------------------------------------------
+def cpu_arm(args, wl, steps, warmup):
+    """Bounded sample of `wl` on the host: every table (rows capped), batch args.cpu_batch.
+    Forward = the reference's AVX2 EmbeddingLookup (oracle/_ref, src/ops/embedding.cc:23-319)
+    when built, else the oracle port; backward = the reference's backward_task_cpu for bag 1,
+    the oracle port of embed_backward (src/ops/embedding.cu:192-217) for multi-hot bags, which
+    the reference's CPU code cannot do.  One task per table, tables spread over P host threads
+    (Legion -ll:cpu P; dlrm_strategy_hetero.cc:28-36)."""
+    import numpy as np
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle as O
+    O.lib()
+    have_ref = O.ref_cpu_available(ndebug=True)
+    cores = os.cpu_count() or 1
+    P = min(cores, wl.num_tables)
+    B = min(args.cpu_batch, wl.batch)
+    cap = args.cpu_rows_cap
+    rng = np.random.default_rng(1234)
+    tabs = []
+    for t in range(wl.num_tables):
+        R = min(wl.rows[t], cap)
+        W = np.empty((R, wl.dim), np.float32)
+        rng.random(out=W, dtype=np.float32)
+        W *= 2 * (1.0 / R) ** 0.5
+        idx = [rng.integers(0, R, (B, wl.bags[t]), dtype=np.int64) for _ in range(2)]
+        g = rng.random((B, wl.dim), dtype=np.float32) * 2 - 1
+        tabs.append((R, W, idx, g, np.zeros((R, wl.dim), np.float32)))
+    kind = "reference" if have_ref and all(l == 1 for l in wl.bags) else "port"
+
+    def run_table(t, p):
+        R, W, idx, g, Wg = tabs[t]
+        L = wl.bags[t]
+        if have_ref:
+            O.ref_cpu_lookup(idx[p], W, normalize=(wl.aggr != 21), ndebug=True)
+        else:
+            O.forward(idx[p], W, 122 if wl.aggr != 21 else 21, check_range=False)
+        if have_ref and L == 1:
+            O.ref_cpu_backward_task(idx[p], g, Wg, ndebug=True)
+        else:
+            O.backward_dense(idx[p], g, R, wl.aggr, Wgrad=Wg)
+
+    order = sorted(range(wl.num_tables), key=lambda t: -wl.bags[t])  # longest tasks first
+    with ThreadPoolExecutor(P) as pool:
+        def one_step(k):
+            list(pool.map(lambda t: run_table(t, k % 2), order))
+        for k in range(warmup):
+            one_step(k)
+        t0 = time.perf_counter()
+        for k in range(steps):
+            one_step(warmup + k)
+        dt = time.perf_counter() - t0
+    lookups = B * sum(wl.bags)
+    return {"value": lookups / (dt / steps), "unit": UNIT, "cores": P, "kind": kind,
+            "ms_per_step": dt / steps * 1e3, "host_cores": cores,
+            "sample": f"{wl.name}: all {wl.num_tables} tables, batch {B} of {wl.batch}, rows capped at {cap}; "
+                      f"fwd={'reference AVX2 EmbeddingLookup (oracle/_ref)' if have_ref else 'oracle port'}, "
+                      f"bwd={'reference backward_task_cpu' if kind == 'reference' else 'oracle port of embed_backward (multi-hot)'}"
+                      f"; task bodies only (no dense zero-fill / sgd_update)"}
+
+
+def cpu_baseline(args, wl, steps, warmup):
+    try:
+        return cpu_arm(args, wl, steps, warmup)
+    except Exception as e:  # the baseline is a reported figure, never a reason to lose the line
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"failed: {e!r}"}
+
+
+def reference_arm(args, world):
+    pkg = importlib.import_module("dlrm-flexflow_b200")
+    wl = pkg.synth.config(args.workload, args.scale)
+    steps, warmup = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
+    r = cpu_arm(args, wl, steps, warmup)
+    return {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world,
+            "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl.name, "tables": wl.num_tables, "dim": wl.dim, "batch": wl.batch,
+                       "bags": wl.bags, "aggr": wl.aggr, "index_dist": wl.dist},
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
+                             "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+if __name__ == "__main__":
+    sys.exit(main())

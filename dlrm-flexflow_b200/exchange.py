@@ -1,0 +1,88 @@
+"""Exchange of pooled embeddings between table owners and the data-parallel part of the model.
+
+The reference has no collective here: each table's pooled output lives in zero-copy host memory
+and Legion copies batch slices to the consumer GPUs when the data-parallel Concat partitions it
+(/root/reference/src/ops/embedding.cu:295-298, src/ops/concat.cu:88-97).  That
+implicit all-to-all is made explicit here:
+
+  forward : owner g holds pooled [B][D] for each owned table; sample block h of every owned
+            table goes to rank h and lands in column block t of rank h's interaction input
+            x_h [B_h][T*D]  (the Concat layout, src/ops/concat.cu:211-251).
+  backward: the transpose — column block t of dx_h goes back to owner(t) rows [lo_h, hi_h).
+
+TableWiseExchange is the collective form (torch.distributed all_to_all_single: NCCL on GPUs,
+gloo in the CPU tests).  The batch split is Legion's blocked split (sharding.batch_block).
+"""
+import torch
+import torch.distributed as dist
+
+from .sharding import batch_block
+
+
+class TableWiseExchange:
+    def __init__(self, num_tables, owner, batch, dim, rank, world, device, group=None):
+        self.T, self.owner, self.B, self.D = int(num_tables), list(owner), int(batch), int(dim)
+        self.rank, self.world, self.device, self.group = rank, world, device, group
+        self.owned_by = [[t for t in range(self.T) if self.owner[t] == g] for g in range(world)]
+        self.owned = self.owned_by[rank]
+        self.blocks = [batch_block(self.B, world, h) for h in range(world)]
+        lo, hi = self.blocks[rank]
+        self.local_batch = hi - lo
+        n = len(self.owned)
+        # forward: send to h the block of h of each owned table; receive from g its tables' rows of my block
+        self.fwd_send = [n * (b[1] - b[0]) * self.D for b in self.blocks]
+        self.fwd_recv = [len(self.owned_by[g]) * self.local_batch * self.D for g in range(world)]
+        f32 = dict(dtype=torch.float32, device=device)
+        self.sendbuf = torch.empty(max(1, sum(self.fwd_send)), **f32)
+        self.recvbuf = torch.empty(max(1, sum(self.fwd_recv)), **f32)
+        self.x = torch.zeros((self.local_batch, self.T * self.D), **f32)    # interaction input (embedding part)
+        self.dx = torch.zeros((self.local_batch, self.T * self.D), **f32)   # its gradient
+
+    def _offsets(self, counts):
+        off, o = [], 0
+        for c in counts:
+            off.append(o)
+            o += c
+        return off
+
+    def forward(self, outs):
+        """outs: pooled [B][D] per owned table (owner side) -> self.x on every rank."""
+        n, D = len(self.owned), self.D
+        off = self._offsets(self.fwd_send)
+        for h, (lo, hi) in enumerate(self.blocks):
+            if n and hi > lo:
+                dst = self.sendbuf[off[h]:off[h] + self.fwd_send[h]].view(n, hi - lo, D)
+                for i in range(n):
+                    dst[i].copy_(outs[i][lo:hi])
+        dist.all_to_all_single(self.recvbuf[:sum(self.fwd_recv)], self.sendbuf[:sum(self.fwd_send)],
+                               self.fwd_recv, self.fwd_send, group=self.group)
+        roff = self._offsets(self.fwd_recv)
+        xv = self.x.view(self.local_batch, self.T, D)
+        for g in range(self.world):
+            ts = self.owned_by[g]
+            if ts and self.local_batch:
+                src = self.recvbuf[roff[g]:roff[g] + self.fwd_recv[g]].view(len(ts), self.local_batch, D)
+                for i, t in enumerate(ts):
+                    xv[:, t, :].copy_(src[i])
+        return self.x
+
+    def backward(self, outgrads):
+        """self.dx on every rank -> outgrads: [B][D] per owned table on its owner."""
+        n, D = len(self.owned), self.D
+        roff = self._offsets(self.fwd_recv)
+        dxv = self.dx.view(self.local_batch, self.T, D)
+        for g in range(self.world):
+            ts = self.owned_by[g]
+            if ts and self.local_batch:
+                dst = self.recvbuf[roff[g]:roff[g] + self.fwd_recv[g]].view(len(ts), self.local_batch, D)
+                for i, t in enumerate(ts):
+                    dst[i].copy_(dxv[:, t, :])
+        dist.all_to_all_single(self.sendbuf[:sum(self.fwd_send)], self.recvbuf[:sum(self.fwd_recv)],
+                               self.fwd_send, self.fwd_recv, group=self.group)
+        off = self._offsets(self.fwd_send)
+        for h, (lo, hi) in enumerate(self.blocks):
+            if n and hi > lo:
+                src = self.sendbuf[off[h]:off[h] + self.fwd_send[h]].view(n, hi - lo, D)
+                for i in range(n):
+                    outgrads[i][lo:hi].copy_(src[i])
+        return outgrads
