@@ -27,6 +27,8 @@
 // reference's arithmetic (g summed into 0, then one FFMA), i.e. bit-identical updates.
 #include <cub/device/device_radix_sort.cuh>
 
+#include <type_traits>
+
 #include "ffemb_internal.cuh"
 
 namespace ffemb {
@@ -35,6 +37,8 @@ static constexpr int kThreads = 256;
 static constexpr int CH1 = 64;  // level-1 tile (sorted lookups per slot)
 static constexpr int CH2 = 32;  // level-k tile (partial rows per slot)
 static constexpr int kSmallLevel = 1 << 15;  // <= this many partial slots: finish in one CTA
+static constexpr int BAG_BITS = 26;          // sort payload = (table << 26) | bag
+static constexpr uint32_t BAG_MASK = (1u << BAG_BITS) - 1;
 
 __device__ __forceinline__ void f4_add(float4 &a, const float4 &b) {
   a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
@@ -69,7 +73,7 @@ keygen_kernel(const __grid_constant__ TableBatch tb, int64_t B, K *keys, uint32_
   const int64_t b = i / L;
   const int64_t row = __ldg(td.idx + i);
   keys[td.lookup_base + i] = (K)(tb.row_base[blockIdx.y] + (uint64_t)row);
-  vals[td.lookup_base + i] = (uint32_t)(blockIdx.y * B + b);
+  vals[td.lookup_base + i] = ((uint32_t)blockIdx.y << BAG_BITS) | (uint32_t)b;
 }
 
 // table of a global row id: row_base is ascending, <= 65 entries
@@ -227,6 +231,172 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
   }
 }
 
+// ---- 3. level 1, the hot kernel ---------------------------------------------------------------
+// One slot of G lanes owns a tile of CH1 sorted lookups.  Two phases per warp:
+//   phase 1 (parallel over lanes): every lane turns its share of the warp's SLOTS*CH1 entries
+//     into a 16-byte descriptor in shared memory {output-grad row address, table row address if
+//     the entry ENDS its run of equal keys, else 0}.  All integer decoding (table id, bag id,
+//     run ends) happens here, once per entry, off the serial path.
+//   phase 2 (serial per slot, no warp collectives): walk the tile in order, UNR entries per
+//     group, software-pipelined (group k+1's loads are issued before group k is consumed).  Per
+//     entry: one broadcast LDS.128, one 16-byte gather of the output-grad row fragment per lane
+//     (L2 evict_last: a table's output-grad is re-read L times while its rows are reduced) and,
+//     for run ends, the table row (L2 evict_first: touched once per step), then FADDs in sorted
+//     order and at a run end the FFMA + store.
+// Runs cut by a tile edge leave as partial rows for the upper levels (same contract as before).
+struct __align__(16) EntryDesc {
+  const float *gp;  // output-grad row of this lookup (nullptr: past the end of the array)
+  float *wp;        // table row to update when this entry ends its run, else nullptr
+};
+
+template <int G> struct L1Threads { static constexpr int value = G >= 16 ? 256 : (G >= 4 ? 128 : (G == 2 ? 64 : 32)); };
+
+template <typename K, int G, int C, int MODE, bool AVG>
+__global__ void __launch_bounds__(L1Threads<G>::value, 512 / L1Threads<G>::value)
+reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
+               const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
+               float *rows_out) {
+  constexpr int THREADS = L1Threads<G>::value;
+  constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
+  constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
+  constexpr int NG = CH1 / UNR;
+  constexpr K INV = KeyTraits<K>::INV;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  EntryDesc *wd = reinterpret_cast<EntryDesc *>(smem_raw) + warp * EPW;
+  float *wscale = reinterpret_cast<float *>(smem_raw + sizeof(EntryDesc) * WARPS * EPW) + warp * EPW;
+  const int64_t wbase = ((int64_t)blockIdx.x * WARPS + warp) * EPW;
+  if (wbase >= n) return;  // warp-uniform; only __syncwarp below
+  const int D4 = D >> 2;
+
+  // ---- phase 1 ----
+#pragma unroll
+  for (int i = 0; i < EPW / 32; i++) {
+    const int e = i * 32 + lane;
+    const int64_t p = wbase + e;
+    EntryDesc d;
+    d.gp = nullptr;
+    d.wp = nullptr;
+    if (p < n) {
+      const K k = keys[p];
+      const uint32_t v = vals[p];
+      const bool is_end = (p + 1 == n) || (keys[p + 1] != k);
+      const uint32_t t = v >> BAG_BITS, b = v & BAG_MASK;
+      d.gp = tb.t[t].out + (int64_t)b * D;
+      if (is_end) d.wp = tb.t[t].table + (int64_t)((uint64_t)k - tb.row_base[t]) * D;
+      if (AVG) wscale[e] = (float)tb.t[t].L;
+    }
+    wd[e] = d;
+  }
+  __syncwarp();
+
+  // ---- phase 2 ----
+  const int sub = lane / G, sl = lane % G;
+  const int64_t tile = wbase / CH1 + sub;
+  const int64_t t0 = tile * CH1;
+  if (t0 >= n) return;  // this slot's tile is empty (its descriptors are all null)
+  const EntryDesc *dq = wd + sub * CH1;
+  const float *sq = wscale + sub * CH1;
+  const int cnt = (int)min((int64_t)CH1, n - t0);
+  bool first_open = (t0 > 0) && (keys[t0 - 1] == keys[t0]);  // first run continues the previous tile
+  bool pending = false, wrote_head = false;
+  const uint64_t pol_keep = policy_evict_last(), pol_stream = policy_evict_first();
+
+  float4 acc[C];
+#pragma unroll
+  for (int c = 0; c < C; c++) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 g[2][UNR][C], w[2][UNR][C];
+  float *wp[2][UNR];
+  bool ok[2][UNR];
+
+  auto issue = [&](auto BF, int grp) {
+    constexpr int bf = decltype(BF)::value;
+#pragma unroll
+    for (int u = 0; u < UNR; u++) {
+      const EntryDesc d = dq[grp * UNR + u];
+      ok[bf][u] = d.gp != nullptr;
+      wp[bf][u] = d.wp;
+      if (d.gp) {
+#pragma unroll
+        for (int c = 0; c < C; c++)
+          if (sl + c * G < D4) g[bf][u][c] = ldg_row_hint(d.gp + 4 * (sl + c * G), pol_keep);
+      }
+      if (d.wp) {
+#pragma unroll
+        for (int c = 0; c < C; c++)
+          if (sl + c * G < D4) w[bf][u][c] = ld_row_hint(d.wp + 4 * (sl + c * G), pol_stream);
+      }
+    }
+  };
+  auto consume = [&](auto BF, int grp) {
+    constexpr int bf = decltype(BF)::value;
+#pragma unroll
+    for (int u = 0; u < UNR; u++) {
+      if (!ok[bf][u]) continue;
+#pragma unroll
+      for (int c = 0; c < C; c++) {
+        if (sl + c * G < D4) {
+          float4 x = g[bf][u][c];
+          if (AVG) x = f4_div(x, sq[grp * UNR + u]);  // g / in_dim per element, embedding.cu:210
+          f4_add(acc[c], x);
+        }
+      }
+      pending = true;
+      if (wp[bf][u]) {
+        if (first_open) {  // head partial: the run began in an earlier tile
+          if (sl == 0) keys_out[2 * tile] = keys[t0 + grp * UNR + u];
+#pragma unroll
+          for (int c = 0; c < C; c++)
+            if (sl + c * G < D4) st_f4(rows_out + (2 * tile) * (int64_t)D + 4 * (sl + c * G), acc[c]);
+          wrote_head = true;
+        } else {  // complete run: the one read-modify-write of this table row
+#pragma unroll
+          for (int c = 0; c < C; c++) {
+            if (sl + c * G < D4) {
+              float4 o = w[bf][u][c];
+              if (MODE == APPLY_SGD) {  // W -= lr*gt, contracted like the reference's FFMA
+                o.x = fmaf(-acc[c].x, lr, o.x); o.y = fmaf(-acc[c].y, lr, o.y);
+                o.z = fmaf(-acc[c].z, lr, o.z); o.w = fmaf(-acc[c].w, lr, o.w);
+              } else {
+                f4_add(o, acc[c]);
+              }
+              st_row_hint(wp[bf][u] + 4 * (sl + c * G), o, pol_stream);
+            }
+          }
+        }
+        first_open = false;
+        pending = false;
+#pragma unroll
+        for (int c = 0; c < C; c++) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  };
+  using B0 = std::integral_constant<int, 0>;
+  using B1 = std::integral_constant<int, 1>;
+  issue(B0{}, 0);
+#pragma unroll 1
+  for (int grp = 0; grp < NG; grp += 2) {
+    issue(B1{}, grp + 1);
+    consume(B0{}, grp);
+    if (grp + 2 < NG && (grp + 2) * UNR < cnt) issue(B0{}, grp + 2);
+    else {
+#pragma unroll
+      for (int u = 0; u < UNR; u++) ok[0][u] = false;
+    }
+    consume(B1{}, grp + 1);
+    if ((grp + 2) * UNR >= cnt) break;
+  }
+  if (pending) {  // tail partial: the run goes on in a later tile
+#pragma unroll
+    for (int c = 0; c < C; c++)
+      if (sl + c * G < D4) st_f4(rows_out + (2 * tile + 1) * (int64_t)D + 4 * (sl + c * G), acc[c]);
+  }
+  if (sl == 0) {
+    if (!wrote_head) keys_out[2 * tile] = INV;
+    keys_out[2 * tile + 1] = pending ? keys[t0 + cnt - 1] : INV;
+  }
+}
+
 template <typename K, int G, int C, bool LEVEL1, int MODE>
 __global__ void __launch_bounds__(kThreads)
 reduce_level_kernel(const __grid_constant__ TableBatch tb, const K *keys, const uint32_t *vals,
@@ -362,9 +532,16 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
   K *pk0 = (K *)c.pkeys[0], *pk1 = (K *)c.pkeys[1];
   {
     ProfScope prof(FFEMB_PHASE_REDUCE1, 1, s);
-    reduce_level_kernel<K, G, C, true, MODE>
-        <<<(unsigned)((ntiles1 + slots_per_cta - 1) / slots_per_cta), kThreads, 0, s>>>(
-            tb, keys_b, c.vals_b, nullptr, n, CH1, D, (uint32_t)B, aggr, lr, pk0, c.prows[0]);
+    constexpr int T1 = L1Threads<G>::value;
+    constexpr int EPC = (T1 / 32) * SLOTS * CH1;  // entries per CTA
+    const unsigned grid1 = (unsigned)((n + EPC - 1) / EPC);
+    if (aggr == FFEMB_AGGR_SUM) {
+      reduce1_kernel<K, G, C, MODE, false><<<grid1, T1, EPC * sizeof(EntryDesc), s>>>(
+          tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0]);
+    } else {
+      reduce1_kernel<K, G, C, MODE, true><<<grid1, T1, EPC * (sizeof(EntryDesc) + sizeof(float)), s>>>(
+          tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0]);
+    }
   }
   int64_t m = 2 * ntiles1;
   if (ntiles1 > 1) {
@@ -412,7 +589,7 @@ int launch_backward_sorted(const TableBatch &tb, int64_t D, int64_t B, int aggr,
     set_error("sorted backward needs D %% 4 == 0 and D <= 512 (got %lld)", (long long)D);
     return FFEMB_EINVAL;
   }
-  if (n >= (1ll << 31) || (int64_t)tb.num_tables * B >= (1ll << 32)) {
+  if (n >= (1ll << 31) || B > (1ll << BAG_BITS)) {
     set_error("sorted backward: too many lookups for one call (%lld)", (long long)n);
     return FFEMB_EINVAL;
   }

@@ -69,6 +69,53 @@ __device__ __forceinline__ void st_stream(float *p, float4 v) {
                "f"(v.y), "f"(v.z), "f"(v.w)
                : "memory");
 }
+// ---- L2 eviction-priority hints (createpolicy + .L2::cache_hint) ---------------------------
+// evict_last : gathered data that is re-read soon (output-grad rows of the table being reduced,
+//              rows of tables small enough to live in the 126 MB L2);
+// evict_first: data touched once per step (rows of big tables, index streams, pooled outputs),
+//              so that it does not push the former out.
+__device__ __forceinline__ uint64_t policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_normal() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+// read-only 16-byte gather with an L2 policy (no L1 allocation)
+__device__ __forceinline__ float4 ldg_row_hint(const float *p, uint64_t pol) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p), "l"(pol));
+  return v;
+}
+// coherent 16-byte load / store with an L2 policy (table rows that this kernel also writes)
+__device__ __forceinline__ float4 ld_row_hint(const float *p, uint64_t pol) {
+  float4 v;
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p), "l"(pol)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_row_hint(float *p, float4 v, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p),
+               "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol)
+               : "memory");
+}
+__device__ __forceinline__ int64_t ldg_idx_stream(const int64_t *p, uint64_t pol) {
+  int64_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.b64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
+  return v;
+}
 __device__ __forceinline__ int64_t shfl_i64(int64_t v, int src) {
   int lo = __shfl_sync(0xffffffffu, (int)(v & 0xffffffffll), src);
   int hi = __shfl_sync(0xffffffffu, (int)(v >> 32), src);
