@@ -36,7 +36,7 @@ namespace ffemb {
 static constexpr int kThreads = 256;
 static constexpr int CH1 = 64;  // level-1 tile (sorted lookups per slot)
 static constexpr int CH2 = 32;  // level-k tile (partial rows per slot)
-static constexpr int kSmallLevel = 1 << 15;  // <= this many partial slots: finish in one CTA
+static constexpr int kSmallLevel = 1 << 12;  // <= this many partial slots: finish in one CTA
 static constexpr int BAG_BITS = 26;          // sort payload = (table << 26) | bag
 static constexpr uint32_t BAG_MASK = (1u << BAG_BITS) - 1;
 
@@ -45,6 +45,18 @@ __device__ __forceinline__ void f4_add(float4 &a, const float4 &b) {
 }
 __device__ __forceinline__ float4 f4_div(float4 a, float d) {
   return make_float4(a.x / d, a.y / d, a.z / d, a.w / d);
+}
+// a / d, correctly rounded, without the division subroutine: r = RN(1/d), q = RN(a*r), then two
+// exact-residual corrections (Markstein).  Valid while no intermediate under/overflows, i.e. for
+// every gradient that is not denormal-small; d is a bag width (1 .. 2^31).
+__device__ __forceinline__ float div_rn(float a, float d, float r) {
+  float q = a * r;
+  q = fmaf(fmaf(-d, q, a), r, q);
+  q = fmaf(fmaf(-d, q, a), r, q);
+  return q;
+}
+__device__ __forceinline__ float4 f4_div_rn(float4 a, float d, float r) {
+  return make_float4(div_rn(a.x, d, r), div_rn(a.y, d, r), div_rn(a.z, d, r), div_rn(a.w, d, r));
 }
 __device__ __forceinline__ float4 ld_f4(const float *p) { return *reinterpret_cast<const float4 *>(p); }
 __device__ __forceinline__ void st_f4(float *p, float4 v) { *reinterpret_cast<float4 *>(p) = v; }
@@ -251,7 +263,7 @@ struct __align__(16) EntryDesc {
 
 template <int G> struct L1Threads { static constexpr int value = G >= 16 ? 256 : (G >= 4 ? 128 : (G == 2 ? 64 : 32)); };
 
-template <typename K, int G, int C, int MODE, bool AVG>
+template <typename K, int G, int C, int MODE, bool AVG, bool PIPE>
 __global__ void __launch_bounds__(L1Threads<G>::value, 512 / L1Threads<G>::value)
 reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
                const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
@@ -264,7 +276,7 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   EntryDesc *wd = reinterpret_cast<EntryDesc *>(smem_raw) + warp * EPW;
-  float *wscale = reinterpret_cast<float *>(smem_raw + sizeof(EntryDesc) * WARPS * EPW) + warp * EPW;
+  float2 *wscale = reinterpret_cast<float2 *>(smem_raw + sizeof(EntryDesc) * WARPS * EPW) + warp * EPW;
   const int64_t wbase = ((int64_t)blockIdx.x * WARPS + warp) * EPW;
   if (wbase >= n) return;  // warp-uniform; only __syncwarp below
   const int D4 = D >> 2;
@@ -284,7 +296,7 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
       const uint32_t t = v >> BAG_BITS, b = v & BAG_MASK;
       d.gp = tb.t[t].out + (int64_t)b * D;
       if (is_end) d.wp = tb.t[t].table + (int64_t)((uint64_t)k - tb.row_base[t]) * D;
-      if (AVG) wscale[e] = (float)tb.t[t].L;
+      if (AVG) wscale[e] = make_float2((float)tb.t[t].L, __frcp_rn((float)tb.t[t].L));
     }
     wd[e] = d;
   }
@@ -296,12 +308,11 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
   const int64_t t0 = tile * CH1;
   if (t0 >= n) return;  // this slot's tile is empty (its descriptors are all null)
   const EntryDesc *dq = wd + sub * CH1;
-  const float *sq = wscale + sub * CH1;
+  const float2 *sq = wscale + sub * CH1;
   const int cnt = (int)min((int64_t)CH1, n - t0);
   bool first_open = (t0 > 0) && (keys[t0 - 1] == keys[t0]);  // first run continues the previous tile
   bool pending = false, wrote_head = false;
   const uint64_t pol_keep = policy_evict_last(), pol_stream = policy_evict_first();
-
   float4 acc[C];
 #pragma unroll
   for (int c = 0; c < C; c++) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -309,92 +320,167 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
   float *wp[2][UNR];
   bool ok[2][UNR];
 
-  auto issue = [&](auto BF, int grp) {
-    constexpr int bf = decltype(BF)::value;
+  if constexpr (PIPE) {
+    // Gathers that miss L2 (output-grad of one table larger than L2): latency-bound.  The loop
+    // body is branch-free (predicated loads/stores + selects) so that ptxas keeps the two
+    // register buffers on separate scoreboard barriers and group k+1's loads really are in
+    // flight while group k is added (a branch in the body puts every load on one barrier).
+    int head_e = 0;
+    bool own[C];
 #pragma unroll
-    for (int u = 0; u < UNR; u++) {
-      const EntryDesc d = dq[grp * UNR + u];
-      ok[bf][u] = d.gp != nullptr;
-      wp[bf][u] = d.wp;
-      if (d.gp) {
+    for (int c = 0; c < C; c++) own[c] = sl + c * G < D4;
+    float *const head_row = rows_out + (2 * tile) * (int64_t)D;
 #pragma unroll
-        for (int c = 0; c < C; c++)
-          if (sl + c * G < D4) g[bf][u][c] = ldg_row_hint(d.gp + 4 * (sl + c * G), pol_keep);
-      }
-      if (d.wp) {
+    for (int i = 0; i < 2; i++)
 #pragma unroll
-        for (int c = 0; c < C; c++)
-          if (sl + c * G < D4) w[bf][u][c] = ld_row_hint(d.wp + 4 * (sl + c * G), pol_stream);
-      }
-    }
-  };
-  auto consume = [&](auto BF, int grp) {
-    constexpr int bf = decltype(BF)::value;
+      for (int u = 0; u < UNR; u++)
 #pragma unroll
-    for (int u = 0; u < UNR; u++) {
-      if (!ok[bf][u]) continue;
+        for (int c = 0; c < C; c++) g[i][u][c] = w[i][u][c] = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto issue = [&](int bf, int grp) {
 #pragma unroll
-      for (int c = 0; c < C; c++) {
-        if (sl + c * G < D4) {
-          float4 x = g[bf][u][c];
-          if (AVG) x = f4_div(x, sq[grp * UNR + u]);  // g / in_dim per element, embedding.cu:210
-          f4_add(acc[c], x);
+      for (int u = 0; u < UNR; u++) {
+        const EntryDesc d = dq[min(grp * UNR + u, CH1 - 1)];
+        const bool in = grp < NG;
+        ok[bf][u] = in && d.gp != nullptr;
+        wp[bf][u] = in ? d.wp : nullptr;
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+          ldg_row_hint_if(g[bf][u][c], d.gp + 4 * (sl + c * G), pol_keep, ok[bf][u] && own[c]);
+          ld_row_hint_if(w[bf][u][c], d.wp + 4 * (sl + c * G), pol_stream, wp[bf][u] != nullptr && own[c]);
         }
       }
-      pending = true;
-      if (wp[bf][u]) {
-        if (first_open) {  // head partial: the run began in an earlier tile
-          if (sl == 0) keys_out[2 * tile] = keys[t0 + grp * UNR + u];
+    };
+    auto consume = [&](int bf, int grp) {
 #pragma unroll
+      for (int u = 0; u < UNR; u++) {
+        const bool on = ok[bf][u];
+        const bool end = on && wp[bf][u] != nullptr;
+        const bool head = end && first_open;  // head partial: the run began in an earlier tile
+        float2 sc = make_float2(1.f, 1.f);
+        if (AVG) sc = sq[min(grp * UNR + u, CH1 - 1)];
+        float *dst = head ? head_row : wp[bf][u];
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+          float4 x = g[bf][u][c];
+          if (AVG) x = f4_div_rn(x, sc.x, sc.y);  // g / in_dim per element, embedding.cu:210
+          if (!on) x = make_float4(0.f, 0.f, 0.f, 0.f);
+          f4_add(acc[c], x);
+          float4 o = w[bf][u][c];
+          if (MODE == APPLY_SGD) {  // W -= lr*gt, contracted like the reference's FFMA
+            o.x = fmaf(-acc[c].x, lr, o.x); o.y = fmaf(-acc[c].y, lr, o.y);
+            o.z = fmaf(-acc[c].z, lr, o.z); o.w = fmaf(-acc[c].w, lr, o.w);
+          } else {
+            f4_add(o, acc[c]);
+          }
+          if (head) o = acc[c];
+          st_row_hint_if(dst + 4 * (sl + c * G), o, pol_stream, end && own[c]);
+          if (end) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        head_e = head ? grp * UNR + u : head_e;
+        wrote_head = wrote_head || head;
+        pending = end ? false : (pending || on);
+        first_open = first_open && !end;
+      }
+    };
+    issue(0, 0);
+#pragma unroll 1
+    for (int grp = 0; grp < NG; grp += 2) {
+      issue(1, grp + 1);
+      consume(0, grp);
+      issue(0, grp + 2);  // predicated off past the tile
+      consume(1, grp + 1);
+      if ((grp + 2) * UNR >= cnt) break;
+    }
+    if (sl == 0) keys_out[2 * tile] = wrote_head ? keys[t0 + head_e] : INV;
+  } else {
+    // Gathers that hit L2 (the usual case: one table's output-grad is a few tens of MB): the
+    // walk is instruction-bound, so the run-end handling is a branch and the common entry costs
+    // four FADDs; loads are still issued a group ahead.
+    auto issue = [&](auto BF, int grp) {
+      constexpr int bf = decltype(BF)::value;
+  #pragma unroll
+      for (int u = 0; u < UNR; u++) {
+        const EntryDesc d = dq[grp * UNR + u];
+        ok[bf][u] = d.gp != nullptr;
+        wp[bf][u] = d.wp;
+        if (d.gp) {
+  #pragma unroll
           for (int c = 0; c < C; c++)
-            if (sl + c * G < D4) st_f4(rows_out + (2 * tile) * (int64_t)D + 4 * (sl + c * G), acc[c]);
-          wrote_head = true;
-        } else {  // complete run: the one read-modify-write of this table row
-#pragma unroll
-          for (int c = 0; c < C; c++) {
-            if (sl + c * G < D4) {
-              float4 o = w[bf][u][c];
-              if (MODE == APPLY_SGD) {  // W -= lr*gt, contracted like the reference's FFMA
-                o.x = fmaf(-acc[c].x, lr, o.x); o.y = fmaf(-acc[c].y, lr, o.y);
-                o.z = fmaf(-acc[c].z, lr, o.z); o.w = fmaf(-acc[c].w, lr, o.w);
-              } else {
-                f4_add(o, acc[c]);
-              }
-              st_row_hint(wp[bf][u] + 4 * (sl + c * G), o, pol_stream);
-            }
+            if (sl + c * G < D4) g[bf][u][c] = ldg_row_hint(d.gp + 4 * (sl + c * G), pol_keep);
+        }
+        if (d.wp) {
+  #pragma unroll
+          for (int c = 0; c < C; c++)
+            if (sl + c * G < D4) w[bf][u][c] = ld_row_hint(d.wp + 4 * (sl + c * G), pol_stream);
+        }
+      }
+    };
+    auto consume = [&](auto BF, int grp) {
+      constexpr int bf = decltype(BF)::value;
+  #pragma unroll
+      for (int u = 0; u < UNR; u++) {
+        if (!ok[bf][u]) continue;
+  #pragma unroll
+        for (int c = 0; c < C; c++) {
+          if (sl + c * G < D4) {
+            float4 x = g[bf][u][c];
+            if (AVG) x = f4_div_rn(x, sq[grp * UNR + u].x, sq[grp * UNR + u].y);  // g / in_dim per element, embedding.cu:210
+            f4_add(acc[c], x);
           }
         }
-        first_open = false;
-        pending = false;
-#pragma unroll
-        for (int c = 0; c < C; c++) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+        pending = true;
+        if (wp[bf][u]) {
+          if (first_open) {  // head partial: the run began in an earlier tile
+            if (sl == 0) keys_out[2 * tile] = keys[t0 + grp * UNR + u];
+  #pragma unroll
+            for (int c = 0; c < C; c++)
+              if (sl + c * G < D4) st_f4(rows_out + (2 * tile) * (int64_t)D + 4 * (sl + c * G), acc[c]);
+            wrote_head = true;
+          } else {  // complete run: the one read-modify-write of this table row
+  #pragma unroll
+            for (int c = 0; c < C; c++) {
+              if (sl + c * G < D4) {
+                float4 o = w[bf][u][c];
+                if (MODE == APPLY_SGD) {  // W -= lr*gt, contracted like the reference's FFMA
+                  o.x = fmaf(-acc[c].x, lr, o.x); o.y = fmaf(-acc[c].y, lr, o.y);
+                  o.z = fmaf(-acc[c].z, lr, o.z); o.w = fmaf(-acc[c].w, lr, o.w);
+                } else {
+                  f4_add(o, acc[c]);
+                }
+                st_row_hint(wp[bf][u] + 4 * (sl + c * G), o, pol_stream);
+              }
+            }
+          }
+          first_open = false;
+          pending = false;
+  #pragma unroll
+          for (int c = 0; c < C; c++) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
       }
+    };
+    using B0 = std::integral_constant<int, 0>;
+    using B1 = std::integral_constant<int, 1>;
+    issue(B0{}, 0);
+  #pragma unroll 1
+    for (int grp = 0; grp < NG; grp += 2) {
+      issue(B1{}, grp + 1);
+      consume(B0{}, grp);
+      if (grp + 2 < NG && (grp + 2) * UNR < cnt) issue(B0{}, grp + 2);
+      else {
+  #pragma unroll
+        for (int u = 0; u < UNR; u++) ok[0][u] = false;
+      }
+      consume(B1{}, grp + 1);
+      if ((grp + 2) * UNR >= cnt) break;
     }
-  };
-  using B0 = std::integral_constant<int, 0>;
-  using B1 = std::integral_constant<int, 1>;
-  issue(B0{}, 0);
-#pragma unroll 1
-  for (int grp = 0; grp < NG; grp += 2) {
-    issue(B1{}, grp + 1);
-    consume(B0{}, grp);
-    if (grp + 2 < NG && (grp + 2) * UNR < cnt) issue(B0{}, grp + 2);
-    else {
-#pragma unroll
-      for (int u = 0; u < UNR; u++) ok[0][u] = false;
-    }
-    consume(B1{}, grp + 1);
-    if ((grp + 2) * UNR >= cnt) break;
+    if (sl == 0 && !wrote_head) keys_out[2 * tile] = INV;
   }
   if (pending) {  // tail partial: the run goes on in a later tile
 #pragma unroll
     for (int c = 0; c < C; c++)
       if (sl + c * G < D4) st_f4(rows_out + (2 * tile + 1) * (int64_t)D + 4 * (sl + c * G), acc[c]);
   }
-  if (sl == 0) {
-    if (!wrote_head) keys_out[2 * tile] = INV;
-    keys_out[2 * tile + 1] = pending ? keys[t0 + cnt - 1] : INV;
-  }
+  if (sl == 0) keys_out[2 * tile + 1] = pending ? keys[t0 + cnt - 1] : INV;
 }
 
 template <typename K, int G, int C, bool LEVEL1, int MODE>
@@ -535,12 +621,18 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     constexpr int T1 = L1Threads<G>::value;
     constexpr int EPC = (T1 / 32) * SLOTS * CH1;  // entries per CTA
     const unsigned grid1 = (unsigned)((n + EPC - 1) / EPC);
+    // output-grad of one table larger than (half of) L2 -> the gathers miss: pipelined variant
+    const bool pipe = B * (int64_t)D * 4 > (48ll << 20);
+    const size_t sm_sum = EPC * sizeof(EntryDesc), sm_avg = EPC * (sizeof(EntryDesc) + sizeof(float2));
+    auto go = [&](auto kern, size_t sm) {
+      kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0]);
+    };
     if (aggr == FFEMB_AGGR_SUM) {
-      reduce1_kernel<K, G, C, MODE, false><<<grid1, T1, EPC * sizeof(EntryDesc), s>>>(
-          tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0]);
+      if (pipe) go(reduce1_kernel<K, G, C, MODE, false, true>, sm_sum);
+      else go(reduce1_kernel<K, G, C, MODE, false, false>, sm_sum);
     } else {
-      reduce1_kernel<K, G, C, MODE, true><<<grid1, T1, EPC * (sizeof(EntryDesc) + sizeof(float)), s>>>(
-          tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0]);
+      if (pipe) go(reduce1_kernel<K, G, C, MODE, true, true>, sm_avg);
+      else go(reduce1_kernel<K, G, C, MODE, true, false>, sm_avg);
     }
   }
   int64_t m = 2 * ntiles1;

@@ -3,16 +3,22 @@
 // Replaces embed_forward (/root/reference/src/ops/embedding.cu:166-190), which runs one thread
 // per output float, re-reads the 8-byte index D times per bag and read-modify-writes the output
 // in memory once per bag element.  Here:
-//   * a "slot" of G = next_pow2(D/4) lanes owns one bag; every lane keeps its 16-byte fragment of
-//     the pooled row in registers and accumulates j = 0..L-1 SEQUENTIALLY, so every output
-//     element sees exactly the reference's order of fp32 additions (bit-identical results);
-//   * the bag's indices are read once, coalesced (8*G bytes per slot), and handed out with
-//     warp shuffles; row reads are 16-byte ld.global.nc, batched UNR at a time so each lane
-//     has UNR independent loads in flight;
-//   * bag width 1 (the DLRM default) takes a dedicated path with U bags per slot in flight;
-//   * all tables of a GPU go in one launch (blockIdx.y = table, descriptors in param space).
+//   * a "slot" of G = next_pow2(D/4) lanes owns a run of consecutive bags; every lane keeps its
+//     16-byte fragment of the pooled row in registers and accumulates j = 0..L-1 SEQUENTIALLY,
+//     so every output element sees exactly the reference's order of fp32 additions
+//     (bit-identical results);
+//   * the slot's indices are one contiguous stretch of the [B][L] index array: read once,
+//     coalesced, a chunk ahead, and handed out with width-G warp shuffles; row reads are 16-byte
+//     ld.global.nc issued one group ahead of the adds, so loads stay in flight across bag and
+//     chunk boundaries (bag width 1, the DLRM default, is simply the case "store after every add");
+//   * L2 eviction hints: rows of tables far larger than L2, the index stream and the pooled
+//     outputs are evict_first; rows of small tables keep normal priority and stay resident;
+//   * all tables of a GPU go in one launch: a flat grid, each CTA finds its table in a prefix
+//     table passed in parameter space.
 // HBM-bound integer/float streaming work: no tensor cores, no smem staging needed (the index
 // stream is perfectly coalesced and the rows are random 64..512-byte gathers).
+#include <stdlib.h>
+
 #include "ffemb_internal.cuh"
 
 namespace ffemb {
@@ -30,10 +36,166 @@ __device__ __forceinline__ void f4_mul(float4 &a, float m) {
   a.x *= m; a.y *= m; a.z *= m; a.w *= m;
 }
 
-// ---- general bag width -------------------------------------------------------------------
+// ---- the vector path ---------------------------------------------------------------------
+// A slot of G lanes owns `bps` consecutive bags of one table = a contiguous run of bps*L
+// indices.  The run is cut into chunks of G*K lookups: every lane holds K row numbers of the
+// chunk in registers (loaded coalesced, the NEXT chunk's already in flight), and the row loads
+// are issued UNR at a time, one group ahead of the adds (two register buffers), so a slot keeps
+// UNR..2*UNR independent 16-byte loads per lane in flight without a bubble at bag or chunk
+// boundaries.  The adds stay strictly sequential in j per output element (embedding.cu:180-188),
+// and a bag's pooled row is stored the moment its last lookup has been added.
+template <int G> struct FwdCfg { static constexpr int K = G >= 16 ? 2 : (G >= 4 ? 4 : (G == 2 ? 8 : 16)); };
+static constexpr int kFwdTargetMax = 128;            // lookups per slot when there is plenty of work
+static constexpr int64_t kStreamBytes = 64ll << 20;  // tables above this do not try to stay in L2
+static constexpr int64_t kL1Bytes = 128ll << 10;     // tables up to this are read through L1
+
+__host__ __device__ __forceinline__ int fwd_bags_per_slot(int L, int target) {
+  return L <= 0 ? target : (L >= target ? 1 : target / L);
+}
+
+// The pipelined walk of one slot.  TINY: the table fits one SM's L1, rows are read with L1
+// allocation (a handful of hot rows otherwise all queue on the same L2 slices: measured 1.1 ms
+// for a 3-row table against 0.06 ms for a 1000-row one at the same lookup count).
+// FULL: D4 == G*C, every lane of a slot owns a fragment (no per-lane width check).
+template <int G, int C, int AG, int UNR, bool FULL, bool TINY>
+__device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const float *__restrict__ W,
+                                         float *op, int L, int D, int nl, int nl_max, int sl,
+                                         uint64_t pol_rows, uint64_t pol_stream) {
+  constexpr int K = FwdCfg<G>::K, CH = G * K, NG = CH / UNR;
+  static_assert(CH % UNR == 0 && NG % 2 == 0, "group pipeline needs an even number of groups");
+  const int D4 = D >> 2;
+  const float Lf = (float)L;
+  bool own[C];  // does this lane hold fragment c of the row?
+#pragma unroll
+  for (int c = 0; c < C; c++) own[c] = FULL || (sl + c * G < D4);
+
+  uint32_t cur[K], nxt[K];
+#pragma unroll
+  for (int k = 0; k < K; k++) nxt[k] = 0u;
+  auto load_idx = [&](uint32_t (&r)[K], int base) {
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+      const int e = base + k * G + sl;
+      r[k] = e < nl ? (uint32_t)ldg_idx_stream(ip + e, pol_stream) : 0u;
+    }
+  };
+  float4 v[2][UNR][C];
+  float4 acc[C];
+#pragma unroll
+  for (int c = 0; c < C; c++) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int i = 0; i < 2; i++)
+#pragma unroll
+    for (int u = 0; u < UNR; u++)
+#pragma unroll
+      for (int c = 0; c < C; c++) v[i][u][c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  int rem = L;
+
+  // branch-free: UNR predicated LDG.128 in a row
+  auto issue = [&](int bf, const uint32_t (&r)[K], int grp, int base) {
+#pragma unroll
+    for (int u = 0; u < UNR; u++) {
+      const int e0 = grp * UNR;
+      const uint32_t row = __shfl_sync(0xffffffffu, r[(e0 + u) / G], (e0 + u) % G, G);
+      const float *rp = W + (int64_t)row * D;
+      const bool on = base + e0 + u < nl;
+#pragma unroll
+      for (int c = 0; c < C; c++) {
+        if (TINY) ldg_row_l1_if(v[bf][u][c], rp + 4 * c * G, on && own[c]);
+        else ldg_row_hint_if(v[bf][u][c], rp + 4 * c * G, pol_rows, on && own[c]);
+      }
+    }
+  };
+  // Measured (profiles/r1_notes.md): making this part branch-free too lets ptxas give the two
+  // buffers separate scoreboard barriers, but the extra selects cost more than the finer
+  // overlap wins (big-table forward 0.125 ms -> 0.19 ms), so the adds and the store branch.
+  auto consume = [&](int bf, int grp, int base) {
+#pragma unroll
+    for (int u = 0; u < UNR; u++) {
+      if (base + grp * UNR + u < nl) {
+#pragma unroll
+        for (int c = 0; c < C; c++) f4_add(acc[c], v[bf][u][c]);
+        if (--rem == 0) {  // last lookup of the bag: store the pooled row
+#pragma unroll
+          for (int c = 0; c < C; c++) {
+            if (AG == AG_MEAN) f4_mul(acc[c], 1.0f / Lf);  // one multiply by 1/len, embedding.cc:302-313
+            if (own[c]) st_row_hint(op + 4 * c * G, acc[c], pol_stream);
+            acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          op += D;
+          rem = L;
+        }
+      }
+    }
+  };
+
+  load_idx(cur, 0);
+  issue(0, cur, 0, 0);
+#pragma unroll 1
+  for (int base = 0; base < nl_max; base += CH) {
+    const bool more = base + CH < nl_max;
+    if (more) load_idx(nxt, base + CH);
+#pragma unroll
+    for (int g = 0; g < NG; g++) {  // fully unrolled: buffer, group and register numbers are constants
+      if (g + 1 < NG) issue((g + 1) & 1, cur, g + 1, base);
+      else issue(0, nxt, 0, base + CH);  // all predicated off when there is no next chunk
+      consume(g & 1, g, base);
+    }
+#pragma unroll
+    for (int k = 0; k < K; k++) cur[k] = nxt[k];
+  }
+}
+
+template <int G, int C, int AG, int UNR, bool FULL>
+__global__ void __launch_bounds__(kThreads, C >= 2 ? 2 : 4)
+fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, int64_t stream_bytes) {
+  static_assert(AG != AG_AVG, "the in-loop divide lives in fwd_avg_kernel");
+  constexpr int SLOTS = 32 / G;
+  // which table does this CTA work on?  cta_base is ascending, <= 65 entries
+  int t = 0;
+  {
+    int lo = 0, hi = tb.num_tables - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (tb.cta_base[mid] <= blockIdx.x) lo = mid; else hi = mid - 1;
+    }
+    t = lo;
+  }
+  const TableDesc &td = tb.t[t];
+  const int L = td.L;
+  const int bps = fwd_bags_per_slot(L, target);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane / G, sl = lane % G;
+  const int64_t slot = ((int64_t)(blockIdx.x - tb.cta_base[t]) * (kThreads / 32) + warp) * SLOTS + sub;
+  const int64_t bag0 = slot * bps;
+  const int nb = bag0 < B ? (int)min((int64_t)bps, B - bag0) : 0;
+  float *op = td.out + bag0 * (int64_t)D + 4 * sl;
+  const uint64_t pol_stream = policy_evict_first();
+  if (L == 0) {  // empty bags pool to 0 (out = 0, no lookups)
+    for (int i = 0; i < nb; i++, op += D)
+#pragma unroll
+      for (int c = 0; c < C; c++)
+        if (sl + c * G < (D >> 2)) st_row_hint(op + 4 * c * G, make_float4(0.f, 0.f, 0.f, 0.f), pol_stream);
+    return;
+  }
+  const int nl = nb * L;        // valid lookups of this slot
+  const int nl_max = bps * L;   // CTA-uniform trip count (the shuffles need every lane)
+  const int64_t *ip = td.idx + bag0 * (int64_t)L;
+  const float *W = td.table + 4 * sl;
+  const int64_t bytes = td.R * (int64_t)D * 4;
+  const uint64_t pol_rows = bytes > stream_bytes ? pol_stream : policy_evict_normal();
+  if (td.R > 0 && bytes <= kL1Bytes)
+    fwd_slot<G, C, AG, UNR, FULL, true>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream);
+  else
+    fwd_slot<G, C, AG, UNR, FULL, false>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream);
+}
+
+// ---- AGGR_MODE_AVG as the reference computes it (divide inside the bag loop) ----------------
+// One bag per slot, loads batched UNR at a time.  Kept apart from the pipelined kernel: the IEEE
+// division is a subroutine call on this target, which does not mix with the branch-free body.
 template <int G, int C, int AG>
 __global__ void __launch_bounds__(kThreads)
-fwd_pool_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B) {
+fwd_avg_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B) {
   constexpr int SLOTS = 32 / G;
   constexpr int UNR = (C == 1) ? 8 : (C == 2 ? 4 : 2);
   const TableDesc &td = tb.t[blockIdx.y];
@@ -94,47 +256,6 @@ fwd_pool_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B) {
   }
 }
 
-// ---- bag width 1: U bags per slot in flight ------------------------------------------------
-template <int G, int C, int U>
-__global__ void __launch_bounds__(kThreads)
-fwd_onehot_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B) {
-  constexpr int SLOTS = 32 / G;
-  constexpr int NB = SLOTS * U;  // bags per warp, <= 32
-  static_assert(NB <= 32, "one index per lane");
-  const TableDesc &td = tb.t[blockIdx.y];
-  const int D4 = D >> 2;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int sub = lane / G, sl = lane % G;
-  const int64_t bag0 = ((int64_t)blockIdx.x * (kThreads / 32) + warp) * NB;
-  if (bag0 >= B) return;  // warp-uniform
-  const int64_t mine = (lane < NB && bag0 + lane < B) ? __ldg(td.idx + bag0 + lane) : 0;
-  const float *__restrict__ W = td.table;
-  float4 v[U][C];
-#pragma unroll
-  for (int u = 0; u < U; u++) {
-    const int64_t r = shfl_i64(mine, u * SLOTS + sub);
-    const float *rp = W + r * (int64_t)D;
-#pragma unroll
-    for (int c = 0; c < C; c++)
-      if (sl + c * G < D4) v[u][c] = ldg_row(rp + 4 * (sl + c * G));
-  }
-#pragma unroll
-  for (int u = 0; u < U; u++) {
-    const int64_t bag = bag0 + u * SLOTS + sub;
-    if (bag < B) {
-      float *op = td.out + bag * (int64_t)D;
-#pragma unroll
-      for (int c = 0; c < C; c++) {
-        if (sl + c * G < D4) {
-          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);  // out = 0; out += w  (-0 -> +0 like the ref)
-          f4_add(a, v[u][c]);
-          st_stream(op + 4 * (sl + c * G), a);
-        }
-      }
-    }
-  }
-}
-
 // ---- any D / any alignment: one warp per bag, lane per float --------------------------------
 __global__ void __launch_bounds__(kThreads)
 fwd_generic_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int ag) {
@@ -156,23 +277,43 @@ fwd_generic_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int 
   }
 }
 
+template <int G, int C, bool FULL>
+static void launch_vec2(const TableBatch &tb, int D, int64_t B, int ag, int target, unsigned ctas,
+                        cudaStream_t s) {
+  constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
+  int64_t stream_bytes = kStreamBytes;
+  if (const char *e = getenv("FFEMB_STREAM_MB")) stream_bytes = atoll(e) << 20;  // tuning aid
+  switch (ag) {
+    case AG_SUM: fwd_kernel<G, C, AG_SUM, UNR, FULL><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes); break;
+    default: fwd_kernel<G, C, AG_MEAN, UNR, FULL><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes); break;
+  }
+}
+
 template <int G, int C>
-static void launch_vec(const TableBatch &tb, int D, int64_t B, int ag, bool onehot, cudaStream_t s) {
+static void launch_vec(const TableBatch &tb_in, int D, int64_t B, int ag, cudaStream_t s) {
   constexpr int SLOTS = 32 / G;
-  if (onehot) {
-    constexpr int U = (C == 1) ? (G < 8 ? G : 8) : (C == 2 ? 4 : 2);
-    const int64_t per_cta = (int64_t)(kThreads / 32) * SLOTS * U;
-    dim3 grid((unsigned)((B + per_cta - 1) / per_cta), tb.num_tables);
-    fwd_onehot_kernel<G, C, U><<<grid, kThreads, 0, s>>>(tb, D, B);
+  if (ag == AG_AVG) {
+    const int64_t per_cta = (int64_t)(kThreads / 32) * SLOTS;
+    dim3 grid((unsigned)((B + per_cta - 1) / per_cta), tb_in.num_tables);
+    fwd_avg_kernel<G, C, AG_AVG><<<grid, kThreads, 0, s>>>(tb_in, D, B);
     return;
   }
-  const int64_t per_cta = (int64_t)(kThreads / 32) * SLOTS;
-  dim3 grid((unsigned)((B + per_cta - 1) / per_cta), tb.num_tables);
-  switch (ag) {
-    case AG_SUM: fwd_pool_kernel<G, C, AG_SUM><<<grid, kThreads, 0, s>>>(tb, D, B); break;
-    case AG_AVG: fwd_pool_kernel<G, C, AG_AVG><<<grid, kThreads, 0, s>>>(tb, D, B); break;
-    default: fwd_pool_kernel<G, C, AG_MEAN><<<grid, kThreads, 0, s>>>(tb, D, B); break;
+  TableBatch tb = tb_in;
+  // lookups per slot: enough slots to fill 148 SMs x 64 warps first, then amortise per-slot cost
+  int64_t n = 0;
+  for (int t = 0; t < tb.num_tables; t++) n += B * (tb.t[t].L > 0 ? tb.t[t].L : 1);
+  int target = 8;
+  while (target < kFwdTargetMax && n / (2 * target) >= (int64_t)148 * 64 * SLOTS) target *= 2;
+  if (const char *e = getenv("FFEMB_FWD_TARGET")) target = atoi(e);  // tuning aid
+  uint32_t ctas = 0;
+  for (int t = 0; t < tb.num_tables; t++) {
+    tb.cta_base[t] = ctas;
+    const int64_t per_cta = (int64_t)fwd_bags_per_slot(tb.t[t].L, target) * SLOTS * (kThreads / 32);
+    ctas += (uint32_t)((B + per_cta - 1) / per_cta);
   }
+  tb.cta_base[tb.num_tables] = ctas;
+  if (D / 4 == G * C) launch_vec2<G, C, true>(tb, D, B, ag, target, ctas, s);
+  else launch_vec2<G, C, false>(tb, D, B, ag, target, ctas, s);
 }
 
 int launch_forward(const TableBatch &tb, int64_t D64, int64_t B, int aggr, cudaStream_t s) {
@@ -181,24 +322,22 @@ int launch_forward(const TableBatch &tb, int64_t D64, int64_t B, int aggr, cudaS
   if (B == 0 || tb.num_tables == 0) return FFEMB_OK;
   ProfScope prof(FFEMB_PHASE_FORWARD, 1, s);
   bool vec = (D % 4 == 0) && D <= 512;
-  bool onehot = true;
-  for (int t = 0; t < tb.num_tables; t++) {
-    vec = vec && (((uintptr_t)tb.t[t].table | (uintptr_t)tb.t[t].out) % 16 == 0);
-    onehot = onehot && tb.t[t].L == 1;
-  }
+  for (int t = 0; t < tb.num_tables; t++)
+    vec = vec && (((uintptr_t)tb.t[t].table | (uintptr_t)tb.t[t].out) % 16 == 0) &&
+          tb.t[t].R <= (1ll << 32);  // row numbers travel as 32 bits inside the kernel
   if (!vec) {
     dim3 grid((unsigned)((B + kThreads / 32 - 1) / (kThreads / 32)), tb.num_tables);
     fwd_generic_kernel<<<grid, kThreads, 0, s>>>(tb, D, B, ag);
   } else {
     const int D4 = D / 4;
-    if (D4 <= 1) launch_vec<1, 1>(tb, D, B, ag, onehot, s);
-    else if (D4 <= 2) launch_vec<2, 1>(tb, D, B, ag, onehot, s);
-    else if (D4 <= 4) launch_vec<4, 1>(tb, D, B, ag, onehot, s);
-    else if (D4 <= 8) launch_vec<8, 1>(tb, D, B, ag, onehot, s);
-    else if (D4 <= 16) launch_vec<16, 1>(tb, D, B, ag, onehot, s);
-    else if (D4 <= 32) launch_vec<32, 1>(tb, D, B, ag, onehot, s);
-    else if (D4 <= 64) launch_vec<32, 2>(tb, D, B, ag, onehot, s);
-    else launch_vec<32, 4>(tb, D, B, ag, onehot, s);
+    if (D4 <= 1) launch_vec<1, 1>(tb, D, B, ag, s);
+    else if (D4 <= 2) launch_vec<2, 1>(tb, D, B, ag, s);
+    else if (D4 <= 4) launch_vec<4, 1>(tb, D, B, ag, s);
+    else if (D4 <= 8) launch_vec<8, 1>(tb, D, B, ag, s);
+    else if (D4 <= 16) launch_vec<16, 1>(tb, D, B, ag, s);
+    else if (D4 <= 32) launch_vec<32, 1>(tb, D, B, ag, s);
+    else if (D4 <= 64) launch_vec<32, 2>(tb, D, B, ag, s);
+    else launch_vec<32, 4>(tb, D, B, ag, s);
   }
   return cuda_fail(cudaGetLastError(), "forward launch");
 }

@@ -10,7 +10,18 @@
 #error "libffemb is written for sm_100a (B200) only"
 #endif
 
+#include <type_traits>
+
 namespace ffemb {
+
+// compile-time loop: f(std::integral_constant<int, I>{}) for I in [0, N)
+template <int I, int N, typename F>
+__device__ __forceinline__ void static_for(F &&f) {
+  if constexpr (I < N) {
+    f(std::integral_constant<int, I>{});
+    static_for<I + 1, N>(f);
+  }
+}
 
 // Descriptor array passed BY VALUE as a kernel parameter (64 x 40 B = 2.5 KB of the 4 KB
 // parameter space): no per-step H2D copy, no device-side descriptor allocation.
@@ -25,6 +36,7 @@ struct TableDesc {
 struct TableBatch {
   TableDesc t[FFEMB_MAX_TABLES];
   uint64_t row_base[FFEMB_MAX_TABLES + 1];  // first global row id of each table (bwd keys)
+  uint32_t cta_base[FFEMB_MAX_TABLES + 1];  // first CTA of each table in the flat forward grid
   int32_t num_tables;
 };
 
@@ -110,6 +122,42 @@ __device__ __forceinline__ void st_row_hint(float *p, float4 v, uint64_t pol) {
   asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p),
                "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol)
                : "memory");
+}
+// Predicated forms: ONE predicated LDG and no branch, so that a batch of them stays in a
+// straight line and ptxas can give consecutive batches their own scoreboard barriers (a load
+// wrapped in `if` becomes its own BSSY/BRA region and every such load ends up on one barrier,
+// which turns a register double buffer into a serial chain: measured, see profiles/).
+__device__ __forceinline__ void ldg_row_hint_if(float4 &v, const float *p, uint64_t pol, bool on) {
+  asm volatile(
+      "{\n .reg .pred q;\n setp.ne.b32 q, %6, 0;\n"
+      " @q ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;\n}"
+      : "+f"(v.x), "+f"(v.y), "+f"(v.z), "+f"(v.w)
+      : "l"(p), "l"(pol), "r"((int)on));
+}
+// L1-allocating variant for tables small enough to live in one SM's L1 (a handful of hot rows
+// otherwise all hit the same L2 slices: measured 1.1 ms for a 3-row table vs 0.06 ms for a
+// 1000-row one at the same lookup count)
+__device__ __forceinline__ void ldg_row_l1_if(float4 &v, const float *p, bool on) {
+  asm volatile(
+      "{\n .reg .pred q;\n setp.ne.b32 q, %5, 0;\n"
+      " @q ld.global.nc.L1::evict_last.v4.f32 {%0,%1,%2,%3}, [%4];\n}"
+      : "+f"(v.x), "+f"(v.y), "+f"(v.z), "+f"(v.w)
+      : "l"(p), "r"((int)on));
+}
+__device__ __forceinline__ void ld_row_hint_if(float4 &v, const float *p, uint64_t pol, bool on) {
+  asm volatile(
+      "{\n .reg .pred q;\n setp.ne.b32 q, %6, 0;\n"
+      " @q ld.global.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;\n}"
+      : "+f"(v.x), "+f"(v.y), "+f"(v.z), "+f"(v.w)
+      : "l"(p), "l"(pol), "r"((int)on)
+      : "memory");
+}
+__device__ __forceinline__ void st_row_hint_if(float *p, float4 v, uint64_t pol, bool on) {
+  asm volatile(
+      "{\n .reg .pred q;\n setp.ne.b32 q, %6, 0;\n"
+      " @q st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;\n}" ::"l"(p),
+      "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol), "r"((int)on)
+      : "memory");
 }
 __device__ __forceinline__ int64_t ldg_idx_stream(const int64_t *p, uint64_t pol) {
   int64_t v;
