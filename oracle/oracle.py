@@ -28,12 +28,15 @@ def build(ref=True):
     targets = ["oracle"]
     if ref and os.path.isdir("/root/reference/src/ops"):
         targets.append("ref")
+        if os.path.exists(os.path.join(HERE, "..", "dlrm-flexflow_b200", "libffemb.so")):
+            targets.append("dropin")
     subprocess.run(["make", "-s", "-C", HERE] + targets, check=True,
                    stdout=subprocess.DEVNULL, stderr=subprocess.PIPE)
     return [p for p in (os.path.join(HERE, "libffemb_oracle.so"),
                         os.path.join(HERE, "_ref", "libffref_cpu.so"),
                         os.path.join(HERE, "_ref", "libffref_cpu_ndebug.so"),
-                        os.path.join(HERE, "_ref", "libffref_gpu.so")) if os.path.exists(p)]
+                        os.path.join(HERE, "_ref", "libffref_gpu.so"),
+                        os.path.join(HERE, "_ref", "libffdropin_gpu.so")) if os.path.exists(p)]
 
 
 _lib = None
@@ -263,11 +266,8 @@ def ref_gpu_available():
     return os.path.exists(os.path.join(HERE, "_ref", "libffref_gpu.so"))
 
 
-def ref_gpu():
-    """libffref_gpu.so: all arguments are device pointers passed as ints (tensor.data_ptr())."""
-    global _ref_gpu
-    if _ref_gpu is None:
-        L = C.CDLL(os.path.join(HERE, "_ref", "libffref_gpu.so"))
+def _bind_gpu(L):
+    if True:
         L.ffref_gpu_forward_task.argtypes = [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _int]
         L.ffref_gpu_forward_task.restype = None
         L.ffref_gpu_backward_task.argtypes = [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _int]
@@ -280,5 +280,34 @@ def ref_gpu():
         L.ffref_gpu_zero_task.restype = None
         L.ffref_gpu_sgd_task.argtypes = [_vp, _vp, _i64, _i64, C.c_double, C.c_double]
         L.ffref_gpu_sgd_task.restype = None
-        _ref_gpu = L
+        L.ffref_gpu_set_workspace.argtypes = [_vp, C.c_size_t]
+        L.ffref_gpu_set_workspace.restype = None
+    return L
+
+
+def ref_gpu():
+    """libffref_gpu.so: all arguments are device pointers passed as ints (tensor.data_ptr())."""
+    global _ref_gpu
+    if _ref_gpu is None:
+        _ref_gpu = _bind_gpu(C.CDLL(os.path.join(HERE, "_ref", "libffref_gpu.so")))
     return _ref_gpu
+
+
+_dropin_gpu = None
+
+
+def dropin_gpu_available():
+    return os.path.exists(os.path.join(HERE, "_ref", "libffdropin_gpu.so"))
+
+
+def dropin_gpu():
+    """libffdropin_gpu.so: the SAME task frames and the reference's own accessor objects, with
+    the reference's embedding.cu swapped for dlrm-flexflow_b200/csrc/flexflow/embedding_ffemb.cu
+    (which calls libffemb.so).  Same entry points as ref_gpu() + the fused leaf task."""
+    global _dropin_gpu
+    if _dropin_gpu is None:
+        L = _bind_gpu(C.CDLL(os.path.join(HERE, "_ref", "libffdropin_gpu.so")))
+        L.ffdropin_gpu_backward_sgd_task.argtypes = [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _int, _f32]
+        L.ffdropin_gpu_backward_sgd_task.restype = None
+        _dropin_gpu = L
+    return _dropin_gpu

@@ -96,9 +96,13 @@ struct TaskFrame {
     regions.push_back(Legion::PhysicalRegion(base, dom));
   }
 };
+void *g_workspace = NULL;  /* FFHandler::workSpace stand-in (set by ffref_gpu_set_workspace) */
+size_t g_workspace_bytes = 0;
 EmbeddingMeta *make_meta(int aggr) {
   FFHandler h;
   memset(&h, 0, sizeof(h));
+  h.workSpace = g_workspace;
+  h.workSpaceSize = g_workspace_bytes;
   EmbeddingMeta *m = new EmbeddingMeta(h);
   m->profiling = false;
   m->aggr = (AggrMode)aggr;
@@ -106,7 +110,40 @@ EmbeddingMeta *make_meta(int aggr) {
 }
 }  // namespace
 
+#ifdef FFEMB_DROPIN
+/* the fused leaf body of dlrm-flexflow_b200/csrc/flexflow/embedding_ffemb.cu */
+void ffemb_embedding_backward_sgd_task(const Legion::Task *task,
+                                       const std::vector<Legion::PhysicalRegion> &regions,
+                                       Legion::Context ctx, Legion::Runtime *runtime);
+#endif
+
 extern "C" {
+
+/* The per-GPU scratch Legion would hand every task through FFHandler (1 GB by default,
+ * src/runtime/model.cc:2219, src/runtime/model.cu:97-109).                                   */
+void ffref_gpu_set_workspace(void *ws, size_t bytes) {
+  g_workspace = ws;
+  g_workspace_bytes = bytes;
+}
+
+#ifdef FFEMB_DROPIN
+/* Only in libffdropin_gpu.so (the drop-in's task bodies linked in place of the reference's):
+ * the opt-in fused backward + SGD leaf task; regions[2] is the table itself.                 */
+void ffdropin_gpu_backward_sgd_task(const int64_t *idx, const float *outgrad, float *W, int64_t L,
+                                    int64_t D, int64_t B, int64_t R, int aggr, float lr) {
+  TaskFrame f;
+  f.add((void *)idx, L, B);
+  f.add((void *)outgrad, D, B);
+  f.add((void *)W, R, D);
+  EmbeddingMeta *m = make_meta(aggr);
+  f.task.local_args = &m;
+  f.task.local_arglen = sizeof(m);
+  f.task.args = &lr;
+  f.task.arglen = sizeof(lr);
+  ffemb_embedding_backward_sgd_task(&f.task, f.regions, NULL, &f.runtime);
+  delete m;
+}
+#endif
 
 /* Embedding::forward_task (src/ops/embedding.cu:238-272) on device pointers; stream 0
  * (built with DISABLE_LEGION_CUDA_HIJACK, src/runtime/cuda_helper.cu:22-30).               */

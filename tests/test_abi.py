@@ -2,8 +2,11 @@
 declares, and rejects bad arguments before touching a device (no compute without a GPU)."""
 import ctypes as C
 import os
+import subprocess
 
 import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def test_library_built_and_exports_every_declared_symbol(ffemb):
@@ -54,3 +57,18 @@ def test_compute_fails_loudly_without_library(ffemb, monkeypatch):
     monkeypatch.setattr(b, "library_path", lambda: "/nonexistent/libffemb.so")
     with pytest.raises(ffemb.FFEmbError):
         b.lib()
+
+
+def test_dropin_binding_defines_the_reference_symbols():
+    """csrc/flexflow/embedding_ffemb.cu, compiled against the reference's own include/model.h,
+    defines exactly the members of class Embedding it replaces (include/model.h:1154-1186)."""
+    so = os.path.join(ROOT, "oracle", "_ref", "libffdropin_gpu.so")
+    if not os.path.exists(so):
+        pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
+    out = subprocess.run(["nm", "-DC", "--defined-only", so], stdout=subprocess.PIPE, text=True, check=True).stdout
+    for sym in ("Embedding::forward_kernel(", "Embedding::backward_kernel(", "Embedding::forward_task(",
+                "Embedding::backward_task(", "ffemb_embedding_backward_sgd_task("):
+        assert sym in out, sym
+    und = subprocess.run(["nm", "-D", "--undefined-only", so], stdout=subprocess.PIPE, text=True, check=True).stdout
+    assert "ffemb_forward" in und and "ffemb_backward_sgd" in und  # the numeric work is libffemb's
+    assert "embed_forward" not in out and "embed_backward" not in out  # none of the reference kernels

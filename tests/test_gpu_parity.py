@@ -250,3 +250,57 @@ def test_linearity_and_roundtrip_at_full_size(ffemb, torch_cuda):
     for k in range(len(big)):
         assert torch.count_nonzero(Wb[k][idxb[k][:, 0]]).item() == 0
         assert abs(Wb[k].double().sum().item() - (sums_before[k] - gathered[k])) <= 1e-6 * sums_before[k]
+
+
+# ---------------------------------------------------------------------------------------------
+# the drop-in boundary: the reference's Legion task frames driving OUR task bodies
+# ---------------------------------------------------------------------------------------------
+def _have_dropin():
+    from oracle import oracle as O
+    return O.ref_gpu_available() and O.dropin_gpu_available()
+
+
+@pytest.mark.skipif(not _have_dropin(), reason="oracle/_ref not built (needs /root/reference at build time)")
+@pytest.mark.parametrize("R,D,L,B,aggr", [(1000, 64, 1, 2048, 21), (5000, 128, 7, 700, 21), (300, 16, 5, 999, 22),
+                                          (40, 18, 3, 50, 21), (100000, 128, 20, 513, 22)])
+def test_dropin_task_bodies_match_reference_task_bodies(oracle, torch_cuda, R, D, L, B, aggr):
+    """Embedding::forward_task / backward_task of csrc/flexflow/embedding_ffemb.cu, linked in place
+    of the reference's embedding.cu behind the same (Task, PhysicalRegion) frames and the
+    reference's own TensorAccessor objects, against the reference's task bodies run here."""
+    torch = torch_cuda
+    ref, ours = oracle.ref_gpu(), oracle.dropin_gpu()
+    W, idx, g = make_inputs(R, D, L, B, seed=R + L)
+    dW, didx, dg = dev(torch, W), dev(torch, idx), dev(torch, g)
+    ws = torch.empty(64 << 20, dtype=torch.uint8, device="cuda")
+    outs = []
+    for lib in (ref, ours):
+        out = torch.full((B, D), float("nan"), device="cuda")
+        lib.ffref_gpu_forward_task(didx.data_ptr(), out.data_ptr(), dW.data_ptr(), L, D, B, R, aggr)
+        torch.cuda.synchronize()
+        outs.append(out.cpu().numpy())
+    assert np.array_equal(outs[0], outs[1])  # bit-exact, AVG-in-loop quirk included
+    cnt = np.bincount(idx.reshape(-1), minlength=R)
+    exact = oracle.backward_dense_f64(idx, g, R, aggr)
+    tol = REL_TOL * np.maximum(np.abs(exact), 1.0) * np.maximum(1, cnt)[:, None]
+    grads = {}
+    for name, lib, wsb in (("ref", ref, 0), ("ours-atomic", ours, 0), ("ours-sorted", ours, ws.numel())):
+        lib.ffref_gpu_set_workspace(ws.data_ptr() if wsb else None, wsb)
+        G = torch.zeros((R, D), device="cuda")  # Op::zero_grad ran first
+        lib.ffref_gpu_backward_task(didx.data_ptr(), dg.data_ptr(), G.data_ptr(), L, D, B, R, aggr)
+        torch.cuda.synchronize()
+        grads[name] = G.cpu().numpy()
+        assert np.all(np.abs(grads[name] - exact) <= tol), name
+    single = cnt <= 1
+    assert np.array_equal(grads["ref"][single], grads["ours-atomic"][single])
+    if D % 4 == 0:
+        assert np.array_equal(grads["ref"][single], grads["ours-sorted"][single])
+        # fused leaf task == zero-fill -> backward_task -> ps_update_task of the reference
+        Wref = dev(torch, W)
+        ref.ffref_gpu_sgd_task(dev(torch, grads["ref"]).data_ptr(), Wref.data_ptr(), R, D, 0.01, 0.0)
+        Wours = dev(torch, W)
+        ours.ffref_gpu_set_workspace(ws.data_ptr(), ws.numel())
+        ours.ffdropin_gpu_backward_sgd_task(didx.data_ptr(), dg.data_ptr(), Wours.data_ptr(), L, D, B, R, aggr, 0.01)
+        torch.cuda.synchronize()
+        a, b = Wours.cpu().numpy(), Wref.cpu().numpy()
+        assert np.array_equal(a[single], b[single])
+        assert np.all(np.abs(a - b) <= 2 * table_tol(W) * np.maximum(1, np.sqrt(cnt))[:, None])
