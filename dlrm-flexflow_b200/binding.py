@@ -81,6 +81,7 @@ def lib():
     L.ffemb_backward_dense_batched.argtypes = [tp, i32, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_workspace.argtypes = [i64, i64, i64]
     L.ffemb_backward_workspace.restype = sz
+    L.ffemb_backward_path.argtypes = [i64, i64, i64, i64]
     L.ffemb_check_indices.argtypes = [vp, i64, i64, vp, vp]
     L.ffemb_profile_enable.argtypes = [i32]
     L.ffemb_profile_collect.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_int64)]
@@ -92,7 +93,7 @@ def lib():
     return L
 
 
-PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic"]
+PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small"]
 
 
 def profile_enable(on=True):

@@ -242,6 +242,8 @@ int ffemb_profile_collect(float *ms_per_phase, int64_t *launches_per_phase) {
 
 int64_t ffemb_launch_count(void) { return (int64_t)g_launches.load(); }
 
+int ffemb_backward_path(int64_t R, int64_t L, int64_t D, int64_t B) { return backward_path(R, L, D, B); }
+
 size_t ffemb_backward_workspace(int64_t num_lookups, int64_t total_rows, int64_t D) {
   return backward_workspace_bytes(num_lookups, total_rows, D);
 }

@@ -27,6 +27,8 @@
 // reference's arithmetic (g summed into 0, then one FFMA), i.e. bit-identical updates.
 #include <cub/device/device_radix_sort.cuh>
 
+#include <stdlib.h>
+#include <string.h>
 #include <type_traits>
 
 #include "ffemb_internal.cuh"
@@ -45,15 +47,6 @@ __device__ __forceinline__ void f4_add(float4 &a, const float4 &b) {
 }
 __device__ __forceinline__ float4 f4_div(float4 a, float d) {
   return make_float4(a.x / d, a.y / d, a.z / d, a.w / d);
-}
-// a / d, correctly rounded, without the division subroutine: r = RN(1/d), q = RN(a*r), then two
-// exact-residual corrections (Markstein).  Valid while no intermediate under/overflows, i.e. for
-// every gradient that is not denormal-small; d is a bag width (1 .. 2^31).
-__device__ __forceinline__ float div_rn(float a, float d, float r) {
-  float q = a * r;
-  q = fmaf(fmaf(-d, q, a), r, q);
-  q = fmaf(fmaf(-d, q, a), r, q);
-  return q;
 }
 __device__ __forceinline__ float4 f4_div_rn(float4 a, float d, float r) {
   return make_float4(div_rn(a.x, d, r), div_rn(a.y, d, r), div_rn(a.z, d, r), div_rn(a.w, d, r));
@@ -267,7 +260,7 @@ template <typename K, int G, int C, int MODE, bool AVG, bool PIPE>
 __global__ void __launch_bounds__(L1Threads<G>::value, 512 / L1Threads<G>::value)
 reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
                const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
-               float *rows_out) {
+               float *rows_out, int flags) {
   constexpr int THREADS = L1Threads<G>::value;
   constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
@@ -296,6 +289,8 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
       const uint32_t t = v >> BAG_BITS, b = v & BAG_MASK;
       d.gp = tb.t[t].out + (int64_t)b * D;
       if (is_end) d.wp = tb.t[t].table + (int64_t)((uint64_t)k - tb.row_base[t]) * D;
+      if ((flags & 1) && is_end) prefetch_l2_bulk(d.wp, D * 4);
+      if (flags & 2) prefetch_l2_bulk(d.gp, D * 4);
       if (AVG) wscale[e] = make_float2((float)tb.t[t].L, __frcp_rn((float)tb.t[t].L));
     }
     wd[e] = d;
@@ -586,7 +581,7 @@ static Carve carve(char *base, int64_t n, int64_t total_rows, int64_t D) {
 
 size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t D) {
   if (num_lookups <= 0 || total_rows <= 0 || D <= 0 || num_lookups >= (1ll << 31)) return 0;
-  return carve(nullptr, num_lookups, total_rows, D).total;
+  return carve(nullptr, num_lookups, total_rows, D).total + small_partials_bound(D);
 }
 
 // ---- host driver -----------------------------------------------------------------------------
@@ -622,10 +617,13 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     constexpr int EPC = (T1 / 32) * SLOTS * CH1;  // entries per CTA
     const unsigned grid1 = (unsigned)((n + EPC - 1) / EPC);
     // output-grad of one table larger than (half of) L2 -> the gathers miss: pipelined variant
-    const bool pipe = B * (int64_t)D * 4 > (48ll << 20);
+    bool pipe = B * (int64_t)D * 4 > (48ll << 20);
+    int flags = 0;
+    if (const char *e = getenv("FFEMB_R1_FLAGS")) flags = atoi(e);  // tuning aid
+    if (const char *e = getenv("FFEMB_R1_PIPE")) pipe = atoi(e) != 0;
     const size_t sm_sum = EPC * sizeof(EntryDesc), sm_avg = EPC * (sizeof(EntryDesc) + sizeof(float2));
     auto go = [&](auto kern, size_t sm) {
-      kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0]);
+      kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], flags);
     };
     if (aggr == FFEMB_AGGR_SUM) {
       if (pipe) go(reduce1_kernel<K, G, C, MODE, false, true>, sm_sum);
@@ -671,26 +669,61 @@ static int dispatch_g(const TableBatch &tb, int D, int64_t B, int aggr, float lr
   return run_sorted<K, 32, 4, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
 }
 
-int launch_backward_sorted(const TableBatch &tb, int64_t D, int64_t B, int aggr, float lr,
+int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int aggr, float lr,
                            ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s) {
-  int64_t n = 0;
-  for (int t = 0; t < tb.num_tables; t++) n += B * tb.t[t].L;
-  const int64_t rows = (int64_t)tb.row_base[tb.num_tables];
-  if (n == 0) return FFEMB_OK;
+  int64_t n_all = 0;
+  for (int t = 0; t < tb_all.num_tables; t++) n_all += B * tb_all.t[t].L;
+  if (n_all == 0) return FFEMB_OK;
   if (D % 4 != 0 || D > 512) {
     set_error("sorted backward needs D %% 4 == 0 and D <= 512 (got %lld)", (long long)D);
     return FFEMB_EINVAL;
   }
-  if (n >= (1ll << 31) || B > (1ll << BAG_BITS)) {
-    set_error("sorted backward: too many lookups for one call (%lld)", (long long)n);
+  for (int t = 0; t < tb_all.num_tables; t++) {
+    if (((uintptr_t)tb_all.t[t].table | (uintptr_t)tb_all.t[t].out) % 16 != 0) {
+      set_error("sorted backward needs 16-byte aligned table and output-grad pointers (table %d)", t);
+      return FFEMB_EINVAL;
+    }
+  }
+  if (n_all >= (1ll << 31) || B > (1ll << BAG_BITS)) {
+    set_error("sorted backward: too many lookups for one call (%lld)", (long long)n_all);
     return FFEMB_EINVAL;
   }
-  const size_t need = backward_workspace_bytes(n, rows, D);
+  const size_t need = backward_workspace_bytes(n_all, (int64_t)tb_all.row_base[tb_all.num_tables], D);
   if (!ws || ((uintptr_t)ws & 255) || ws_bytes < need) {
     set_error("workspace: need %zu bytes, 256-byte aligned (got %zu at %p)", need, ws_bytes, ws);
     return FFEMB_EWORKSPACE;
   }
-  const Carve c = carve((char *)ws, n, rows, D);
+  // Split: tables whose whole gradient fits on chip go bag-major (no sort), the rest are sorted.
+  TableBatch tb, ts;
+  memset(&tb, 0, sizeof(tb));
+  memset(&ts, 0, sizeof(ts));
+  int n_tiny = 0;
+  for (int pass = 1; pass <= 2; pass++) {  // tiny tables first, then small ones
+    for (int t = 0; t < tb_all.num_tables; t++) {
+      if (tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) == pass) {
+        ts.t[ts.num_tables++] = tb_all.t[t];
+        n_tiny += pass == 1;
+      }
+    }
+  }
+  uint64_t rows_l = 0, n = 0;
+  for (int t = 0; t < tb_all.num_tables; t++) {
+    if (tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) != 0) continue;
+    TableDesc &d = tb.t[tb.num_tables];
+    d = tb_all.t[t];
+    d.lookup_base = (uint32_t)n;
+    tb.row_base[tb.num_tables++] = rows_l;
+    rows_l += (uint64_t)d.R;
+    n += (uint64_t)B * d.L;
+  }
+  tb.row_base[tb.num_tables] = rows_l;
+  const int64_t rows = (int64_t)rows_l;
+  const Carve c = carve((char *)ws, (int64_t)n, rows > 0 ? rows : 1, D);
+  if (ts.num_tables) {
+    const int rc = launch_backward_small(ts, n_tiny, D, B, aggr, lr, mode, (float *)((char *)ws + c.total), s);
+    if (rc) return rc;
+  }
+  if (n == 0) return FFEMB_OK;
   if (wide_keys(rows)) {
     return mode == APPLY_SGD
                ? dispatch_g<uint64_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s)

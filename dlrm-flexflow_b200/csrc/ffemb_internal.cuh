@@ -64,6 +64,11 @@ enum ApplyMode { APPLY_SGD = 0, APPLY_GRAD = 1 };
 int launch_backward_sorted(const TableBatch &tb, int64_t D, int64_t B, int aggr, float lr,
                            ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s);
 size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t D);
+// tables whose whole gradient fits on chip (ffemb_backward_small.cu)
+int backward_path(int64_t R, int64_t L, int64_t D, int64_t B);  // 0 sorted, 1 tiny, 2 small
+size_t small_partials_bound(int64_t D);
+int launch_backward_small(TableBatch &tb, int n_tiny, int64_t D, int64_t B, int aggr, float lr,
+                          ApplyMode mode, float *partials, cudaStream_t s);
 
 // ---- device helpers --------------------------------------------------------------------
 // 16-byte read-only load of a table row fragment.  Rows are touched once per lookup, so keep
@@ -159,10 +164,24 @@ __device__ __forceinline__ void st_row_hint_if(float *p, float4 v, uint64_t pol,
       "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol), "r"((int)on)
       : "memory");
 }
+// one-instruction L2 prefetch of a whole row (TMA bulk prefetch: no registers, no smem);
+// p 16-byte aligned, bytes a multiple of 16
+__device__ __forceinline__ void prefetch_l2_bulk(const void *p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ int64_t ldg_idx_stream(const int64_t *p, uint64_t pol) {
   int64_t v;
   asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.b64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
   return v;
+}
+// a / d, correctly rounded, without the division subroutine: r = RN(1/d), q = RN(a*r), then two
+// exact-residual corrections (Markstein).  Valid while no intermediate under/overflows, i.e. for
+// every gradient that is not denormal-small; d is a bag width (1 .. 2^31).
+__device__ __forceinline__ float div_rn(float a, float d, float r) {
+  float q = a * r;
+  q = fmaf(fmaf(-d, q, a), r, q);
+  q = fmaf(fmaf(-d, q, a), r, q);
+  return q;
 }
 __device__ __forceinline__ int64_t shfl_i64(int64_t v, int src) {
   int lo = __shfl_sync(0xffffffffu, (int)(v & 0xffffffffll), src);

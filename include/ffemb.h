@@ -121,6 +121,11 @@ FFEMB_API int ffemb_backward_dense_batched(const ffemb_table_t *tables, int num_
  * tables holding `total_rows` = sum_t R_t rows of D floats.  0 on invalid arguments.         */
 FFEMB_API size_t ffemb_backward_workspace(int64_t num_lookups, int64_t total_rows, int64_t D);
 
+/* Which backward algorithm a table of R rows, bag width L takes at batch B (informational; the
+ * accounting in bench.py uses it): 0 = radix sort + segmented sum, 1 = "tiny" (R <= 16, register
+ * accumulators), 2 = "small" (whole [R][D] gradient in shared memory).  All are deterministic.  */
+FFEMB_API int ffemb_backward_path(int64_t R, int64_t L, int64_t D, int64_t B);
+
 /* ---- debug aid (not on the timed path) -----------------------------------------------------
  * Writes the number of indices outside [0, R) to *bad_count (device int64).                   */
 FFEMB_API int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int64_t *bad_count,
@@ -139,7 +144,8 @@ FFEMB_API int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int6
 #define FFEMB_PHASE_REDUCE1 3   /* level-1 segmented sum + row update */
 #define FFEMB_PHASE_REDUCE_UP 4 /* upper levels */
 #define FFEMB_PHASE_ATOMIC 5    /* atomic comparison backward */
-#define FFEMB_NUM_PHASES 6
+#define FFEMB_PHASE_SMALL 6     /* bag-major backward of tables whose gradient fits on chip */
+#define FFEMB_NUM_PHASES 7
 FFEMB_API int ffemb_profile_enable(int on);
 FFEMB_API int ffemb_profile_collect(float *ms_per_phase, int64_t *launches_per_phase);
 FFEMB_API int64_t ffemb_launch_count(void);

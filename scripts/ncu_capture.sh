@@ -1,12 +1,13 @@
 # ncu evidence for one round (run under gpurun, one GPU).  $1 = tag (e.g. r1b).
-# 1) plain run must exit 0;  2) launch list (gpu__time_duration) of the same command;
-# 3) one --set full capture of the hot kernels.  Rows are capped at 4M for the replays (ncu
-# saves/restores written memory per pass; the 96 GB working set would take minutes per kernel).
+# 1) plain run must exit 0;  2) launch list (gpu__time_duration) of the same command, timed region
+# only (bench.py brackets it with cudaProfilerStart/Stop);  3) one --set full capture of our kernels.
+# Rows are capped at 4M for the replays (ncu saves/restores written memory per pass; the 96 GB
+# working set would take minutes per kernel).
 TAG=${1:-r1}
 mkdir -p gpurun_out
 CMD="python bench.py --rows-cap 4000000 --steps 2 --warmup 1 --no-e2e --no-cpu"
 $CMD > gpurun_out/${TAG}_plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain.log; exit 1; }
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"fwd_kernel|reduce1_kernel|keygen_kernel|reduce_level_kernel|reduce_tail_kernel" --launch-skip 12 -c 6 -o gpurun_out/${TAG}_full $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
+ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
+ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:"fwd_kernel|reduce1_kernel|keygen_kernel|reduce_level_kernel|reduce_tail_kernel|bwd_small" -c 8 -o gpurun_out/${TAG}_full $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
 ncu -i gpurun_out/${TAG}_full.ncu-rep --page raw --csv > gpurun_out/${TAG}_full_raw.csv 2>/dev/null
-tail -2 gpurun_out/${TAG}_plain.log | cut -c1-600; tail -3 gpurun_out/${TAG}_ncu2.log; wc -l gpurun_out/${TAG}_launches.csv
+tail -1 gpurun_out/${TAG}_plain.log | cut -c1-300; tail -3 gpurun_out/${TAG}_ncu2.log; wc -l gpurun_out/${TAG}_launches.csv

@@ -148,6 +148,11 @@ BWD_SHAPES = [  # R, D, L, B   (D % 4 == 0 for the sorted path)
     (1000, 16, 7, 1000), (1000, 64, 20, 257), (1000, 128, 20, 300), (2000, 128, 64, 130),
     (4, 16, 1, 20000), (3, 128, 20, 700), (1, 64, 1, 5000), (11, 8, 3, 9999), (50, 4, 1, 100),
     (100, 48, 5, 99), (100, 20, 3, 77), (64, 256, 9, 70), (64, 512, 3, 40), (7, 16, 64, 3000),
+    # tables whose whole gradient fits on chip (ffemb_backward_small.cu): tiny = register
+    # accumulators (R <= 16), small = shared-memory accumulator; ragged tails, bag > lanes per slot
+    (3, 128, 19, 3001), (4, 128, 16, 2049), (10, 64, 16, 4099), (14, 32, 20, 1777), (16, 128, 1, 20011),
+    (1, 128, 3, 6000), (2, 96, 64, 515), (36, 128, 18, 2000), (63, 128, 3, 7001), (155, 128, 7, 4099),
+    (108, 64, 18, 1500), (17, 32, 40, 999), (160, 128, 5, 5000), (300, 48, 2, 20000),
 ]
 
 
@@ -190,22 +195,36 @@ def test_backward_dense_variants(ffemb, oracle, torch_cuda, R, D, L, B, aggr):
         assert np.array_equal(got[cnt == 0], pre[cnt == 0])
 
 
-def test_backward_is_deterministic_and_atomic_is_the_comparison(ffemb, torch_cuda):
-    """Two runs of the sorted backward are bit-identical (the reference's atomics are not
-    required to be)."""
+@pytest.mark.parametrize("R,D,L,B", [(37, 64, 8, 20000), (5, 128, 9, 9000), (5000, 64, 8, 20000)])
+def test_backward_is_deterministic_and_atomic_is_the_comparison(ffemb, torch_cuda, R, D, L, B):
+    """Runs of the deterministic backward are bit-identical on every path (small: shared-memory
+    accumulator, tiny: register accumulators, sorted) — the reference's atomics are not."""
     torch = torch_cuda
-    W, idx, g = make_inputs(37, 64, 8, 20000, seed=5)  # every row ~4300 duplicates
+    W, idx, g = make_inputs(R, D, L, B, seed=5)  # heavy duplication
     outs = []
     for _ in range(3):
         dW = dev(torch, W)
-        ffemb.Embedding(37, 64, 21).backward_sgd(dev(torch, idx), dev(torch, g), dW, 0.01)
+        ffemb.Embedding(R, D, 21).backward_sgd(dev(torch, idx), dev(torch, g), dW, 0.01)
         outs.append(dW.cpu().numpy())
     assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
 
 
-def test_backward_batched_ragged_tables(ffemb, oracle, torch_cuda):
+def test_backward_path_selection(ffemb):
+    """Which tables leave the sorted path (informational query of the C ABI)."""
+    path = ffemb.lib().ffemb_backward_path
+    assert path(3, 19, 128, 65536) == 1 and path(16, 1, 128, 65536) == 1
+    assert path(36, 18, 128, 65536) == 2 and path(108, 18, 128, 65536) == 2
+    assert path(155, 7, 128, 65536) == 0 and path(63, 3, 128, 65536) == 0   # short bags: little re-reading to save
+    assert path(976, 20, 128, 65536) == 0 and path(40000000, 20, 128, 65536) == 0
+    assert path(3, 19, 16, 65536) == 0 and path(3, 19, 256, 65536) == 0   # D outside [32, 128]
+    assert path(3, 1, 128, 100) == 0                                       # too little work
+
+
+@pytest.mark.parametrize("D,B", [(16, 2500), (64, 9000), (128, 17000)])
+def test_backward_batched_ragged_tables(ffemb, oracle, torch_cuda, D, B):
+    """One batched call mixing tiny, small and sorted tables (for D >= 32 and enough lookups)."""
     torch = torch_cuda
-    rows, bags, D, B = [5, 100000, 33, 20000, 4, 1], [1, 3, 20, 2, 7, 1], 16, 2500
+    rows, bags = [5, 100000, 33, 20000, 4, 1], [1, 3, 20, 2, 7, 1]
     Ws, idxs, gs = [], [], []
     for t, (R, L) in enumerate(zip(rows, bags)):
         W, idx, g = make_inputs(R, D, L, B, seed=200 + t)
