@@ -46,7 +46,7 @@ def test_workspace_query(ffemb):
     # keys widen to 64 bits once the global row id no longer fits 32
     assert L.ffemb_backward_workspace(100000, 1 << 33, 16) > big
     # missing workspace is reported, not dereferenced
-    rc = L.ffemb_backward_sgd(8, 8, 8, 1, 16, 4, 100, ffemb.AGGR_MODE_SUM, 0.01, None, 0, None)
+    rc = L.ffemb_backward_sgd(16, 16, 16, 1, 16, 4, 100, ffemb.AGGR_MODE_SUM, 0.01, None, 0, None)
     assert rc == 3 and b"workspace" in L.ffemb_last_error()
 
 
