@@ -50,7 +50,11 @@ def parse():
     ap.add_argument("--pool", type=int, default=4, help="distinct index batches cycled")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--placement", default="modulo", choices=["modulo", "balanced"])
+    ap.add_argument("--placement", default="balanced", choices=["modulo", "balanced"],
+                    help="N>1: modulo = the reference's t %% G; balanced = greedy by measured per-lookup cost")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="N>1: fused = pooled rows stored straight into the peer's Concat input by the "
+                         "gather-pool kernel (NVLink peer memory); nccl = all_to_all_single + pack/unpack copies")
     ap.add_argument("--backward", default="sorted", choices=["sorted", "atomic"],
                     help="atomic = dense-grad atomicAdd comparison (not the product path)")
     ap.add_argument("--rows-cap", type=int, default=0, help="cap rows per table (profiling under ncu only)")
@@ -131,11 +135,18 @@ def placement(wl, world, kind):
     T = wl.num_tables
     if kind == "modulo" or world == 1:
         return [t % world for t in range(T)]
+    # per-lookup cost classes measured on one B200 (profiles/r1_notes.md): rows from HBM and a row
+    # read-modify-write per lookup (big tables) > L2-resident tables through the sorted path > tables
+    # whose gradient fits on chip; + a per-bag term for the pooled-row write / output-grad read
+    def cost(t):
+        bytes_ = wl.rows[t] * wl.dim * 4
+        per = 1.0 if bytes_ > (64 << 20) else (0.25 if wl.rows[t] <= 16 or (bytes_ <= (80 << 10) and wl.bags[t] >= 8) else 0.55)
+        return wl.bags[t] * per + 0.6
     load, mem, own = [0.0] * world, [0.0] * world, [0] * T
-    for t in sorted(range(T), key=lambda t: -(wl.bags[t] + 1)):
+    for t in sorted(range(T), key=lambda t: -cost(t)):
         cands = sorted(range(world), key=lambda g: (load[g], mem[g]))
         g = next((g for g in cands if mem[g] + wl.rows[t] * wl.dim * 4 < 150e9), cands[0])
-        own[t], load[g], mem[g] = g, load[g] + wl.bags[t] + 1, mem[g] + wl.rows[t] * wl.dim * 4
+        own[t], load[g], mem[g] = g, load[g] + cost(t), mem[g] + wl.rows[t] * wl.dim * 4
     return own
 
 
@@ -229,7 +240,13 @@ def main():
     own = placement(wl, world, args.placement)
     owned = [t for t in range(wl.num_tables) if own[t] == rank]
     dw = DeviceWorkload(torch, pkg, wl, owned, dev, args.pool, seed=1234)
-    ex = pkg.exchange.TableWiseExchange(wl.num_tables, own, wl.batch, wl.dim, rank, world, dev) if world > 1 else None
+    ex = fx = None
+    if world > 1 and args.exchange == "nccl":
+        ex = pkg.exchange.TableWiseExchange(wl.num_tables, own, wl.batch, wl.dim, rank, world, dev)
+    elif world > 1:
+        fx = pkg.exchange.FusedTableWiseExchange(wl.num_tables, own, wl.batch, wl.dim, rank, world, dev)
+        fx.dx.uniform_(-1, 1)
+        dw.outgrad = fx.outgrads  # the owners' output-grad buffers are the peers' push targets
     stream = torch.cuda.current_stream()
 
     wgrads = None
@@ -239,6 +256,12 @@ def main():
     def step(k):
         p = k % dw.pool
         idx = [b[p] for b in dw.idx]
+        if fx is not None:
+            fx.forward(dw.coll, idx)      # gather-pool + exchange in one kernel, then a barrier
+            fx.backward()                 # dx column blocks pushed to the table owners, barrier
+            if dw.coll is not None:
+                dw.coll.backward_sgd(idx, dw.outgrad, wl.lr)
+            return
         if dw.coll is not None:
             dw.coll.forward(idx, dw.out)
         if ex is not None:
@@ -293,7 +316,7 @@ def main():
     # ---- e2e: host buffers, copies inside the timed region ----------------------------------
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(torch, pkg, args, wl, dw, ex, dist, dev, barrier, total_lookups)
+        e2e = run_e2e(torch, pkg, args, wl, dw, ex, fx, dist, dev, barrier, total_lookups)
 
     # ---- roofline of the dominant kernel phase ----------------------------------------------
     peak, peak_src = peaks()
@@ -308,6 +331,7 @@ def main():
     U_s = sum(sum(dw.uniq[i]) / len(dw.uniq[i]) for i in small)
     alg = {"forward": fwd_b, "atomic": bwd_b, "sort": 0, "reduce_up": 0,
            "reduce1": 4 * D * (T_own - len(small)) * B + 8 * D * (U - U_s) + 8 * (n_own - n_s),
+           "exchange": (8 * D * wl.num_tables * fx.local_batch) if fx is not None else 0,
            "keygen": 8 * (n_own - n_s), "small": 8 * n_s + 4 * D * len(small) * B + 8 * D * U_s}
     dom = max(kernel_phases, key=kernel_phases.get) if kernel_phases else "forward"
     dom_ms = kernel_phases.get(dom, ms_step)
@@ -334,7 +358,9 @@ def main():
         "config": {"workload": wl.name, "tables": wl.num_tables, "dim": wl.dim, "batch": wl.batch,
                    "bags": wl.bags, "rows_total": int(sum(wl.rows)), "lookups_per_step": total_lookups,
                    "aggr": wl.aggr, "index_dist": wl.dist, "lr": wl.lr,
-                   "parallelism": ("single" if world == 1 else f"table-wise x{world} ({args.placement}) + all-to-all"),
+                   "parallelism": ("single" if world == 1 else
+                                   f"table-wise x{world} ({args.placement} placement), exchange={args.exchange}"),
+                   "table_owner": own if world > 1 else None,
                    "backward": args.backward,
                    "cache": f"inputs larger than L2: {args.pool} index batches cycled, "
                             f"{sum(wl.rows) * wl.dim * 4 / 1e9:.1f} GB of tables, random rows",
@@ -362,9 +388,11 @@ def load_traffic(phase):
         return None
 
 
-def run_e2e(torch, pkg, args, wl, dw, ex, dist, dev, barrier, total_lookups):
+def run_e2e(torch, pkg, args, wl, dw, ex, fx, dist, dev, barrier, total_lookups):
     """Same step, HOST buffers: per step H2D of that step's indices and output-grads from
     pinned memory, D2H of the pooled outputs; the step ends when the D2H has landed."""
+    if fx is not None:
+        return run_e2e_fused(torch, pkg, args, wl, dw, fx, dist, dev, barrier, total_lookups)
     if dw.coll is None:
         h_idx = h_g = h_out = []
     else:
@@ -408,6 +436,46 @@ def run_e2e(torch, pkg, args, wl, dw, ex, dist, dev, barrier, total_lookups):
         dist.all_reduce(t[:1], op=dist.ReduceOp.MAX)
         dist.all_reduce(t[1:], op=dist.ReduceOp.SUM)
         ms, h2d, d2h = t[0].item(), t[1].item(), t[2].item()
+    return {"value": total_lookups / (ms / steps * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
+            "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
+
+
+def run_e2e_fused(torch, pkg, args, wl, dw, fx, dist, dev, barrier, total_lookups):
+    """N>1, fused exchange: per step H2D of the owned tables' indices (whole batch) and of this
+    rank's dx (its samples' output-grads), D2H of this rank's interaction input x."""
+    h_idx = [[b.cpu().pin_memory() for b in bs[:2]] for bs in dw.idx]
+    d_idx = [bs[0].clone() for bs in dw.idx]
+    h_dx = fx.dx.cpu().pin_memory()
+    h_x = torch.empty(fx.x.shape, dtype=fx.x.dtype).pin_memory()
+    h2d = sum(x[0].numel() * 8 for x in h_idx) + h_dx.numel() * 4
+    d2h = h_x.numel() * 4
+    stream = torch.cuda.current_stream()
+
+    def step(k):
+        for t in range(len(d_idx)):
+            d_idx[t].copy_(h_idx[t][k % 2], non_blocking=True)
+        fx.dx.copy_(h_dx, non_blocking=True)
+        fx.forward(dw.coll, d_idx)
+        h_x.copy_(fx.x, non_blocking=True)
+        fx.backward()
+        if dw.coll is not None:
+            dw.coll.backward_sgd(d_idx, dw.outgrad, wl.lr)
+        torch.cuda.current_stream().synchronize()
+
+    steps = max(3, min(args.steps, 10))
+    for k in range(2):
+        step(k)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for k in range(steps):
+        step(k)
+    e1.record(stream)
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1), h2d, d2h], dtype=torch.float64, device=dev)
+    dist.all_reduce(t[:1], op=dist.ReduceOp.MAX)
+    dist.all_reduce(t[1:], op=dist.ReduceOp.SUM)
+    ms, h2d, d2h = t[0].item(), t[1].item(), t[2].item()
     return {"value": total_lookups / (ms / steps * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
             "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
 

@@ -14,6 +14,7 @@ AGGR_MODE_MEAN = 122  # opt-in true mean (not a reference enum value)
 
 FFEMB_OK, FFEMB_EINVAL, FFEMB_ECUDA, FFEMB_EWORKSPACE, FFEMB_ERANGE = 0, 1, 2, 3, 4
 FFEMB_MAX_TABLES = 64
+FFEMB_MAX_PEERS = 8
 
 
 class FFEmbError(RuntimeError):
@@ -25,6 +26,11 @@ class FFEmbError(RuntimeError):
 class ffemb_table_t(C.Structure):
     _fields_ = [("idx", C.c_void_p), ("out", C.c_void_p), ("table", C.c_void_p),
                 ("R", C.c_int64), ("L", C.c_int32), ("reserved", C.c_int32)]
+
+
+class ffemb_exchange_t(C.Structure):
+    _fields_ = [("peer_x", C.c_void_p * FFEMB_MAX_PEERS), ("num_peers", C.c_int32),
+                ("reserved", C.c_int32), ("batch_per_peer", C.c_int64), ("row_stride", C.c_int64)]
 
 
 def library_path():
@@ -74,6 +80,8 @@ def lib():
     L.ffemb_version.restype = i32
     L.ffemb_forward.argtypes = [vp, vp, vp, i64, i64, i64, i32, vp]
     L.ffemb_forward_batched.argtypes = [tp, i32, i64, i64, i32, vp]
+    L.ffemb_forward_exchange.argtypes = [tp, i32, i64, i64, i32, C.POINTER(ffemb_exchange_t), vp]
+    L.ffemb_exchange_backward.argtypes = [tp, i32, i64, vp, i64, i64, i64, vp]
     L.ffemb_backward_dense_atomic.argtypes = [vp, vp, vp, i64, i64, i64, i32, vp]
     L.ffemb_backward_dense.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_sgd.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, f32, vp, sz, vp]
@@ -93,7 +101,7 @@ def lib():
     return L
 
 
-PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small"]
+PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small", "exchange"]
 
 
 def profile_enable(on=True):

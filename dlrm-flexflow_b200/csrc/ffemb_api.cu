@@ -64,7 +64,7 @@ void prof_end(int phase, int launches, cudaStream_t s) {
 // (src/ops/embedding.cu:251-258: input/output batch agree, weight/output width agree) as far
 // as raw pointers allow, plus what the reference leaves to UB.
 static int pack(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B, int aggr,
-                TableBatch &tb) {
+                TableBatch &tb, bool need_out = true, bool need_table = true) {
   if (!aggr_valid(aggr)) {
     // AGGR_MODE_NONE reaches assert(aggr == AGGR_MODE_AVG) in the reference kernels
     // (src/ops/embedding.cu:185,209)
@@ -82,7 +82,8 @@ static int pack(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t 
   uint64_t rows = 0, lookups = 0;
   for (int t = 0; t < num_tables; t++) {
     const ffemb_table_t &x = tables[t];
-    if (x.L < 0 || x.R < 0 || (B > 0 && (!x.out || !x.table || (x.L > 0 && !x.idx)))) {
+    if (x.L < 0 || x.R < 0 ||
+        (B > 0 && ((need_out && !x.out) || (need_table && (!x.table || (x.L > 0 && !x.idx)))))) {
       set_error("table %d: invalid descriptor (idx=%p out=%p table=%p R=%lld L=%d)", t,
                 (const void *)x.idx, (void *)x.out, (void *)x.table, (long long)x.R, x.L);
       return FFEMB_EINVAL;
@@ -143,7 +144,9 @@ int ffemb_forward(const int64_t *idx, float *out, const float *table, int64_t L,
   TableBatch tb;
   int rc = pack1(idx, out, table, L, D, B, 0, aggr, tb);
   if (rc) return rc;
-  return launch_forward(tb, D, B, aggr, (cudaStream_t)stream);
+  OutMap om;
+  memset(&om, 0, sizeof(om));
+  return launch_forward(tb, D, B, aggr, om, (cudaStream_t)stream);
 }
 
 int ffemb_forward_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
@@ -151,7 +154,64 @@ int ffemb_forward_batched(const ffemb_table_t *tables, int num_tables, int64_t D
   TableBatch tb;
   int rc = pack(tables, num_tables, D, B, aggr, tb);
   if (rc) return rc;
-  return launch_forward(tb, D, B, aggr, (cudaStream_t)stream);
+  OutMap om;
+  memset(&om, 0, sizeof(om));
+  return launch_forward(tb, D, B, aggr, om, (cudaStream_t)stream);
+}
+
+int ffemb_forward_exchange(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                           int aggr, const ffemb_exchange_t *ex, ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack(tables, num_tables, D, B, aggr, tb, /*need_out=*/false);
+  if (rc) return rc;
+  if (!ex || ex->num_peers < 1 || ex->num_peers > FFEMB_MAX_PEERS || ex->batch_per_peer < 1 ||
+      ex->row_stride < D || ex->batch_per_peer * ex->num_peers < B) {
+    set_error("forward_exchange: invalid exchange descriptor");
+    return FFEMB_EINVAL;
+  }
+  OutMap om;
+  memset(&om, 0, sizeof(om));
+  for (int h = 0; h < ex->num_peers; h++) {
+    if (!ex->peer_x[h] && B > (int64_t)h * ex->batch_per_peer) {
+      set_error("forward_exchange: peer_x[%d] is NULL", h);
+      return FFEMB_EINVAL;
+    }
+    om.peer[h] = ex->peer_x[h];
+  }
+  om.npeers = ex->num_peers;
+  om.ext = ex->batch_per_peer;
+  om.stride = ex->row_stride;
+  for (int t = 0; t < num_tables; t++) {
+    if (tables[t].reserved < 0 || (int64_t)tables[t].reserved + D > ex->row_stride) {
+      set_error("forward_exchange: table %d column offset %d outside a row of %lld floats", t,
+                tables[t].reserved, (long long)ex->row_stride);
+      return FFEMB_EINVAL;
+    }
+    tb.t[t].lookup_base = (uint32_t)tables[t].reserved;  // column offset of the table's block
+  }
+  return launch_forward(tb, D, B, aggr, om, (cudaStream_t)stream);
+}
+
+int ffemb_exchange_backward(const ffemb_table_t *tables, int num_tables, int64_t D, const float *dx,
+                            int64_t n_samples, int64_t first_sample, int64_t row_stride,
+                            ffemb_stream_t stream) {
+  if (!tables || num_tables < 0 || num_tables > FFEMB_MAX_TABLES || D <= 0 || n_samples < 0 ||
+      first_sample < 0 || row_stride < D || (n_samples > 0 && !dx)) {
+    set_error("exchange_backward: invalid arguments");
+    return FFEMB_EINVAL;
+  }
+  TableBatch tb;
+  memset(&tb, 0, sizeof(tb));
+  tb.num_tables = num_tables;
+  for (int t = 0; t < num_tables; t++) {
+    if (!tables[t].out || tables[t].reserved < 0 || (int64_t)tables[t].reserved + D > row_stride) {
+      set_error("exchange_backward: table %d: invalid destination or column offset", t);
+      return FFEMB_EINVAL;
+    }
+    tb.t[t].out = tables[t].out;
+    tb.t[t].lookup_base = (uint32_t)tables[t].reserved;
+  }
+  return launch_exchange_backward(tb, D, dx, n_samples, first_sample, row_stride, (cudaStream_t)stream);
 }
 
 int ffemb_backward_dense_atomic(const int64_t *idx, const float *outgrad, float *wgrad, int64_t L,

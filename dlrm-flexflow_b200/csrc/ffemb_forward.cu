@@ -57,10 +57,19 @@ __host__ __device__ __forceinline__ int fwd_bags_per_slot(int L, int target) {
 // allocation (a handful of hot rows otherwise all queue on the same L2 slices: measured 1.1 ms
 // for a 3-row table against 0.06 ms for a 1000-row one at the same lookup count).
 // FULL: D4 == G*C, every lane of a slot owns a fragment (no per-lane width check).
-template <int G, int C, int AG, int UNR, bool FULL, bool TINY>
+// Output pointer of one bag (lane fragment excluded).  Plain: td.out + b*D.  Fused exchange: the
+// Concat input of the rank that owns sample b (include/ffemb.h, ffemb_forward_exchange).
+__device__ __forceinline__ float *out_row(const TableDesc &td, const OutMap &om, int64_t b, int D) {
+  if (om.npeers == 0) return td.out + b * (int64_t)D;
+  const int64_t h = b / om.ext;
+  return om.peer[h] + (b - h * om.ext) * om.stride + td.lookup_base;
+}
+
+template <int G, int C, int AG, int UNR, bool FULL, bool TINY, bool EXCH>
 __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const float *__restrict__ W,
                                          float *op, int L, int D, int nl, int nl_max, int sl,
-                                         uint64_t pol_rows, uint64_t pol_stream) {
+                                         uint64_t pol_rows, uint64_t pol_stream, const OutMap &om,
+                                         int64_t bag0, uint32_t col) {
   constexpr int K = FwdCfg<G>::K, CH = G * K, NG = CH / UNR;
   static_assert(CH % UNR == 0 && NG % 2 == 0, "group pipeline needs an even number of groups");
   const int D4 = D >> 2;
@@ -90,6 +99,13 @@ __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const f
 #pragma unroll
       for (int c = 0; c < C; c++) v[i][u][c] = make_float4(0.f, 0.f, 0.f, 0.f);
   int rem = L;
+  // fused exchange: (rank, local sample) of the bag being pooled; op walks that rank's buffer
+  int xh = 0;
+  int64_t xb = 0;
+  if (EXCH) {
+    xh = (int)(bag0 / om.ext);
+    xb = bag0 - xh * om.ext;
+  }
 
   // branch-free: UNR predicated LDG.128 in a row
   auto issue = [&](int bf, const uint32_t (&r)[K], int grp, int base) {
@@ -122,7 +138,17 @@ __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const f
             if (own[c]) st_row_hint(op + 4 * c * G, acc[c], pol_stream);
             acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
           }
-          op += D;
+          if (EXCH) {
+            if (++xb == om.ext) {  // next sample belongs to the next rank
+              xb = 0;
+              ++xh;
+              op = om.peer[xh < om.npeers ? xh : om.npeers - 1] + col + 4 * sl;
+            } else {
+              op += om.stride;
+            }
+          } else {
+            op += D;
+          }
           rem = L;
         }
       }
@@ -146,9 +172,10 @@ __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const f
   }
 }
 
-template <int G, int C, int AG, int UNR, bool FULL>
+template <int G, int C, int AG, int UNR, bool FULL, bool EXCH>
 __global__ void __launch_bounds__(kThreads, C >= 2 ? 2 : 4)
-fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, int64_t stream_bytes) {
+fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, int64_t stream_bytes,
+           const __grid_constant__ OutMap om) {
   static_assert(AG != AG_AVG, "the in-loop divide lives in fwd_avg_kernel");
   constexpr int SLOTS = 32 / G;
   // which table does this CTA work on?  cta_base is ascending, <= 65 entries
@@ -169,13 +196,15 @@ fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, 
   const int64_t slot = ((int64_t)(blockIdx.x - tb.cta_base[t]) * (kThreads / 32) + warp) * SLOTS + sub;
   const int64_t bag0 = slot * bps;
   const int nb = bag0 < B ? (int)min((int64_t)bps, B - bag0) : 0;
-  float *op = td.out + bag0 * (int64_t)D + 4 * sl;
+  float *op = (nb > 0 ? out_row(td, om, bag0, D) : td.out) + 4 * sl;
   const uint64_t pol_stream = policy_evict_first();
   if (L == 0) {  // empty bags pool to 0 (out = 0, no lookups)
-    for (int i = 0; i < nb; i++, op += D)
+    for (int i = 0; i < nb; i++) {
+      float *zp = out_row(td, om, bag0 + i, D) + 4 * sl;
 #pragma unroll
       for (int c = 0; c < C; c++)
-        if (sl + c * G < (D >> 2)) st_row_hint(op + 4 * c * G, make_float4(0.f, 0.f, 0.f, 0.f), pol_stream);
+        if (sl + c * G < (D >> 2)) st_row_hint(zp + 4 * c * G, make_float4(0.f, 0.f, 0.f, 0.f), pol_stream);
+    }
     return;
   }
   const int nl = nb * L;        // valid lookups of this slot
@@ -185,9 +214,9 @@ fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, 
   const int64_t bytes = td.R * (int64_t)D * 4;
   const uint64_t pol_rows = bytes > stream_bytes ? pol_stream : policy_evict_normal();
   if (td.R > 0 && bytes <= kL1Bytes)
-    fwd_slot<G, C, AG, UNR, FULL, true>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream);
+    fwd_slot<G, C, AG, UNR, FULL, true, EXCH>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream, om, bag0, td.lookup_base);
   else
-    fwd_slot<G, C, AG, UNR, FULL, false>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream);
+    fwd_slot<G, C, AG, UNR, FULL, false, EXCH>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream, om, bag0, td.lookup_base);
 }
 
 // ---- AGGR_MODE_AVG as the reference computes it (divide inside the bag loop) ----------------
@@ -195,7 +224,7 @@ fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, 
 // division is a subroutine call on this target, which does not mix with the branch-free body.
 template <int G, int C, int AG>
 __global__ void __launch_bounds__(kThreads)
-fwd_avg_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B) {
+fwd_avg_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, const __grid_constant__ OutMap om) {
   constexpr int SLOTS = 32 / G;
   constexpr int UNR = (C == 1) ? 8 : (C == 2 ? 4 : 2);
   const TableDesc &td = tb.t[blockIdx.y];
@@ -249,7 +278,7 @@ fwd_avg_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B) {
     for (int c = 0; c < C; c++) f4_mul(acc[c], inv);
   }
   if (valid) {
-    float *op = td.out + b * (int64_t)D;
+    float *op = out_row(td, om, b, D);
 #pragma unroll
     for (int c = 0; c < C; c++)
       if (sl + c * G < D4) st_stream(op + 4 * (sl + c * G), acc[c]);
@@ -258,7 +287,7 @@ fwd_avg_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B) {
 
 // ---- any D / any alignment: one warp per bag, lane per float --------------------------------
 __global__ void __launch_bounds__(kThreads)
-fwd_generic_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int ag) {
+fwd_generic_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int ag, const __grid_constant__ OutMap om) {
   const TableDesc &td = tb.t[blockIdx.y];
   const int L = td.L;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -273,29 +302,32 @@ fwd_generic_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int 
       if (ag == AG_AVG) acc = acc / Lf;
     }
     if (ag == AG_MEAN && L > 0) acc *= (1.0f / Lf);
-    td.out[bag * (int64_t)D + d] = acc;
+    out_row(td, om, bag, D)[d] = acc;
   }
 }
 
 template <int G, int C, bool FULL>
 static void launch_vec2(const TableBatch &tb, int D, int64_t B, int ag, int target, unsigned ctas,
-                        cudaStream_t s) {
+                        const OutMap &om, cudaStream_t s) {
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
   int64_t stream_bytes = kStreamBytes;
   if (const char *e = getenv("FFEMB_STREAM_MB")) stream_bytes = atoll(e) << 20;  // tuning aid
-  switch (ag) {
-    case AG_SUM: fwd_kernel<G, C, AG_SUM, UNR, FULL><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes); break;
-    default: fwd_kernel<G, C, AG_MEAN, UNR, FULL><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes); break;
+  if (om.npeers == 0) {
+    if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om);
+    else fwd_kernel<G, C, AG_MEAN, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om);
+  } else {
+    if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om);
+    else fwd_kernel<G, C, AG_MEAN, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om);
   }
 }
 
 template <int G, int C>
-static void launch_vec(const TableBatch &tb_in, int D, int64_t B, int ag, cudaStream_t s) {
+static void launch_vec(const TableBatch &tb_in, int D, int64_t B, int ag, const OutMap &om, cudaStream_t s) {
   constexpr int SLOTS = 32 / G;
   if (ag == AG_AVG) {
     const int64_t per_cta = (int64_t)(kThreads / 32) * SLOTS;
     dim3 grid((unsigned)((B + per_cta - 1) / per_cta), tb_in.num_tables);
-    fwd_avg_kernel<G, C, AG_AVG><<<grid, kThreads, 0, s>>>(tb_in, D, B);
+    fwd_avg_kernel<G, C, AG_AVG><<<grid, kThreads, 0, s>>>(tb_in, D, B, om);
     return;
   }
   TableBatch tb = tb_in;
@@ -312,34 +344,109 @@ static void launch_vec(const TableBatch &tb_in, int D, int64_t B, int ag, cudaSt
     ctas += (uint32_t)((B + per_cta - 1) / per_cta);
   }
   tb.cta_base[tb.num_tables] = ctas;
-  if (D / 4 == G * C) launch_vec2<G, C, true>(tb, D, B, ag, target, ctas, s);
-  else launch_vec2<G, C, false>(tb, D, B, ag, target, ctas, s);
+  if (D / 4 == G * C) launch_vec2<G, C, true>(tb, D, B, ag, target, ctas, om, s);
+  else launch_vec2<G, C, false>(tb, D, B, ag, target, ctas, om, s);
 }
 
-int launch_forward(const TableBatch &tb, int64_t D64, int64_t B, int aggr, cudaStream_t s) {
+int launch_forward(const TableBatch &tb, int64_t D64, int64_t B, int aggr, const OutMap &om, cudaStream_t s) {
   const int D = (int)D64;
   const int ag = aggr == FFEMB_AGGR_SUM ? AG_SUM : (aggr == FFEMB_AGGR_AVG ? AG_AVG : AG_MEAN);
   if (B == 0 || tb.num_tables == 0) return FFEMB_OK;
   ProfScope prof(FFEMB_PHASE_FORWARD, 1, s);
   bool vec = (D % 4 == 0) && D <= 512;
   for (int t = 0; t < tb.num_tables; t++)
-    vec = vec && (((uintptr_t)tb.t[t].table | (uintptr_t)tb.t[t].out) % 16 == 0) &&
+    vec = vec && (((uintptr_t)tb.t[t].table | (uintptr_t)(om.npeers ? nullptr : tb.t[t].out)) % 16 == 0) &&
           tb.t[t].R <= (1ll << 32);  // row numbers travel as 32 bits inside the kernel
+  if (om.npeers) {  // every destination of the fused exchange must keep 16-byte fragments aligned
+    vec = vec && om.stride % 4 == 0;
+    for (int h = 0; h < om.npeers; h++) vec = vec && (uintptr_t)om.peer[h] % 16 == 0;
+    for (int t = 0; t < tb.num_tables; t++) vec = vec && tb.t[t].lookup_base % 4 == 0;
+  }
   if (!vec) {
     dim3 grid((unsigned)((B + kThreads / 32 - 1) / (kThreads / 32)), tb.num_tables);
-    fwd_generic_kernel<<<grid, kThreads, 0, s>>>(tb, D, B, ag);
+    fwd_generic_kernel<<<grid, kThreads, 0, s>>>(tb, D, B, ag, om);
   } else {
     const int D4 = D / 4;
-    if (D4 <= 1) launch_vec<1, 1>(tb, D, B, ag, s);
-    else if (D4 <= 2) launch_vec<2, 1>(tb, D, B, ag, s);
-    else if (D4 <= 4) launch_vec<4, 1>(tb, D, B, ag, s);
-    else if (D4 <= 8) launch_vec<8, 1>(tb, D, B, ag, s);
-    else if (D4 <= 16) launch_vec<16, 1>(tb, D, B, ag, s);
-    else if (D4 <= 32) launch_vec<32, 1>(tb, D, B, ag, s);
-    else if (D4 <= 64) launch_vec<32, 2>(tb, D, B, ag, s);
-    else launch_vec<32, 4>(tb, D, B, ag, s);
+    if (D4 <= 1) launch_vec<1, 1>(tb, D, B, ag, om, s);
+    else if (D4 <= 2) launch_vec<2, 1>(tb, D, B, ag, om, s);
+    else if (D4 <= 4) launch_vec<4, 1>(tb, D, B, ag, om, s);
+    else if (D4 <= 8) launch_vec<8, 1>(tb, D, B, ag, om, s);
+    else if (D4 <= 16) launch_vec<16, 1>(tb, D, B, ag, om, s);
+    else if (D4 <= 32) launch_vec<32, 1>(tb, D, B, ag, om, s);
+    else if (D4 <= 64) launch_vec<32, 2>(tb, D, B, ag, om, s);
+    else launch_vec<32, 4>(tb, D, B, ag, om, s);
   }
   return cuda_fail(cudaGetLastError(), "forward launch");
+}
+
+// ---- output-grad push (the transposed exchange) -----------------------------------------------
+// This rank's dx [n][stride] -> column block of table t of every sample goes to the owner's
+// output-grad rows [first, first + n): contiguous D-float pieces, read locally (coalesced), written
+// over NVLink peer memory with 16-byte stores.  One slot of G lanes per (sample, table).
+template <int G, int C>
+__global__ void __launch_bounds__(kThreads)
+exchange_bwd_kernel(const __grid_constant__ TableBatch tb, int D, const float *__restrict__ dx,
+                    int64_t n, int64_t first, int64_t stride) {
+  constexpr int SLOTS = 32 / G;
+  const TableDesc &td = tb.t[blockIdx.y];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane / G, sl = lane % G;
+  const int D4 = D >> 2;
+  const uint64_t pol = policy_evict_first();
+  for (int64_t sidx = ((int64_t)blockIdx.x * (kThreads / 32) + warp) * SLOTS + sub; sidx < n;
+       sidx += (int64_t)gridDim.x * (kThreads / 32) * SLOTS) {
+    const float *src = dx + sidx * stride + td.lookup_base;
+    float *dst = td.out + (first + sidx) * (int64_t)D;
+#pragma unroll
+    for (int c = 0; c < C; c++)
+      if (sl + c * G < D4) st_row_hint(dst + 4 * (sl + c * G), ldg_row_hint(src + 4 * (sl + c * G), pol), pol);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+exchange_bwd_generic_kernel(const __grid_constant__ TableBatch tb, int D, const float *__restrict__ dx,
+                            int64_t n, int64_t first, int64_t stride) {
+  const TableDesc &td = tb.t[blockIdx.y];
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n * D; i += (int64_t)gridDim.x * kThreads) {
+    const int64_t sidx = i / D, d = i - sidx * D;
+    td.out[(first + sidx) * D + d] = dx[sidx * stride + td.lookup_base + d];
+  }
+}
+
+template <int G, int C>
+static void launch_xbwd(const TableBatch &tb, int D, const float *dx, int64_t n, int64_t first, int64_t stride,
+                        cudaStream_t s) {
+  const int64_t per_cta = (int64_t)(kThreads / 32) * (32 / G);
+  int64_t bx = (n + per_cta - 1) / per_cta;
+  const int64_t cap = (148ll * 8 + tb.num_tables - 1) / tb.num_tables;  // ~8 CTAs per SM in total
+  if (bx > cap) bx = cap;
+  dim3 grid((unsigned)bx, tb.num_tables);
+  exchange_bwd_kernel<G, C><<<grid, kThreads, 0, s>>>(tb, D, dx, n, first, stride);
+}
+
+int launch_exchange_backward(const TableBatch &tb, int64_t D64, const float *dx, int64_t n, int64_t first,
+                             int64_t stride, cudaStream_t s) {
+  const int D = (int)D64;
+  if (n == 0 || tb.num_tables == 0) return FFEMB_OK;
+  ProfScope prof(FFEMB_PHASE_EXCHANGE, 1, s);
+  bool vec = (D % 4 == 0) && D <= 512 && stride % 4 == 0 && (uintptr_t)dx % 16 == 0;
+  for (int t = 0; t < tb.num_tables; t++)
+    vec = vec && (uintptr_t)tb.t[t].out % 16 == 0 && tb.t[t].lookup_base % 4 == 0;
+  if (!vec) {
+    dim3 grid(148 * 2, tb.num_tables);
+    exchange_bwd_generic_kernel<<<grid, kThreads, 0, s>>>(tb, D, dx, n, first, stride);
+  } else {
+    const int D4 = D / 4;
+    if (D4 <= 1) launch_xbwd<1, 1>(tb, D, dx, n, first, stride, s);
+    else if (D4 <= 2) launch_xbwd<2, 1>(tb, D, dx, n, first, stride, s);
+    else if (D4 <= 4) launch_xbwd<4, 1>(tb, D, dx, n, first, stride, s);
+    else if (D4 <= 8) launch_xbwd<8, 1>(tb, D, dx, n, first, stride, s);
+    else if (D4 <= 16) launch_xbwd<16, 1>(tb, D, dx, n, first, stride, s);
+    else if (D4 <= 32) launch_xbwd<32, 1>(tb, D, dx, n, first, stride, s);
+    else if (D4 <= 64) launch_xbwd<32, 2>(tb, D, dx, n, first, stride, s);
+    else launch_xbwd<32, 4>(tb, D, dx, n, first, stride, s);
+  }
+  return cuda_fail(cudaGetLastError(), "exchange backward launch");
 }
 
 }  // namespace ffemb

@@ -40,6 +40,14 @@ struct TableBatch {
   int32_t num_tables;
 };
 
+// Where pooled rows go.  npeers == 0: td.out + b*D (plain).  Else the fused exchange: sample b
+// belongs to rank b / ext and lands in that rank's Concat input (include/ffemb.h).
+struct OutMap {
+  float *peer[FFEMB_MAX_PEERS];
+  int64_t ext, stride;
+  int32_t npeers;
+};
+
 void set_error(const char *fmt, ...);
 int cuda_fail(cudaError_t e, const char *what);
 
@@ -58,7 +66,9 @@ static inline bool aggr_valid(int aggr) {
 }
 
 // launchers (defined in the .cu files)
-int launch_forward(const TableBatch &tb, int64_t D, int64_t B, int aggr, cudaStream_t s);
+int launch_forward(const TableBatch &tb, int64_t D, int64_t B, int aggr, const OutMap &om, cudaStream_t s);
+int launch_exchange_backward(const TableBatch &tb, int64_t D, const float *dx, int64_t n, int64_t first,
+                             int64_t stride, cudaStream_t s);
 int launch_backward_atomic(const TableBatch &tb, int64_t D, int64_t B, int aggr, cudaStream_t s);
 enum ApplyMode { APPLY_SGD = 0, APPLY_GRAD = 1 };
 int launch_backward_sorted(const TableBatch &tb, int64_t D, int64_t B, int aggr, float lr,

@@ -86,3 +86,88 @@ class TableWiseExchange:
                 for i in range(n):
                     outgrads[i][lo:hi].copy_(src[i])
         return outgrads
+
+
+class FusedTableWiseExchange:
+    """The exchange fused into the kernels, over NVLink peer memory (no NCCL on the data path).
+
+    forward : ffemb_forward_exchange — the gather-pool kernel of the table owner stores every pooled
+              row straight into the interaction input x_h [B_h][T*D] of the rank h that owns the
+              sample (the Concat layout, /root/reference/src/ops/concat.cu:211-251), tile by tile
+              while it computes; one cross-rank barrier on the stream orders the consumers.
+    backward: ffemb_exchange_backward — every rank pushes column block t of its dx_h into rows
+              [lo_h, hi_h) of the owner's output-grad buffer for table t; barrier; then the owner's
+              fused backward + SGD runs locally.
+    Buffers are torch symmetric memory (peer-mapped allocations + signal pads: plumbing only).
+    Same placement / batch split as TableWiseExchange (the collective form, kept as the comparison).
+    """
+
+    def __init__(self, num_tables, owner, batch, dim, rank, world, device, group=None):
+        import torch.distributed._symmetric_memory as symm
+        self.T, self.owner, self.B, self.D = int(num_tables), list(owner), int(batch), int(dim)
+        self.rank, self.world, self.device = rank, world, device
+        self.group = group if group is not None else dist.group.WORLD
+        self.owned_by = [[t for t in range(self.T) if self.owner[t] == g] for g in range(world)]
+        self.owned = self.owned_by[rank]
+        self.slot = {t: i for g in range(world) for i, t in enumerate(self.owned_by[g])}
+        self.ext = (self.B + world - 1) // world
+        self.lo, self.hi = batch_block(self.B, world, rank)
+        self.local_batch = self.hi - self.lo
+        self.stride = self.T * self.D
+        max_owned = max(1, max(len(o) for o in self.owned_by))
+        f32 = dict(dtype=torch.float32, device=device)
+        self.x = symm.empty((self.ext, self.stride), **f32)            # interaction input (embedding part)
+        self.gbuf = symm.empty((max_owned, self.B, self.D), **f32)     # output-grads of the owned tables
+        self.hx = symm.rendezvous(self.x, self.group)
+        self.hg = symm.rendezvous(self.gbuf, self.group)
+        self.x.zero_()
+        self.gbuf.zero_()
+        self.dx = torch.zeros((self.local_batch, self.stride), **f32)  # gradient of x, produced locally
+        self.outgrads = [self.gbuf[i] for i in range(len(self.owned))]
+        self._ex = None
+        self._push = None
+        torch.cuda.synchronize(device)
+        dist.barrier(group=self.group)
+
+    def _exchange_desc(self):
+        if self._ex is None:
+            from .binding import ffemb_exchange_t
+            ex = ffemb_exchange_t()
+            for h in range(self.world):
+                ex.peer_x[h] = int(self.hx.buffer_ptrs[h])
+            ex.num_peers, ex.batch_per_peer, ex.row_stride = self.world, self.ext, self.stride
+            self._ex = ex
+        return self._ex
+
+    def forward(self, coll, indices, stream=None):
+        """coll: EmbeddingCollection of the owned tables (in self.owned order). Fills x on all ranks."""
+        import ctypes as C
+        from .binding import check, ffemb_table_t, lib
+        from .embedding import _stream_ptr
+        n = len(self.owned)
+        if n:
+            arr = (ffemb_table_t * n)()
+            for i, t in enumerate(self.owned):
+                arr[i].idx, arr[i].out, arr[i].table = indices[i].data_ptr(), None, coll.weights[i].data_ptr()
+                arr[i].R, arr[i].L, arr[i].reserved = int(coll.weights[i].shape[0]), coll.bags[i], t * self.D
+            check(lib().ffemb_forward_exchange(arr, n, self.D, self.B, coll.aggr,
+                                               C.byref(self._exchange_desc()), _stream_ptr(stream)))
+        self.hx.barrier(channel=0)
+        return self.x
+
+    def backward(self, stream=None):
+        """dx on every rank -> self.outgrads ([B][D] per owned table) on the owners."""
+        from .binding import check, ffemb_table_t, lib
+        from .embedding import _stream_ptr
+        if self._push is None:
+            arr = (ffemb_table_t * self.T)()
+            for t in range(self.T):
+                base = int(self.hg.buffer_ptrs[self.owner[t]])
+                arr[t].out = base + self.slot[t] * self.B * self.D * 4
+                arr[t].reserved = t * self.D
+            self._push = arr
+        if self.local_batch:
+            check(lib().ffemb_exchange_backward(self._push, self.T, self.D, self.dx.data_ptr(),
+                                                self.local_batch, self.lo, self.stride, _stream_ptr(stream)))
+        self.hg.barrier(channel=1)
+        return self.outgrads

@@ -56,6 +56,7 @@ extern "C" {
 #define FFEMB_AGGR_MEAN 122 /* opt-in true mean (sum * (1/L)); not a reference enum value */
 
 #define FFEMB_MAX_TABLES 64 /* tables per batched call */
+#define FFEMB_MAX_PEERS 8   /* GPUs of one NVSwitch box */
 
 /* ABI-compatible with cudaStream_t */
 typedef struct CUstream_st *ffemb_stream_t;
@@ -86,6 +87,38 @@ FFEMB_API int ffemb_forward(const int64_t *idx, float *out, const float *table, 
 /* all tables of one GPU in one launch */
 FFEMB_API int ffemb_forward_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
                           int aggr, ffemb_stream_t stream);
+
+/* ---- forward fused with the exchange (multi-GPU, table-wise sharding) ------------------------
+ * The reference has no collective here: pooled outputs live in zero-copy host memory and Legion
+ * copies each batch slice to the GPU that owns those samples when the data-parallel Concat
+ * re-partitions them (MAP_TO_ZC_MEMORY, src/ops/embedding.cu:295-298; src/ops/concat.cu:88-97).
+ * Here the gather-pool kernel stores every pooled row STRAIGHT into the Concat input of the rank
+ * that owns the sample, over NVLink peer memory — the all-to-all happens tile by tile inside the
+ * compute kernel, in the Concat layout of src/ops/concat.cu:211-251:
+ *     sample b  ->  rank h = b / batch_per_peer (Legion's blocked split, src/runtime/model.cc:876-895)
+ *     peer_x[h][(b - h*batch_per_peer) * row_stride + tables[t].reserved + d]   d in [0, D)
+ * tables[t].reserved = column offset (in floats) of table t's block inside a sample row;
+ * tables[t].out is ignored.  peer_x[] are device pointers valid on THIS device (peer-mapped:
+ * cudaIpc / symmetric memory; peer_x[own rank] is plain local memory).  The caller orders the
+ * consumers after all ranks' kernels (a cross-rank barrier on the stream).                    */
+typedef struct ffemb_exchange {
+  float *peer_x[FFEMB_MAX_PEERS];
+  int32_t num_peers;
+  int32_t reserved;
+  int64_t batch_per_peer;
+  int64_t row_stride;
+} ffemb_exchange_t;
+FFEMB_API int ffemb_forward_exchange(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                           int aggr, const ffemb_exchange_t *ex, ffemb_stream_t stream);
+
+/* The transposed route for the output-grads: this rank holds dx [n_samples][row_stride] (the
+ * gradient of its Concat input, samples [first_sample, first_sample + n_samples) of the batch)
+ * and pushes column block tables[t].reserved of every sample into the output-grad buffer of the
+ * table's owner: tables[t].out = that owner's [B][D] output-grad (peer-mapped pointer),
+ * rows first_sample .. first_sample + n_samples - 1.  idx / table / R / L are ignored.          */
+FFEMB_API int ffemb_exchange_backward(const ffemb_table_t *tables, int num_tables, int64_t D,
+                            const float *dx, int64_t n_samples, int64_t first_sample,
+                            int64_t row_stride, ffemb_stream_t stream);
 
 /* ---- backward, API-exact (unfused): replaces Embedding::backward_kernel -------------------
  * Accumulates into the dense, caller-zeroed weight-grad like embed_backward
@@ -145,7 +178,8 @@ FFEMB_API int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int6
 #define FFEMB_PHASE_REDUCE_UP 4 /* upper levels */
 #define FFEMB_PHASE_ATOMIC 5    /* atomic comparison backward */
 #define FFEMB_PHASE_SMALL 6     /* bag-major backward of tables whose gradient fits on chip */
-#define FFEMB_NUM_PHASES 7
+#define FFEMB_PHASE_EXCHANGE 7  /* output-grad push over peer memory */
+#define FFEMB_NUM_PHASES 8
 FFEMB_API int ffemb_profile_enable(int on);
 FFEMB_API int ffemb_profile_collect(float *ms_per_phase, int64_t *launches_per_phase);
 FFEMB_API int64_t ffemb_launch_count(void);
