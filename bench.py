@@ -57,6 +57,9 @@ def parse():
                          "gather-pool kernel (NVLink peer memory); nccl = all_to_all_single + pack/unpack copies")
     ap.add_argument("--backward", default="sorted", choices=["sorted", "atomic"],
                     help="atomic = dense-grad atomicAdd comparison (not the product path)")
+    ap.add_argument("--no-overlap", action="store_true",
+                    help="run the backward's index sort in stream order instead of on a side stream "
+                         "under the forward pass / exchange (it depends on the indices only)")
     ap.add_argument("--rows-cap", type=int, default=0, help="cap rows per table (profiling under ncu only)")
     ap.add_argument("--cpu-batch", type=int, default=16384)
     ap.add_argument("--cpu-rows-cap", type=int, default=2_000_000)
@@ -253,14 +256,27 @@ def main():
     if args.backward == "atomic":  # the measured comparison: dense grad + atomics + dense update
         wgrads = [torch.zeros_like(w) for w in dw.W]
 
+    overlap = not args.no_overlap and args.backward == "sorted" and dw.coll is not None
+    side = torch.cuda.Stream(device=dev) if overlap else None
+
+    def presort(idx):
+        """keygen + radix sort on the side stream: needs the indices only, so it runs under the
+        forward pass and the exchange; the main stream joins before the segmented sum."""
+        if overlap:
+            side.wait_stream(stream)  # the previous step's reduction is done with the sort buffers
+            dw.coll.backward_prepare(idx, stream=side)
+
     def step(k):
         p = k % dw.pool
         idx = [b[p] for b in dw.idx]
+        presort(idx)
         if fx is not None:
             fx.forward(dw.coll, idx)      # gather-pool + exchange in one kernel, then a barrier
             fx.backward()                 # dx column blocks pushed to the table owners, barrier
             if dw.coll is not None:
-                dw.coll.backward_sgd(idx, dw.outgrad, wl.lr)
+                if overlap:
+                    stream.wait_stream(side)
+                dw.coll.backward_sgd(idx, dw.outgrad, wl.lr, prepared=overlap)
             return
         if dw.coll is not None:
             dw.coll.forward(idx, dw.out)
@@ -270,7 +286,9 @@ def main():
         if dw.coll is None:
             return
         if wgrads is None:
-            dw.coll.backward_sgd(idx, dw.outgrad, wl.lr)
+            if overlap:
+                stream.wait_stream(side)
+            dw.coll.backward_sgd(idx, dw.outgrad, wl.lr, prepared=overlap)
         else:
             for t, w in enumerate(dw.W):
                 wgrads[t].zero_()
@@ -361,7 +379,7 @@ def main():
                    "parallelism": ("single" if world == 1 else
                                    f"table-wise x{world} ({args.placement} placement), exchange={args.exchange}"),
                    "table_owner": own if world > 1 else None,
-                   "backward": args.backward,
+                   "backward": args.backward, "sort_overlapped_on_side_stream": bool(overlap),
                    "cache": f"inputs larger than L2: {args.pool} index batches cycled, "
                             f"{sum(wl.rows) * wl.dim * 4 / 1e9:.1f} GB of tables, random rows",
                    "unique_rows_per_step": int(U)},

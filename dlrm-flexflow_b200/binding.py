@@ -86,6 +86,8 @@ def lib():
     L.ffemb_backward_dense.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_sgd.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, f32, vp, sz, vp]
     L.ffemb_backward_sgd_batched.argtypes = [tp, i32, i64, i64, i32, f32, vp, sz, vp]
+    L.ffemb_backward_prepare.argtypes = [tp, i32, i64, i64, i32, vp, sz, vp]
+    L.ffemb_backward_sgd_prepared.argtypes = [tp, i32, i64, i64, i32, f32, vp, sz, vp]
     L.ffemb_backward_dense_batched.argtypes = [tp, i32, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_workspace.argtypes = [i64, i64, i64]
     L.ffemb_backward_workspace.restype = sz

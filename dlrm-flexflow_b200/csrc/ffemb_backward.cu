@@ -587,18 +587,18 @@ size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t
 // ---- host driver -----------------------------------------------------------------------------
 template <typename K, int G, int C, int MODE>
 static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr, int64_t n,
-                      int64_t total_rows, const Carve &c, cudaStream_t s) {
+                      int64_t total_rows, const Carve &c, cudaStream_t s, int stage) {
   K *keys_a = (K *)c.keys_a, *keys_b = (K *)c.keys_b;
   int max_l = 1;
   for (int t = 0; t < tb.num_tables; t++) max_l = tb.t[t].L > max_l ? tb.t[t].L : max_l;
-  {
+  if (stage != STAGE_APPLY) {
     ProfScope prof(FFEMB_PHASE_KEYGEN, 1, s);
     dim3 grid((unsigned)((B * max_l + kThreads - 1) / kThreads), tb.num_tables);
     keygen_kernel<K><<<grid, kThreads, 0, s>>>(tb, B, keys_a, c.vals_a);
   }
   int end_bit = 1;
   while (end_bit < (int)sizeof(K) * 8 && ((uint64_t)(total_rows - 1) >> end_bit) != 0) end_bit++;
-  {
+  if (stage != STAGE_APPLY) {
     // onesweep: histogram + scan + one pass per 8 key bits
     ProfScope prof(FFEMB_PHASE_SORT, 2 + (end_bit + 7) / 8, s);
     size_t tmp = c.cub_bytes;
@@ -606,6 +606,7 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
                                                     c.vals_b, (int)n, 0, end_bit, s);
     if (e != cudaSuccess) return cuda_fail(e, "radix sort");
   }
+  if (stage == STAGE_SORT) return cuda_fail(cudaGetLastError(), "sort launch");
 
   constexpr int SLOTS = 32 / G;
   const int64_t slots_per_cta = (int64_t)(kThreads / 32) * SLOTS;
@@ -657,20 +658,20 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
 
 template <typename K, int MODE>
 static int dispatch_g(const TableBatch &tb, int D, int64_t B, int aggr, float lr, int64_t n,
-                      int64_t rows, const Carve &c, cudaStream_t s) {
+                      int64_t rows, const Carve &c, cudaStream_t s, int stage) {
   const int D4 = D / 4;
-  if (D4 <= 1) return run_sorted<K, 1, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
-  if (D4 <= 2) return run_sorted<K, 2, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
-  if (D4 <= 4) return run_sorted<K, 4, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
-  if (D4 <= 8) return run_sorted<K, 8, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
-  if (D4 <= 16) return run_sorted<K, 16, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
-  if (D4 <= 32) return run_sorted<K, 32, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
-  if (D4 <= 64) return run_sorted<K, 32, 2, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
-  return run_sorted<K, 32, 4, MODE>(tb, D, B, aggr, lr, n, rows, c, s);
+  if (D4 <= 1) return run_sorted<K, 1, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
+  if (D4 <= 2) return run_sorted<K, 2, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
+  if (D4 <= 4) return run_sorted<K, 4, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
+  if (D4 <= 8) return run_sorted<K, 8, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
+  if (D4 <= 16) return run_sorted<K, 16, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
+  if (D4 <= 32) return run_sorted<K, 32, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
+  if (D4 <= 64) return run_sorted<K, 32, 2, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
+  return run_sorted<K, 32, 4, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
 }
 
 int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int aggr, float lr,
-                           ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s) {
+                           ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s, int stage) {
   int64_t n_all = 0;
   for (int t = 0; t < tb_all.num_tables; t++) n_all += B * tb_all.t[t].L;
   if (n_all == 0) return FFEMB_OK;
@@ -679,7 +680,7 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
     return FFEMB_EINVAL;
   }
   for (int t = 0; t < tb_all.num_tables; t++) {
-    if (((uintptr_t)tb_all.t[t].table | (uintptr_t)tb_all.t[t].out) % 16 != 0) {
+    if (stage != STAGE_SORT && ((uintptr_t)tb_all.t[t].table | (uintptr_t)tb_all.t[t].out) % 16 != 0) {
       set_error("sorted backward needs 16-byte aligned table and output-grad pointers (table %d)", t);
       return FFEMB_EINVAL;
     }
@@ -719,18 +720,18 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
   tb.row_base[tb.num_tables] = rows_l;
   const int64_t rows = (int64_t)rows_l;
   const Carve c = carve((char *)ws, (int64_t)n, rows > 0 ? rows : 1, D);
-  if (ts.num_tables) {
+  if (ts.num_tables && stage != STAGE_SORT) {
     const int rc = launch_backward_small(ts, n_tiny, D, B, aggr, lr, mode, (float *)((char *)ws + c.total), s);
     if (rc) return rc;
   }
   if (n == 0) return FFEMB_OK;
   if (wide_keys(rows)) {
     return mode == APPLY_SGD
-               ? dispatch_g<uint64_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s)
-               : dispatch_g<uint64_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s);
+               ? dispatch_g<uint64_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage)
+               : dispatch_g<uint64_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage);
   }
-  return mode == APPLY_SGD ? dispatch_g<uint32_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s)
-                           : dispatch_g<uint32_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s);
+  return mode == APPLY_SGD ? dispatch_g<uint32_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage)
+                           : dispatch_g<uint32_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage);
 }
 
 // ---- the atomic comparison: reference-equivalent unordered scatter ---------------------------

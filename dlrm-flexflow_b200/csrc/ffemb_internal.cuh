@@ -71,8 +71,11 @@ int launch_exchange_backward(const TableBatch &tb, int64_t D, const float *dx, i
                              int64_t stride, cudaStream_t s);
 int launch_backward_atomic(const TableBatch &tb, int64_t D, int64_t B, int aggr, cudaStream_t s);
 enum ApplyMode { APPLY_SGD = 0, APPLY_GRAD = 1 };
+// stage: the sort depends on the indices only, so it can be enqueued ahead of the output-grads
+enum { STAGE_ALL = 0, STAGE_SORT = 1, STAGE_APPLY = 2 };
 int launch_backward_sorted(const TableBatch &tb, int64_t D, int64_t B, int aggr, float lr,
-                           ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s);
+                           ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s,
+                           int stage = STAGE_ALL);
 size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t D);
 // tables whose whole gradient fits on chip (ffemb_backward_small.cu)
 int backward_path(int64_t R, int64_t L, int64_t D, int64_t B);  // 0 sorted, 1 tiny, 2 small

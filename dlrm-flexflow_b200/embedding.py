@@ -172,16 +172,42 @@ class EmbeddingCollection:
             check(lib().ffemb_forward_batched(sub, e - s, self.dim, batch, self.aggr, _stream_ptr(stream)))
         return outs
 
-    def backward_sgd(self, indices, out_grads, lr, stream=None):
+    def _workspaces(self, batch):
+        """One persistent workspace per chunk of <= 64 tables (prepare/apply pairs share it)."""
+        if not hasattr(self, "_ws") or self._ws_batch != batch:
+            self._ws, self._ws_batch = [], batch
+            for s, e in self._chunks():
+                n = batch * sum(self.bags[s:e])
+                rows = sum(int(w.shape[0]) for w in self.weights[s:e])
+                need = lib().ffemb_backward_workspace(int(n), int(rows), self.dim)
+                self._ws.append(torch.empty(max(need, 256), dtype=torch.uint8, device=self.device))
+        return self._ws
+
+    def backward_prepare(self, indices, stream=None):
+        """Keygen + radix sort of the lookups (needs the indices only): enqueue it early, e.g. on a
+        side stream under the forward pass / exchange; then call backward_sgd(..., prepared=True)."""
+        batch = int(indices[0].shape[0])
+        T = len(self.weights)
+        arr = (ffemb_table_t * T)()
+        for t in range(T):
+            _req(indices[t], torch.int64, "indices")
+            arr[t].idx, arr[t].out, arr[t].table = indices[t].data_ptr(), None, self.weights[t].data_ptr()
+            arr[t].R, arr[t].L = int(self.weights[t].shape[0]), self.bags[t]
+        for k, (s, e) in enumerate(self._chunks()):
+            ws = self._workspaces(batch)[k]
+            sub = C.cast(C.byref(arr, s * C.sizeof(ffemb_table_t)), C.POINTER(ffemb_table_t))
+            check(lib().ffemb_backward_prepare(sub, e - s, self.dim, batch, self.aggr, ws.data_ptr(),
+                                               ws.numel(), _stream_ptr(stream)))
+
+    def backward_sgd(self, indices, out_grads, lr, stream=None, prepared=False):
         batch = int(indices[0].shape[0])
         arr = self._descs(indices, out_grads, self.weights, batch)
-        for s, e in self._chunks():
-            n = batch * sum(self.bags[s:e])
-            rows = sum(int(w.shape[0]) for w in self.weights[s:e])
-            ws = self.meta.ensure_workspace(n, rows, self.dim, self.device)
+        fn = lib().ffemb_backward_sgd_prepared if prepared else lib().ffemb_backward_sgd_batched
+        for k, (s, e) in enumerate(self._chunks()):
+            ws = self._workspaces(batch)[k]
             sub = C.cast(C.byref(arr, s * C.sizeof(ffemb_table_t)), C.POINTER(ffemb_table_t))
-            check(lib().ffemb_backward_sgd_batched(sub, e - s, self.dim, batch, self.aggr, float(lr),
-                                                   ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
+            check(fn(sub, e - s, self.dim, batch, self.aggr, float(lr), ws.data_ptr(), ws.numel(),
+                     _stream_ptr(stream)))
 
     def backward_dense(self, indices, out_grads, weight_grads, stream=None):
         batch = int(indices[0].shape[0])

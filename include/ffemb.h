@@ -146,6 +146,18 @@ FFEMB_API int ffemb_backward_sgd(const int64_t *idx, const float *outgrad, float
 FFEMB_API int ffemb_backward_sgd_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
                                int aggr, float lr, void *workspace, size_t workspace_bytes,
                                ffemb_stream_t stream);
+/* The same, split in two: the sort of the lookups depends on the INDICES only, so a caller can
+ * enqueue it early — on a side stream, under the forward pass, the exchange or the dense MLPs
+ * (in FlexFlow: a task launched next to the forward task of the same step; the indices region is
+ * READ_ONLY in both) — and run only the segmented sum + row update once the output-grads exist.
+ * _prepare ignores tables[t].out; _prepared must get the same tables / D / B / aggr / workspace
+ * and be ordered after _prepare (stream order or an event).  Results are bit-identical to
+ * ffemb_backward_sgd_batched.                                                                 */
+FFEMB_API int ffemb_backward_prepare(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                           int aggr, void *workspace, size_t workspace_bytes, ffemb_stream_t stream);
+FFEMB_API int ffemb_backward_sgd_prepared(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                                int aggr, float lr, void *workspace, size_t workspace_bytes,
+                                ffemb_stream_t stream);
 FFEMB_API int ffemb_backward_dense_batched(const ffemb_table_t *tables, int num_tables, int64_t D,
                                  int64_t B, int aggr, void *workspace, size_t workspace_bytes,
                                  ffemb_stream_t stream);

@@ -242,6 +242,29 @@ def test_backward_batched_ragged_tables(ffemb, oracle, torch_cuda, D, B):
             assert np.all(np.abs(got - exact) <= table_tol(Ws[t]) * np.maximum(1, np.sqrt(cnt))[:, None]), t
 
 
+def test_backward_split_in_prepare_and_apply_is_bit_identical(ffemb, torch_cuda):
+    """ffemb_backward_prepare (sort, indices only, here on a side stream) + ffemb_backward_sgd_prepared
+    == ffemb_backward_sgd_batched, bit for bit."""
+    torch = torch_cuda
+    rows, bags, D, B = [5, 100000, 33, 20000, 4, 977], [1, 3, 20, 2, 7, 9], 64, 9000
+    Ws, idxs, gs = [], [], []
+    for t, (R, L) in enumerate(zip(rows, bags)):
+        W, idx, g = make_inputs(R, D, L, B, seed=300 + t)
+        Ws.append(W), idxs.append(dev(torch, idx)), gs.append(dev(torch, g))
+    a = [dev(torch, w) for w in Ws]
+    ffemb.EmbeddingCollection(a, bags).backward_sgd(idxs, gs, 0.01)
+    b = [dev(torch, w) for w in Ws]
+    coll = ffemb.EmbeddingCollection(b, bags)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    coll.backward_prepare(idxs, stream=side)
+    torch.cuda.current_stream().wait_stream(side)
+    coll.backward_sgd(idxs, gs, 0.01, prepared=True)
+    torch.cuda.synchronize()
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+
+
 def test_linearity_and_roundtrip_at_full_size(ffemb, torch_cuda):
     """Size-independent properties at BASELINE config-2 scale (26 tables, D=16, B=16384) without
     the CPU oracle: (1) forward of bag-1 indices is a pure gather; (2) with lr = 1 and
