@@ -407,36 +407,28 @@ def load_traffic(phase):
 
 
 def run_e2e(torch, pkg, args, wl, dw, ex, fx, dist, dev, barrier, total_lookups):
-    """Same step, HOST buffers: per step H2D of that step's indices and output-grads from
-    pinned memory, D2H of the pooled outputs; the step ends when the D2H has landed."""
-    if fx is not None:
-        return run_e2e_fused(torch, pkg, args, wl, dw, fx, dist, dev, barrier, total_lookups)
-    if dw.coll is None:
-        h_idx = h_g = h_out = []
-    else:
-        h_idx = [[b.cpu().pin_memory() for b in bs[:2]] for bs in dw.idx]
+    """The same step through the public host-buffer API (pkg.HostStep): per step H2D of that step's
+    indices and output-grads from pinned host memory, D2H of the pooled outputs (N>1: of this rank's
+    interaction input x; its dx is the uploaded gradient); a step ends when every copy has landed."""
+    if ex is not None:
+        return None  # the NCCL comparison form has no host-buffer API
+    have = dw.coll is not None
+    h_idx = [[b.cpu().pin_memory() for b in bs[:2]] for bs in dw.idx] if have else []
+    if fx is None:
         h_g = [g.cpu().pin_memory() for g in dw.outgrad]
         h_out = [torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in dw.out]
-    d_idx = [bs[0].clone() for bs in dw.idx]
-    h2d = sum(x[0].numel() * 8 for x in h_idx) + sum(x.numel() * 4 for x in h_g)
-    d2h = sum(x.numel() * 4 for x in h_out)
+        h2d = sum(x[0].numel() * 8 for x in h_idx) + sum(x.numel() * 4 for x in h_g)
+        d2h = sum(x.numel() * 4 for x in h_out)
+    else:
+        h_g = fx.dx.cpu().pin_memory()
+        h_out = torch.empty(fx.x.shape, dtype=fx.x.dtype).pin_memory()
+        h2d = sum(x[0].numel() * 8 for x in h_idx) + h_g.numel() * 4
+        d2h = h_out.numel() * 4
+    hs = pkg.HostStep(dw.coll, wl.batch, exchange=fx)
     stream = torch.cuda.current_stream()
 
     def step(k):
-        p = k % 2
-        for t in range(len(d_idx)):
-            d_idx[t].copy_(h_idx[t][p], non_blocking=True)
-            dw.outgrad[t].copy_(h_g[t], non_blocking=True)
-        if dw.coll is not None:
-            dw.coll.forward(d_idx, dw.out)
-            for t in range(len(d_idx)):
-                h_out[t].copy_(dw.out[t], non_blocking=True)
-        if ex is not None:
-            ex.forward(dw.out)
-            ex.backward(dw.outgrad)
-        if dw.coll is not None:
-            dw.coll.backward_sgd(d_idx, dw.outgrad, wl.lr)
-        torch.cuda.current_stream().synchronize()  # the caller consumes the result every step
+        hs.step([x[k % 2] for x in h_idx], h_g, h_out, wl.lr)
 
     steps = max(3, min(args.steps, 10))
     for k in range(2):
@@ -455,47 +447,8 @@ def run_e2e(torch, pkg, args, wl, dw, ex, fx, dist, dev, barrier, total_lookups)
         dist.all_reduce(t[1:], op=dist.ReduceOp.SUM)
         ms, h2d, d2h = t[0].item(), t[1].item(), t[2].item()
     return {"value": total_lookups / (ms / steps * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
-            "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
-
-
-def run_e2e_fused(torch, pkg, args, wl, dw, fx, dist, dev, barrier, total_lookups):
-    """N>1, fused exchange: per step H2D of the owned tables' indices (whole batch) and of this
-    rank's dx (its samples' output-grads), D2H of this rank's interaction input x."""
-    h_idx = [[b.cpu().pin_memory() for b in bs[:2]] for bs in dw.idx]
-    d_idx = [bs[0].clone() for bs in dw.idx]
-    h_dx = fx.dx.cpu().pin_memory()
-    h_x = torch.empty(fx.x.shape, dtype=fx.x.dtype).pin_memory()
-    h2d = sum(x[0].numel() * 8 for x in h_idx) + h_dx.numel() * 4
-    d2h = h_x.numel() * 4
-    stream = torch.cuda.current_stream()
-
-    def step(k):
-        for t in range(len(d_idx)):
-            d_idx[t].copy_(h_idx[t][k % 2], non_blocking=True)
-        fx.dx.copy_(h_dx, non_blocking=True)
-        fx.forward(dw.coll, d_idx)
-        h_x.copy_(fx.x, non_blocking=True)
-        fx.backward()
-        if dw.coll is not None:
-            dw.coll.backward_sgd(d_idx, dw.outgrad, wl.lr)
-        torch.cuda.current_stream().synchronize()
-
-    steps = max(3, min(args.steps, 10))
-    for k in range(2):
-        step(k)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record(stream)
-    for k in range(steps):
-        step(k)
-    e1.record(stream)
-    barrier()
-    t = torch.tensor([e0.elapsed_time(e1), h2d, d2h], dtype=torch.float64, device=dev)
-    dist.all_reduce(t[:1], op=dist.ReduceOp.MAX)
-    dist.all_reduce(t[1:], op=dist.ReduceOp.SUM)
-    ms, h2d, d2h = t[0].item(), t[1].item(), t[2].item()
-    return {"value": total_lookups / (ms / steps * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
-            "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
+            "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+            "api": "HostStep.step: 3 streams (H2D / compute / D2H), pinned host buffers"}
 
 
 # ---------------------------------------------------------------------------------------------

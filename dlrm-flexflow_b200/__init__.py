@@ -16,7 +16,8 @@ from .binding import (AGGR_MODE_AVG, AGGR_MODE_MEAN, AGGR_MODE_NONE, AGGR_MODE_S
 from . import sharding, synth
 from . import exchange
 from .embedding import Embedding, EmbeddingCollection, EmbeddingMeta
+from .hoststep import HostStep
 
 __all__ = ["AGGR_MODE_AVG", "AGGR_MODE_NONE", "AGGR_MODE_SUM", "AGGR_MODE_MEAN", "FFEmbError",
            "build_library", "declared_symbols", "exported_symbols", "lib", "library_path",
-           "launch_count", "profile_collect", "profile_enable", "Embedding", "EmbeddingCollection", "EmbeddingMeta", "synth", "sharding", "exchange"]
+           "launch_count", "profile_collect", "profile_enable", "Embedding", "EmbeddingCollection", "EmbeddingMeta", "HostStep", "synth", "sharding", "exchange"]

@@ -1,5 +1,2 @@
 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-B="python bench.py --steps 20 --warmup 5 --no-e2e --no-cpu"
-ph() { python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', round(d['ms_per_step'],3), d['roofline']['phases_ms_per_step'])"; }
-$B --no-overlap | ph serial
-$B | ph overlap
+python bench.py --steps 20 --warmup 5 --no-cpu | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['ms_per_step'],3), d['roofline']['phases_ms_per_step'], d['e2e'])"

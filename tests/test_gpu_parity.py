@@ -265,6 +265,29 @@ def test_backward_split_in_prepare_and_apply_is_bit_identical(ffemb, torch_cuda)
         assert torch.equal(x, y)
 
 
+def test_host_step_matches_device_step(ffemb, oracle, torch_cuda):
+    """HostStep (pinned host buffers, three streams) == the device-resident calls, bit for bit, and
+    the pooled outputs that land on the host are the oracle's."""
+    torch = torch_cuda
+    rows, bags, D, B = [5, 50000, 33, 977], [1, 3, 20, 9], 64, 6000
+    Ws, idxs, gs = [], [], []
+    for t, (R, L) in enumerate(zip(rows, bags)):
+        W, idx, g = make_inputs(R, D, L, B, seed=400 + t)
+        Ws.append(W), idxs.append(idx), gs.append(g)
+    a = [dev(torch, w) for w in Ws]
+    ca = ffemb.EmbeddingCollection(a, bags)
+    ca.backward_sgd([dev(torch, i) for i in idxs], [dev(torch, g) for g in gs], 0.01)
+    b = [dev(torch, w) for w in Ws]
+    hs = ffemb.HostStep(ffemb.EmbeddingCollection(b, bags), B)
+    h_idx = [torch.from_numpy(i).pin_memory() for i in idxs]
+    h_g = [torch.from_numpy(g).pin_memory() for g in gs]
+    h_out = [torch.empty((B, D)).pin_memory() for _ in rows]
+    hs.step(h_idx, h_g, h_out, 0.01)
+    for t in range(len(rows)):
+        assert np.array_equal(h_out[t].numpy(), oracle.forward(idxs[t], Ws[t])), t
+        assert torch.equal(a[t], b[t]), t
+
+
 def test_linearity_and_roundtrip_at_full_size(ffemb, torch_cuda):
     """Size-independent properties at BASELINE config-2 scale (26 tables, D=16, B=16384) without
     the CPU oracle: (1) forward of bag-1 indices is a pure gather; (2) with lr = 1 and
