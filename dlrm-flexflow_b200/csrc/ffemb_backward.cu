@@ -478,6 +478,10 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
   if (sl == 0) keys_out[2 * tile + 1] = pending ? keys[t0 + cnt - 1] : INV;
 }
 
+}  // namespace ffemb
+#include "ffemb_reduce1_ring.cuh"
+namespace ffemb {
+
 template <typename K, int G, int C, bool LEVEL1, int MODE>
 __global__ void __launch_bounds__(kThreads)
 reduce_level_kernel(const __grid_constant__ TableBatch tb, const K *keys, const uint32_t *vals,
@@ -626,7 +630,23 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     auto go = [&](auto kern, size_t sm) {
       kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], flags);
     };
-    if (aggr == FFEMB_AGGR_SUM) {
+    // gathers that hit L2 (the usual case): the cp.async ring variant, 4 entries ahead (measured on
+    // cfg3: 1.36 -> 1.22 ms; 8 stages: 1.26); gathers that miss (pipe): the register-pipelined one
+    // (cfg5: 13.9 ms against 14.6 for the ring).  FFEMB_R1_RING=0|4|8 overrides (tuning aid).
+    int ring = pipe ? 0 : 4;
+    if (const char *e = getenv("FFEMB_R1_RING")) ring = atoi(e);
+    if (C == 1 && ring > 0) {
+      auto gor = [&](auto kern, int S) {
+        const size_t sm = EPC * sizeof(EntryDesc) + (size_t)(T1 / 32) * S * 2 * 32 * 16;
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0]);
+      };
+      if constexpr (C == 1) {
+        const bool avg = aggr != FFEMB_AGGR_SUM;
+        if (ring >= 8) { if (avg) gor(reduce1_ring_kernel<K, G, MODE, true, 8>, 8); else gor(reduce1_ring_kernel<K, G, MODE, false, 8>, 8); }
+        else { if (avg) gor(reduce1_ring_kernel<K, G, MODE, true, 4>, 4); else gor(reduce1_ring_kernel<K, G, MODE, false, 4>, 4); }
+      }
+    } else if (aggr == FFEMB_AGGR_SUM) {
       if (pipe) go(reduce1_kernel<K, G, C, MODE, false, true>, sm_sum);
       else go(reduce1_kernel<K, G, C, MODE, false, false>, sm_sum);
     } else {
