@@ -82,6 +82,8 @@ def lib():
     L.ffemb_forward_batched.argtypes = [tp, i32, i64, i64, i32, vp]
     L.ffemb_forward_exchange.argtypes = [tp, i32, i64, i64, i32, C.POINTER(ffemb_exchange_t), vp]
     L.ffemb_exchange_backward.argtypes = [tp, i32, i64, vp, i64, i64, i64, vp]
+    L.ffemb_forward_rowwise.argtypes = [vp, vp, C.POINTER(vp), i32, i64, i64, i64, i64, i32, vp]
+    L.ffemb_rowwise_localize.argtypes = [vp, vp, i64, i64, i32, vp, i64, vp]
     L.ffemb_backward_dense_atomic.argtypes = [vp, vp, vp, i64, i64, i64, i32, vp]
     L.ffemb_backward_dense.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_sgd.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, f32, vp, sz, vp]

@@ -171,3 +171,74 @@ class FusedTableWiseExchange:
                                                 self.local_batch, self.lo, self.stride, _stream_ptr(stream)))
         self.hg.barrier(channel=1)
         return self.outgrads
+
+
+class RowWiseTable:
+    """One table of `rows` rows sharded ROW-WISE over the ranks (for tables beyond one GPU's HBM;
+    not in the reference, see include/ffemb.h).  Shard map: sharding.rows_per_shard / row_owner.
+
+    forward     : this rank's samples only; rows are read from the owner's shard over NVLink peer
+                  memory inside the gather-pool kernel (bit-identical to the unsharded table).
+    backward_sgd: indices and output-grads of the whole batch are all-gathered (the one real
+                  exchange of this path: torch.distributed all_gather, NCCL on GPUs), localised
+                  (foreign rows -> the scratch row appended to the shard) and the ordinary
+                  deterministic backward + SGD runs on the shard.
+    """
+
+    def __init__(self, rows, dim, bag, batch, rank, world, device, aggr=21, group=None):
+        import torch.distributed._symmetric_memory as symm
+        from .embedding import EmbeddingCollection
+        from .sharding import rows_per_shard, shard_rows
+        self.R, self.D, self.L, self.B = int(rows), int(dim), int(bag), int(batch)
+        self.rank, self.world, self.device, self.aggr = rank, world, device, int(aggr)
+        self.group = group if group is not None else dist.group.WORLD
+        self.rps = rows_per_shard(self.R, world)
+        self.local_rows = shard_rows(self.R, world, rank)
+        self.ext = (self.B + world - 1) // world
+        self.lo, self.hi = batch_block(self.B, world, rank)
+        self.shard = symm.empty((self.rps + 1, self.D), dtype=torch.float32, device=device)  # + scratch row
+        self.h = symm.rendezvous(self.shard, self.group)
+        self.shard.zero_()
+        self.idx_full = torch.zeros((world * self.ext, self.L), dtype=torch.int64, device=device)
+        self.idx_local = torch.empty((self.B, self.L), dtype=torch.int64, device=device)
+        self.g_full = torch.zeros((world * self.ext, self.D), dtype=torch.float32, device=device)
+        self._pad_i = torch.zeros((self.ext, self.L), dtype=torch.int64, device=device)
+        self._pad_g = torch.zeros((self.ext, self.D), dtype=torch.float32, device=device)
+        self.coll = EmbeddingCollection([self.shard], [self.L], self.aggr)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=self.group)
+
+    def load_rows(self, full_table):
+        """Test/bench helper: take this rank's rows out of an unsharded [R][D] tensor."""
+        lo = self.rank * self.rps
+        self.shard[:self.local_rows].copy_(full_table[lo:lo + self.local_rows])
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+
+    def forward(self, idx, out=None, stream=None):
+        """idx: int64 [B_h][L] global row ids of this rank's samples -> pooled [B_h][D]."""
+        import ctypes as C
+        from .binding import check, lib
+        from .embedding import _stream_ptr
+        n = int(idx.shape[0])
+        if out is None:
+            out = torch.empty((n, self.D), dtype=torch.float32, device=self.device)
+        ptrs = (C.c_void_p * self.world)(*[int(p) for p in self.h.buffer_ptrs])
+        check(lib().ffemb_forward_rowwise(idx.data_ptr(), out.data_ptr(), ptrs, self.world, self.rps,
+                                          self.L, self.D, n, self.aggr, _stream_ptr(stream)))
+        return out
+
+    def backward_sgd(self, idx, outgrad, lr, stream=None):
+        """idx [B_h][L], outgrad [B_h][D] of this rank's samples; updates this rank's shard."""
+        from .binding import check, lib
+        from .embedding import _stream_ptr
+        n = self.hi - self.lo
+        self._pad_i[:n].copy_(idx)
+        self._pad_g[:n].copy_(outgrad)
+        dist.all_gather_into_tensor(self.idx_full, self._pad_i, group=self.group)  # also orders every
+        dist.all_gather_into_tensor(self.g_full, self._pad_g, group=self.group)    # rank's forward first
+        check(lib().ffemb_rowwise_localize(self.idx_full.data_ptr(), self.idx_local.data_ptr(),
+                                           self.B * self.L, self.rps, self.rank,
+                                           self.shard[self.rps].data_ptr(), self.D, _stream_ptr(stream)))
+        self.coll.backward_sgd([self.idx_local], [self.g_full[:self.B]], lr, stream=stream)
+        self.h.barrier(channel=0)  # shards are consistent before anyone's next forward reads them

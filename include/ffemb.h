@@ -120,6 +120,24 @@ FFEMB_API int ffemb_exchange_backward(const ffemb_table_t *tables, int num_table
                             const float *dx, int64_t n_samples, int64_t first_sample,
                             int64_t row_stride, ffemb_stream_t stream);
 
+/* ---- row-wise sharded tables (a table too large for one GPU) --------------------------------
+ * Not in the reference (Embedding asserts sample-dim-only partitioning, src/ops/embedding.cu:84-85).
+ * Shard map = Legion's blocked restriction on the row dimension (src/runtime/model.cc:880-892):
+ * rows_per_shard = ceil(R / G), owner(row) = row / rows_per_shard, local = row % rows_per_shard.
+ * forward_rowwise pools THIS rank's samples (idx [B][L] holds global row ids) and reads every row
+ * from the owner's shard over NVLink peer memory (peer_shards[g] = device pointer to shard g,
+ * valid on this device); adds are sequential in j, so results are bit-identical to the unsharded
+ * table.  For the backward the shard owner runs ffemb_backward_sgd over the WHOLE batch on local
+ * indices made by rowwise_localize: rows of other shards map to the scratch row `rows_per_shard`
+ * that the owner appends to its shard (the shard buffer holds rows_per_shard + 1 rows; the scratch
+ * row is cleared here and never read by anyone).                                               */
+FFEMB_API int ffemb_forward_rowwise(const int64_t *idx, float *out, const float *const *peer_shards,
+                          int num_peers, int64_t rows_per_shard, int64_t L, int64_t D, int64_t B,
+                          int aggr, ffemb_stream_t stream);
+FFEMB_API int ffemb_rowwise_localize(const int64_t *idx, int64_t *local_idx, int64_t n,
+                           int64_t rows_per_shard, int shard, float *scratch_row, int64_t D,
+                           ffemb_stream_t stream);
+
 /* ---- backward, API-exact (unfused): replaces Embedding::backward_kernel -------------------
  * Accumulates into the dense, caller-zeroed weight-grad like embed_backward
  * (src/ops/embedding.cu:192-217).
