@@ -46,7 +46,7 @@ int backward_path(int64_t R, int64_t L, int64_t D, int64_t B) {
   const int64_t n = B * L;
   if (n < 16384 || n < 16 * R) return 0;  // little duplication / little work: sorting is fine
   if (R <= kTinyRows) return 1;
-  if (R * D * 4 <= kSmallAccBytes && R < 65536 && L >= 8) return 2;  // g re-read L times otherwise
+  if (R * D * 4 <= kSmallAccBytes && R <= 256 && L >= 8) return 2;  // g re-read L times otherwise
   return 0;
 }
 
@@ -201,27 +201,33 @@ bwd_tiny_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, float *
 }
 
 // ---- small: shared-memory accumulator, rows owned by slots ---------------------------------------
-// Per chunk (<= 1024 lookups) the lookups are first put in OWNER order with a stable counting
-// sort in shared memory (warp match + ranks, per-batch counts, one prefix) — positions depend on
-// the data only, so the order is reproducible — then every slot walks its own stretch: per lookup
-// one broadcast LDS (packed bag|row), two LDS.128 (output-grad fragment, accumulator fragment), four
-// FADDs and one STS.128.
-static constexpr int kSmallMaxLookups = 1024, kSmallMaxChunk = 32;
+// Per chunk (<= 512 lookups) the lookups are first put in ROW order — owner-major, so that the rows
+// a slot owns (row % #slots == slot) are one contiguous stretch — with a stable counting sort in
+// shared memory (warp match + ranks, per-batch counts, one prefix): positions depend on the data
+// only, so the order is reproducible.  Then every slot walks its stretch row by row with the row's
+// accumulator fragment in REGISTERS: per lookup one broadcast LDS (bag number), one LDS.128 of the
+// staged output-grad fragment and four FADDs; the accumulator row is read and written once per
+// chunk.  (The first version sorted by owner only and did LDS.128 + STS.128 on the accumulator per
+// lookup: bound by the shared-memory pipe, l1tex 84 %, profiles/r1d_summary.md.)
+static constexpr int kSmallMaxLookups = 512, kSmallMaxChunk = 32, kSmallMaxRows = 256;
 __host__ __device__ __forceinline__ int small_chunk_bags(int L) {
   const int c = kSmallMaxLookups / L;
   return c > kSmallMaxChunk ? kSmallMaxChunk : c;
 }
+__host__ __device__ __forceinline__ int small_bins(int R, int NU) { return ((R + NU - 1) / NU) * NU; }
 
 template <int G, bool AVG>
 __global__ void __launch_bounds__(kSmallThreads)
 bwd_small_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, float *partials, uint32_t cta_off) {
   constexpr int SLOTS = 32 / G, NW = kSmallThreads / 32, NU = NW * SLOTS;  // NU: power of two
-  constexpr int NBATCH = kSmallMaxLookups / 32, PER = kSmallMaxLookups / kSmallThreads;
+  constexpr int NBATCH = kSmallMaxLookups / 32;
+  static_assert(kSmallMaxLookups == kSmallThreads, "one lookup per thread and chunk");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const uint32_t cta = blockIdx.x + cta_off;
   const int t = find_by_cta(tb, cta);
   const TableDesc &td = tb.t[t];
   const int L = td.L, R = (int)td.R;
+  const int rpo = (R + NU - 1) / NU, NBIN = rpo * NU;  // rows per owner; bin = owner * rpo + row / NU
   const int64_t bpc = td.lookup_base;
   const int64_t c = cta - tb.cta_base[t];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -232,13 +238,13 @@ bwd_small_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, float 
   ChunkStage st;
   st.g = td.out; st.idx = td.idx; st.D = D; st.L = L; st.chb = small_chunk_bags(L); st.nthreads = kSmallThreads;
   st.b0 = c * bpc; st.b1 = min(B, st.b0 + bpc);
-  float *acc = reinterpret_cast<float *>(smem_raw);                       // [R][D]
-  st.gs = acc + (size_t)R * D;                                            // [2][chb][D]
-  st.is = reinterpret_cast<int64_t *>(st.gs + 2 * st.chb * D);            // [2][chb][L]
-  uint32_t *sorted = reinterpret_cast<uint32_t *>(st.is + 2 * st.chb * L);  // [1024] (bag << 16) | row
-  uint32_t *wcnt = sorted + kSmallMaxLookups;                             // [NBATCH][NU]
-  uint32_t *start = wcnt + NBATCH * NU;                                   // [NU + 1]
-  uint32_t *total = start + NU + 1;                                       // [NU]
+  float *acc = reinterpret_cast<float *>(smem_raw);                         // [R][D]
+  st.gs = acc + (size_t)R * D;                                              // [2][chb][D]
+  st.is = reinterpret_cast<int64_t *>(st.gs + 2 * st.chb * D);              // [2][chb][L]
+  uint32_t *sorted = reinterpret_cast<uint32_t *>(st.is + 2 * st.chb * L);  // [512] bag number
+  uint32_t *wcnt = sorted + kSmallMaxLookups;                               // [NBATCH][NBIN]
+  uint32_t *start = wcnt + NBATCH * NBIN;                                   // [NBIN + 1]
+  uint32_t *total = start + NBIN + 1;                                       // [NBIN]
 
   for (int i = threadIdx.x; i < R * (D >> 2); i += kSmallThreads)
     reinterpret_cast<float4 *>(acc)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -248,67 +254,75 @@ bwd_small_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, float 
   for (int k = 0; k < nchunks; k++) {
     const int buf = k & 1;
     if (k + 1 < nchunks) { st.issue(k + 1, buf ^ 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
-    for (int i = threadIdx.x; i < NBATCH * NU; i += kSmallThreads) wcnt[i] = 0;
+    for (int i = threadIdx.x; i < NBATCH * NBIN; i += kSmallThreads) wcnt[i] = 0;
     __syncthreads();  // (a) chunk k landed; counts cleared; accumulator zero-fill visible (k == 0)
     const int nb = st.bags(k);
     float *gb = st.gs + (size_t)buf * st.chb * D;
     const int64_t *ib = st.is + (size_t)buf * st.chb * L;
     const int n = nb * L;
-    // 1. rank of every lookup among the lookups of its warp-batch with the same owner
-    int row[PER], rank[PER];
-#pragma unroll
-    for (int q = 0; q < PER; q++) {
-      const int e = q * kSmallThreads + threadIdx.x;  // batch = e >> 5 = q * NW + warp
-      row[q] = e < n ? (int)ib[e] : -1;
-      const int owner = row[q] >= 0 ? (row[q] & (NU - 1)) : NU;
-      const unsigned m = __match_any_sync(0xffffffffu, owner);
-      rank[q] = __popc(m & ((1u << lane) - 1u));
-      if (rank[q] == 0 && row[q] >= 0) wcnt[(q * NW + warp) * NU + owner] = __popc(m);
-    }
+    // 1. rank of every lookup among the lookups of its warp-batch that hit the same row
+    const int e = threadIdx.x;  // batch = warp
+    const int row = e < n ? (int)ib[e] : -1;
+    const int bin = row >= 0 ? (row & (NU - 1)) * rpo + row / NU : NBIN;
+    const unsigned m = __match_any_sync(0xffffffffu, bin);
+    const int rank = __popc(m & ((1u << lane) - 1u));
+    if (rank == 0 && row >= 0) wcnt[warp * NBIN + bin] = __popc(m);
     if (AVG)  // gradient = output-grad / in_dim per element, once per staged row (embedding.cu:210)
       for (int i = threadIdx.x; i < nb * D; i += kSmallThreads) gb[i] = div_rn(gb[i], Lf, Linv);
     __syncthreads();  // (b)
-    // 2. per owner: exclusive prefix of the per-batch counts (lane = batch)
-    for (int o = warp; o < NU; o += NW) {
-      const uint32_t x = wcnt[lane * NU + o];
+    // 2. per bin: exclusive prefix of the per-batch counts (lane = batch)
+    for (int o = warp; o < NBIN; o += NW) {
+      const uint32_t x = lane < NBATCH ? wcnt[lane * NBIN + o] : 0u;
       uint32_t incl = x;
+#pragma unroll
+      for (int d = 1; d < NBATCH; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += y;
+      }
+      if (lane < NBATCH) wcnt[lane * NBIN + o] = incl - x;
+      if (lane == NBATCH - 1) total[o] = incl;
+    }
+    __syncthreads();  // (c)
+    if (warp == 0) {  // exclusive prefix over the bins: a lane takes a run of consecutive bins
+      const int per = (NBIN + 31) / 32;
+      uint32_t mine = 0;
+      for (int i = 0; i < per; i++) {
+        const int o = lane * per + i;
+        if (o < NBIN) mine += total[o];
+      }
+      uint32_t incl = mine;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
         const uint32_t y = __shfl_up_sync(0xffffffffu, incl, d);
         if (lane >= d) incl += y;
       }
-      wcnt[lane * NU + o] = incl - x;
-      if (lane == 31) total[o] = incl;
-    }
-    __syncthreads();  // (c)
-    if (threadIdx.x <= NU) {
-      uint32_t s0 = 0;
-      for (int o = 0; o < (int)threadIdx.x; o++) s0 += total[o];
-      start[threadIdx.x] = s0;
+      uint32_t run = incl - mine;
+      for (int i = 0; i < per; i++) {
+        const int o = lane * per + i;
+        if (o < NBIN) { start[o] = run; run += total[o]; }
+      }
+      if (lane == 31) start[NBIN] = incl;
     }
     __syncthreads();  // (d)
-    // 3. stable scatter into owner order
-#pragma unroll
-    for (int q = 0; q < PER; q++) {
-      if (row[q] >= 0) {
-        const int e = q * kSmallThreads + threadIdx.x;
-        const int owner = row[q] & (NU - 1);
-        const uint32_t bag = L == 1 ? (uint32_t)e : __umulhi((uint32_t)e, magic);
-        sorted[start[owner] + wcnt[(q * NW + warp) * NU + owner] + rank[q]] = (bag << 16) | (uint32_t)row[q];
-      }
+    // 3. stable scatter into row order
+    if (row >= 0) {
+      const uint32_t bag = L == 1 ? (uint32_t)e : __umulhi((uint32_t)e, magic);
+      sorted[start[bin] + wcnt[warp * NBIN + bin] + rank] = bag;
     }
     __syncthreads();  // (e)
-    // 4. every slot adds the lookups of the rows it owns, in (bag, j) order
-    {
+    // 4. every slot adds the lookups of the rows it owns, row by row, in (bag, j) order
+    if (own) {
       const int unit = warp * SLOTS + sub;
-      const uint32_t lo = start[unit], hi = start[unit + 1];
-      if (own) {
-        for (uint32_t i = lo; i < hi; i++) {
-          const uint32_t ent = sorted[i];
-          const float4 x = *reinterpret_cast<const float4 *>(gb + (ent >> 16) * D + 4 * sl);
-          float4 *ap = reinterpret_cast<float4 *>(acc + (ent & 0xffffu) * D + 4 * sl);
+      for (int i = 0; i < rpo; i++) {
+        const int r = i * NU + unit;
+        const uint32_t lo = start[unit * rpo + i], hi = start[unit * rpo + i + 1];
+        if (r < R && hi > lo) {
+          float4 *ap = reinterpret_cast<float4 *>(acc + r * D + 4 * sl);
           float4 a = *ap;
-          a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+          for (uint32_t q = lo; q < hi; q++) {
+            const float4 x = *reinterpret_cast<const float4 *>(gb + sorted[q] * D + 4 * sl);
+            a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+          }
           *ap = a;
         }
       }
@@ -418,11 +432,16 @@ static int run_small(TableBatch &tb, int n_tiny, int D, int64_t B, int aggr, flo
   }
   if (n_small) {
     constexpr int NU = (kSmallThreads / 32) * (32 / G);
-    const size_t fixed = (size_t)kSmallMaxLookups * 4 + (size_t)(kSmallMaxLookups / 32) * NU * 4 + (2 * NU + 2) * 4;
+    auto fixed_of = [&](int R) {
+      const size_t nbin = (size_t)small_bins(R, NU);
+      return (size_t)kSmallMaxLookups * 4 + (size_t)(kSmallMaxLookups / 32) * nbin * 4 + (2 * nbin + 2) * 4;
+    };
+    const size_t fixed = fixed_of(kSmallMaxRows);
     size_t sm = 0;
     for (int t = n_tiny; t < T; t++) {
       const int chb = small_chunk_bags(tb.t[t].L);
-      const size_t x = (size_t)tb.t[t].R * D * 4 + 2 * (size_t)chb * D * 4 + 2 * (size_t)chb * tb.t[t].L * 8 + fixed;
+      const size_t x = (size_t)tb.t[t].R * D * 4 + 2 * (size_t)chb * D * 4 + 2 * (size_t)chb * tb.t[t].L * 8 +
+                       fixed_of((int)tb.t[t].R);
       sm = x > sm ? x : sm;
     }
     auto go = [&](auto kern) -> int {

@@ -393,13 +393,30 @@ exchange_bwd_kernel(const __grid_constant__ TableBatch tb, int D, const float *_
   const int sub = lane / G, sl = lane % G;
   const int D4 = D >> 2;
   const uint64_t pol = policy_evict_first();
-  for (int64_t sidx = ((int64_t)blockIdx.x * (kThreads / 32) + warp) * SLOTS + sub; sidx < n;
-       sidx += (int64_t)gridDim.x * (kThreads / 32) * SLOTS) {
-    const float *src = dx + sidx * stride + td.lookup_base;
-    float *dst = td.out + (first + sidx) * (int64_t)D;
+  constexpr int U = 4;  // samples per slot and iteration: U loads in flight, then U remote stores
+  const int64_t step = (int64_t)gridDim.x * (kThreads / 32) * SLOTS;
+  for (int64_t s0 = ((int64_t)blockIdx.x * (kThreads / 32) + warp) * SLOTS + sub; s0 < n; s0 += U * step) {
+    float4 v[U][C];
 #pragma unroll
-    for (int c = 0; c < C; c++)
-      if (sl + c * G < D4) st_row_hint(dst + 4 * (sl + c * G), ldg_row_hint(src + 4 * (sl + c * G), pol), pol);
+    for (int u = 0; u < U; u++) {
+      const int64_t sidx = s0 + u * step;
+      if (sidx < n) {
+        const float *src = dx + sidx * stride + td.lookup_base;
+#pragma unroll
+        for (int c = 0; c < C; c++)
+          if (sl + c * G < D4) v[u][c] = ldg_row_hint(src + 4 * (sl + c * G), pol);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t sidx = s0 + u * step;
+      if (sidx < n) {
+        float *dst = td.out + (first + sidx) * (int64_t)D;
+#pragma unroll
+        for (int c = 0; c < C; c++)
+          if (sl + c * G < D4) st_row_hint(dst + 4 * (sl + c * G), v[u][c], pol);
+      }
+    }
   }
 }
 
