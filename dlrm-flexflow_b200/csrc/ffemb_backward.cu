@@ -39,6 +39,7 @@ static constexpr int kThreads = 256;
 static constexpr int CH1 = 64;  // level-1 tile (sorted lookups per slot)
 static constexpr int CH2 = 32;  // level-k tile (partial rows per slot)
 static constexpr int kSmallLevel = 1 << 8;   // <= this many partial slots: finish in one CTA (a CTA walks 8 tiles at a time, ~6 us a round)
+static constexpr int64_t kStreamTableBytes = 64ll << 20;  // tables above this do not stay in L2
 static constexpr int BAG_BITS = 26;          // sort payload = (table << 26) | bag
 static constexpr uint32_t BAG_MASK = (1u << BAG_BITS) - 1;
 
@@ -249,6 +250,18 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
 //     for run ends, the table row (L2 evict_first: touched once per step), then FADDs in sorted
 //     order and at a run end the FFMA + store.
 // Runs cut by a tile edge leave as partial rows for the upper levels (same contract as before).
+// CTA -> work item map of level 1.  The sorted array holds the lookups of the tables far larger
+// than L2 first (CTAs [0, split): their row read-modify-writes are HBM-bound), then those of the
+// L2-resident tables (output-grad gathers, L2-bound).  Handing the two regions out proportionally
+// interleaved keeps one table of each kind in flight at any time, so the two regimes overlap;
+// two output-grads (2 x B*D*4 bytes) still fit L2.  Tile contents do not change: same results.
+__device__ __forceinline__ uint32_t mix_cta(uint32_t i, uint32_t grid, uint32_t split) {
+  if (split == 0 || split >= grid) return i;
+  const uint32_t a0 = (uint32_t)(((uint64_t)i * split) / grid);
+  const uint32_t a1 = (uint32_t)(((uint64_t)(i + 1) * split) / grid);
+  return a1 != a0 ? a0 : split + (i - a0);
+}
+
 struct __align__(16) EntryDesc {
   const float *gp;  // output-grad row of this lookup (nullptr: past the end of the array)
   float *wp;        // table row to update when this entry ends its run, else nullptr
@@ -260,7 +273,7 @@ template <typename K, int G, int C, int MODE, bool AVG, bool PIPE>
 __global__ void __launch_bounds__(L1Threads<G>::value, 512 / L1Threads<G>::value)
 reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
                const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
-               float *rows_out, int flags) {
+               float *rows_out, int flags, uint32_t split) {
   constexpr int THREADS = L1Threads<G>::value;
   constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
@@ -270,7 +283,7 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   EntryDesc *wd = reinterpret_cast<EntryDesc *>(smem_raw) + warp * EPW;
   float2 *wscale = reinterpret_cast<float2 *>(smem_raw + sizeof(EntryDesc) * WARPS * EPW) + warp * EPW;
-  const int64_t wbase = ((int64_t)blockIdx.x * WARPS + warp) * EPW;
+  const int64_t wbase = ((int64_t)mix_cta(blockIdx.x, gridDim.x, split) * WARPS + warp) * EPW;
   if (wbase >= n) return;  // warp-uniform; only __syncwarp below
   const int D4 = D >> 2;
 
@@ -591,7 +604,7 @@ size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t
 // ---- host driver -----------------------------------------------------------------------------
 template <typename K, int G, int C, int MODE>
 static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr, int64_t n,
-                      int64_t total_rows, const Carve &c, cudaStream_t s, int stage) {
+                      int64_t total_rows, const Carve &c, cudaStream_t s, int stage, int64_t n_stream) {
   K *keys_a = (K *)c.keys_a, *keys_b = (K *)c.keys_b;
   int max_l = 1;
   for (int t = 0; t < tb.num_tables; t++) max_l = tb.t[t].L > max_l ? tb.t[t].L : max_l;
@@ -621,6 +634,10 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     constexpr int T1 = L1Threads<G>::value;
     constexpr int EPC = (T1 / 32) * SLOTS * CH1;  // entries per CTA
     const unsigned grid1 = (unsigned)((n + EPC - 1) / EPC);
+    // CTAs [0, split) hold the streaming tables' lookups (they come first in the key order)
+    uint32_t split = (uint32_t)((n_stream + EPC - 1) / EPC);
+    if (n_stream == 0 || n_stream >= n) split = 0;
+    if (const char *e = getenv("FFEMB_R1_MIX")) { if (!atoi(e)) split = 0; }  // tuning aid
     // output-grad of one table larger than (half of) L2 -> the gathers miss: pipelined variant
     bool pipe = B * (int64_t)D * 4 > (48ll << 20);
     int flags = 0;
@@ -628,7 +645,7 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     if (const char *e = getenv("FFEMB_R1_PIPE")) pipe = atoi(e) != 0;
     const size_t sm_sum = EPC * sizeof(EntryDesc), sm_avg = EPC * (sizeof(EntryDesc) + sizeof(float2));
     auto go = [&](auto kern, size_t sm) {
-      kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], flags);
+      kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], flags, split);
     };
     // gathers that hit L2 (the usual case): the cp.async ring variant, 4 entries ahead (measured on
     // cfg3: 1.36 -> 1.22 ms; 8 stages: 1.26); gathers that miss (pipe): the register-pipelined one
@@ -639,7 +656,7 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
       auto gor = [&](auto kern, int S) {
         const size_t sm = EPC * sizeof(EntryDesc) + (size_t)(T1 / 32) * S * 2 * 32 * 16;
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0]);
+        kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], split);
       };
       if constexpr (C == 1) {
         const bool avg = aggr != FFEMB_AGGR_SUM;
@@ -678,16 +695,16 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
 
 template <typename K, int MODE>
 static int dispatch_g(const TableBatch &tb, int D, int64_t B, int aggr, float lr, int64_t n,
-                      int64_t rows, const Carve &c, cudaStream_t s, int stage) {
+                      int64_t rows, const Carve &c, cudaStream_t s, int stage, int64_t n_stream) {
   const int D4 = D / 4;
-  if (D4 <= 1) return run_sorted<K, 1, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
-  if (D4 <= 2) return run_sorted<K, 2, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
-  if (D4 <= 4) return run_sorted<K, 4, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
-  if (D4 <= 8) return run_sorted<K, 8, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
-  if (D4 <= 16) return run_sorted<K, 16, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
-  if (D4 <= 32) return run_sorted<K, 32, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
-  if (D4 <= 64) return run_sorted<K, 32, 2, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
-  return run_sorted<K, 32, 4, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage);
+  if (D4 <= 1) return run_sorted<K, 1, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
+  if (D4 <= 2) return run_sorted<K, 2, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
+  if (D4 <= 4) return run_sorted<K, 4, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
+  if (D4 <= 8) return run_sorted<K, 8, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
+  if (D4 <= 16) return run_sorted<K, 16, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
+  if (D4 <= 32) return run_sorted<K, 32, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
+  if (D4 <= 64) return run_sorted<K, 32, 2, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
+  return run_sorted<K, 32, 4, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
 }
 
 int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int aggr, float lr,
@@ -727,15 +744,21 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
       }
     }
   }
-  uint64_t rows_l = 0, n = 0;
-  for (int t = 0; t < tb_all.num_tables; t++) {
-    if (tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) != 0) continue;
-    TableDesc &d = tb.t[tb.num_tables];
-    d = tb_all.t[t];
-    d.lookup_base = (uint32_t)n;
-    tb.row_base[tb.num_tables++] = rows_l;
-    rows_l += (uint64_t)d.R;
-    n += (uint64_t)B * d.L;
+  // key order: the tables far larger than L2 first, then the L2-resident ones (see mix_cta)
+  uint64_t rows_l = 0, n = 0, n_stream = 0;
+  for (int pass = 0; pass < 2; pass++) {
+    for (int t = 0; t < tb_all.num_tables; t++) {
+      if (tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) != 0) continue;
+      const bool streams = tb_all.t[t].R * D * 4 > kStreamTableBytes;
+      if (streams != (pass == 0)) continue;
+      TableDesc &d = tb.t[tb.num_tables];
+      d = tb_all.t[t];
+      d.lookup_base = (uint32_t)n;
+      tb.row_base[tb.num_tables++] = rows_l;
+      rows_l += (uint64_t)d.R;
+      n += (uint64_t)B * d.L;
+    }
+    if (pass == 0) n_stream = n;
   }
   tb.row_base[tb.num_tables] = rows_l;
   const int64_t rows = (int64_t)rows_l;
@@ -747,11 +770,11 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
   if (n == 0) return FFEMB_OK;
   if (wide_keys(rows)) {
     return mode == APPLY_SGD
-               ? dispatch_g<uint64_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage)
-               : dispatch_g<uint64_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage);
+               ? dispatch_g<uint64_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream)
+               : dispatch_g<uint64_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream);
   }
-  return mode == APPLY_SGD ? dispatch_g<uint32_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage)
-                           : dispatch_g<uint32_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage);
+  return mode == APPLY_SGD ? dispatch_g<uint32_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream)
+                           : dispatch_g<uint32_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream);
 }
 
 // ---- the atomic comparison: reference-equivalent unordered scatter ---------------------------

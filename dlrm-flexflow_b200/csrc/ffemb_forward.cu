@@ -35,6 +35,23 @@ __device__ __forceinline__ void f4_div(float4 &a, float d) {
 __device__ __forceinline__ void f4_mul(float4 &a, float m) {
   a.x *= m; a.y *= m; a.z *= m; a.w *= m;
 }
+// a / d exactly as IEEE division rounds it, without the division subroutine on the common path
+// (the reference divides the accumulator inside the bag loop, embedding.cu:186 — one division per
+// lookup and element).  d = bag width, r = RN(1/d).
+//   d a power of two : r is exact and a*r is the correctly rounded quotient, denormal results included;
+//   else             : Markstein's exact-residual correction (div_rn), valid while the residual
+//                      a - d*q does not underflow, i.e. |a| >= 2^-100; smaller non-zero values take
+//                      the IEEE division (a rare, well-predicted branch).
+__device__ __forceinline__ float avg_div(float a, float d, float r, bool pow2) {
+  if (pow2) return a * r;
+  float q = div_rn(a, d, r);
+  if (fabsf(a) < 7.9e-31f) q = a / d;
+  return q;
+}
+__device__ __forceinline__ void f4_avg_div(float4 &a, float d, float r, bool pow2) {
+  a.x = avg_div(a.x, d, r, pow2); a.y = avg_div(a.y, d, r, pow2);
+  a.z = avg_div(a.z, d, r, pow2); a.w = avg_div(a.w, d, r, pow2);
+}
 
 // ---- the vector path ---------------------------------------------------------------------
 // A slot of G lanes owns `bps` consecutive bags of one table = a contiguous run of bps*L
@@ -74,6 +91,8 @@ __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const f
   static_assert(CH % UNR == 0 && NG % 2 == 0, "group pipeline needs an even number of groups");
   const int D4 = D >> 2;
   const float Lf = (float)L;
+  const float Lr = __frcp_rn(Lf);
+  const bool Lpow2 = (L & (L - 1)) == 0;
   bool own[C];  // does this lane hold fragment c of the row?
 #pragma unroll
   for (int c = 0; c < C; c++) own[c] = FULL || (sl + c * G < D4);
@@ -130,7 +149,10 @@ __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const f
     for (int u = 0; u < UNR; u++) {
       if (base + grp * UNR + u < nl) {
 #pragma unroll
-        for (int c = 0; c < C; c++) f4_add(acc[c], v[bf][u][c]);
+        for (int c = 0; c < C; c++) {
+          f4_add(acc[c], v[bf][u][c]);
+          if (AG == AG_AVG) f4_avg_div(acc[c], Lf, Lr, Lpow2);  // the in-loop divide of embedding.cu:186
+        }
         if (--rem == 0) {  // last lookup of the bag: store the pooled row
 #pragma unroll
           for (int c = 0; c < C; c++) {
@@ -175,16 +197,21 @@ __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const f
 template <int G, int C, int AG, int UNR, bool FULL, bool EXCH>
 __global__ void __launch_bounds__(kThreads, C >= 2 ? 2 : 4)
 fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, int64_t stream_bytes,
-           const __grid_constant__ OutMap om) {
-  static_assert(AG != AG_AVG, "the in-loop divide lives in fwd_avg_kernel");
+           const __grid_constant__ OutMap om, uint32_t pmul) {
   constexpr int SLOTS = 32 / G;
+  // Work item of this CTA.  The flat grid lists the tables one after the other; CTAs are handed
+  // their item through a multiplicative permutation (pmul coprime with the grid size, about
+  // 0.618 x grid) so that every wave of resident CTAs is a near-uniform mix of ALL tables: the
+  // HBM-bound gathers (tables >> L2), the L2-bound ones (tables resident in L2) and the L1-bound
+  // ones (tables of a few rows) then overlap instead of running one regime after the other.
+  const uint32_t vb = (uint32_t)(((uint64_t)blockIdx.x * pmul) % gridDim.x);
   // which table does this CTA work on?  cta_base is ascending, <= 65 entries
   int t = 0;
   {
     int lo = 0, hi = tb.num_tables - 1;
     while (lo < hi) {
       const int mid = (lo + hi + 1) >> 1;
-      if (tb.cta_base[mid] <= blockIdx.x) lo = mid; else hi = mid - 1;
+      if (tb.cta_base[mid] <= vb) lo = mid; else hi = mid - 1;
     }
     t = lo;
   }
@@ -193,7 +220,7 @@ fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, 
   const int bps = fwd_bags_per_slot(L, target);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int sub = lane / G, sl = lane % G;
-  const int64_t slot = ((int64_t)(blockIdx.x - tb.cta_base[t]) * (kThreads / 32) + warp) * SLOTS + sub;
+  const int64_t slot = ((int64_t)(vb - tb.cta_base[t]) * (kThreads / 32) + warp) * SLOTS + sub;
   const int64_t bag0 = slot * bps;
   const int nb = bag0 < B ? (int)min((int64_t)bps, B - bag0) : 0;
   float *op = (nb > 0 ? out_row(td, om, bag0, D) : td.out) + 4 * sl;
@@ -312,19 +339,35 @@ static void launch_vec2(const TableBatch &tb, int D, int64_t B, int ag, int targ
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
   int64_t stream_bytes = kStreamBytes;
   if (const char *e = getenv("FFEMB_STREAM_MB")) stream_bytes = atoll(e) << 20;  // tuning aid
+  // CTA -> work item permutation: odd-ish multiplier near the golden ratio of the grid, coprime with it
+  uint32_t pmul = 1;
+  bool perm = tb.num_tables > 1;
+  if (const char *e = getenv("FFEMB_FWD_PERM")) perm = atoi(e) != 0;  // tuning aid
+  if (perm && ctas > 2) {
+    auto gcd = [](uint32_t a, uint32_t b) { while (b) { const uint32_t r = a % b; a = b; b = r; } return a; };
+    pmul = (uint32_t)((double)ctas * 0.6180339887) | 1u;
+    while (gcd(pmul, ctas) != 1) pmul += 2;
+    pmul %= ctas;
+  }
   if (om.npeers == 0) {
-    if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om);
-    else fwd_kernel<G, C, AG_MEAN, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om);
+    if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
+    else if (ag == AG_AVG) fwd_kernel<G, C, AG_AVG, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
+    else fwd_kernel<G, C, AG_MEAN, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
   } else {
-    if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om);
-    else fwd_kernel<G, C, AG_MEAN, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om);
+    if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
+    else if (ag == AG_AVG) fwd_kernel<G, C, AG_AVG, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
+    else fwd_kernel<G, C, AG_MEAN, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
   }
 }
 
 template <int G, int C>
 static void launch_vec(const TableBatch &tb_in, int D, int64_t B, int ag, const OutMap &om, cudaStream_t s) {
   constexpr int SLOTS = 32 / G;
-  if (ag == AG_AVG) {
+  // AVG-literal: the pipelined kernel with the in-loop divide done by avg_div; the one-bag-per-slot
+  // kernel with the IEEE division subroutine is kept as the measured comparison (FFEMB_FWD_AVG_DIV=1)
+  bool avg_old = false;
+  if (const char *e = getenv("FFEMB_FWD_AVG_DIV")) avg_old = atoi(e) != 0;
+  if (ag == AG_AVG && avg_old) {
     const int64_t per_cta = (int64_t)(kThreads / 32) * SLOTS;
     dim3 grid((unsigned)((B + per_cta - 1) / per_cta), tb_in.num_tables);
     fwd_avg_kernel<G, C, AG_AVG><<<grid, kThreads, 0, s>>>(tb_in, D, B, om);

@@ -30,7 +30,7 @@ template <typename K, int G, int MODE, bool AVG, int S>
 __global__ void __launch_bounds__(L1Threads<G>::value)
 reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
                     const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
-                    float *rows_out) {
+                    float *rows_out, uint32_t split) {
   constexpr int THREADS = L1Threads<G>::value;
   constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
   constexpr K INV = KeyTraits<K>::INV;
@@ -41,7 +41,7 @@ reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__
   // (conflict-free); a lane only ever reads back what it copied itself
   float4 *ring = reinterpret_cast<float4 *>(smem_raw + sizeof(EntryDesc) * WARPS * EPW) +
                  (size_t)warp * S * 2 * 32 + lane;
-  const int64_t wbase = ((int64_t)blockIdx.x * WARPS + warp) * EPW;
+  const int64_t wbase = ((int64_t)mix_cta(blockIdx.x, gridDim.x, split) * WARPS + warp) * EPW;
   if (wbase >= n) return;  // warp-uniform
   const int D4 = D >> 2;
 

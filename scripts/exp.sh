@@ -1,5 +1,10 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-B="python bench.py --steps 20 --warmup 5 --no-e2e --no-cpu --no-overlap"
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+B="python bench.py --steps 20 --warmup 5 --no-e2e --no-cpu"
 ph() { python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', round(d['ms_per_step'],3), d['roofline']['phases_ms_per_step'])"; }
-$B | ph cfg3
-ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -k regex:"bwd_tiny|bwd_small|small_apply" -c 3 --csv python bench.py --rows-cap 4000000 --steps 2 --warmup 1 --no-e2e --no-cpu 2>/dev/null | grep -E "bwd_|small_apply" | awk -F'","' '{print $5, $(NF-1), $NF}'
+$B | ph cfg3-new
+$B --no-overlap | ph cfg3-new-nooverlap
+FFEMB_FWD_PERM=0 $B --no-overlap | ph cfg3-noperm-nooverlap
+FFEMB_R1_MIX=0 $B --no-overlap | ph cfg3-nomix-nooverlap
+FFEMB_FWD_PERM=0 FFEMB_R1_MIX=0 $B | ph cfg3-old
+$B --workload 5 --steps 5 --warmup 2 | ph cfg5-new
+FFEMB_FWD_AVG_DIV=1 $B --workload 5 --steps 5 --warmup 2 | ph cfg5-olddiv

@@ -66,6 +66,24 @@ def test_forward_bit_exact_vs_oracle(ffemb, oracle, torch_cuda, R, D, L, B, aggr
     assert np.array_equal(out.cpu().numpy(), oracle.forward(idx, W, aggr))
 
 
+@pytest.mark.parametrize("L", [3, 7, 64])
+@pytest.mark.parametrize("scale", [1e-38, 1e-33, 1e-28, 1e30])
+def test_forward_avg_literal_division_edge_ranges(ffemb, oracle, torch_cuda, L, scale):
+    """AGGR_MODE_AVG divides inside the bag loop (embedding.cu:186).  The kernel replaces the IEEE
+    division by an exact-residual correction that is only valid for |a| >= 2^-100 and falls back
+    to the division below that: denormal / tiny / huge accumulators must still be bit-exact."""
+    torch = torch_cuda
+    R, D, B = 200, 64, 300
+    W, idx, _ = make_inputs(R, D, L, B, seed=L)
+    W = (W.astype(np.float64) / np.abs(W).max() * scale).astype(np.float32)
+    W[1] = 0.0
+    W[2, ::2] = -0.0
+    op = ffemb.Embedding(R, D, 22)
+    out = op.forward(dev(torch, idx), dev(torch, W))
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), oracle.forward(idx, W, 22).view(np.uint32))
+
+
 def test_forward_golden_reference_cpu(ffemb, torch_cuda):
     """Against the reference's own CPU tasks (tests/golden/ref_cpu.npz)."""
     torch = torch_cuda
@@ -240,6 +258,35 @@ def test_backward_batched_ragged_tables(ffemb, oracle, torch_cuda, D, B):
             exact = Ws[t].astype(np.float64) - 0.01 * oracle.backward_dense_f64(idxs[t], gs[t], R, aggr)
             assert np.array_equal(got[cnt <= 1], want[cnt <= 1]), t
             assert np.all(np.abs(got - exact) <= table_tol(Ws[t]) * np.maximum(1, np.sqrt(cnt))[:, None]), t
+
+
+def test_backward_streaming_and_resident_tables_interleaved(ffemb, oracle, torch_cuda):
+    """Tables far larger than L2 (> 64 MB) are keyed first and their level-1 tiles are handed out
+    interleaved with the L2-resident tables' (mix_cta): same results as table by table, and the
+    batched call stays bit-identical to per-table calls on single-lookup rows."""
+    torch = torch_cuda
+    D, B = 128, 3000
+    rows, bags = [2000, 140000, 977, 135000, 64], [5, 2, 9, 1, 3]   # 140000*512 B = 72 MB > 64 MB
+    Ws, idxs, gs = [], [], []
+    for t, (R, L) in enumerate(zip(rows, bags)):
+        W, idx, g = make_inputs(R, D, L, B, seed=400 + t)
+        Ws.append(W), idxs.append(idx), gs.append(g)
+    dWs = [dev(torch, w) for w in Ws]
+    coll = ffemb.EmbeddingCollection(dWs, bags, 21)
+    coll.backward_sgd([dev(torch, i) for i in idxs], [dev(torch, g) for g in gs], 0.01)
+    torch.cuda.synchronize()
+    for t, R in enumerate(rows):
+        got = dWs[t].cpu().numpy()
+        cnt = np.bincount(idxs[t].reshape(-1), minlength=R)
+        want = oracle.reference_step(idxs[t], gs[t], Ws[t], 21, lr=0.01)
+        exact = Ws[t].astype(np.float64) - 0.01 * oracle.backward_dense_f64(idxs[t], gs[t], R, 21)
+        assert np.array_equal(got[cnt <= 1], want[cnt <= 1]), t
+        assert np.all(np.abs(got - exact) <= table_tol(Ws[t]) * np.maximum(1, np.sqrt(cnt))[:, None]), t
+        single = [dev(torch, Ws[t])]
+        ffemb.EmbeddingCollection(single, [bags[t]], 21).backward_sgd([dev(torch, idxs[t])], [dev(torch, gs[t])], 0.01)
+        alone = single[0].cpu().numpy()
+        assert np.array_equal(alone[cnt <= 1], got[cnt <= 1]), t
+        assert np.all(np.abs(alone - got) <= REL_TOL * np.abs(got).max()), t   # repeated rows: tile cuts differ
 
 
 def test_backward_split_in_prepare_and_apply_is_bit_identical(ffemb, torch_cuda):
