@@ -197,7 +197,7 @@ __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const f
 template <int G, int C, int AG, int UNR, bool FULL, bool EXCH>
 __global__ void __launch_bounds__(kThreads, C >= 2 ? 2 : 4)
 fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, int64_t stream_bytes,
-           const __grid_constant__ OutMap om, uint32_t pmul) {
+           const __grid_constant__ OutMap om, uint32_t pmul, int64_t l1_bytes) {
   constexpr int SLOTS = 32 / G;
   // Work item of this CTA.  The flat grid lists the tables one after the other; CTAs are handed
   // their item through a multiplicative permutation (pmul coprime with the grid size, about
@@ -240,7 +240,7 @@ fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, 
   const float *W = td.table + 4 * sl;
   const int64_t bytes = td.R * (int64_t)D * 4;
   const uint64_t pol_rows = bytes > stream_bytes ? pol_stream : policy_evict_normal();
-  if (td.R > 0 && bytes <= kL1Bytes)
+  if (td.R > 0 && bytes <= l1_bytes)
     fwd_slot<G, C, AG, UNR, FULL, true, EXCH>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream, om, bag0, td.lookup_base);
   else
     fwd_slot<G, C, AG, UNR, FULL, false, EXCH>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream, om, bag0, td.lookup_base);
@@ -339,6 +339,8 @@ static void launch_vec2(const TableBatch &tb, int D, int64_t B, int ag, int targ
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
   int64_t stream_bytes = kStreamBytes;
   if (const char *e = getenv("FFEMB_STREAM_MB")) stream_bytes = atoll(e) << 20;  // tuning aid
+  int64_t l1_bytes = kL1Bytes;
+  if (const char *e = getenv("FFEMB_L1_KB")) l1_bytes = atoll(e) << 10;  // tuning aid
   // CTA -> work item permutation: odd-ish multiplier near the golden ratio of the grid, coprime with it
   uint32_t pmul = 1;
   bool perm = tb.num_tables > 1;
@@ -350,13 +352,13 @@ static void launch_vec2(const TableBatch &tb, int D, int64_t B, int ag, int targ
     pmul %= ctas;
   }
   if (om.npeers == 0) {
-    if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
-    else if (ag == AG_AVG) fwd_kernel<G, C, AG_AVG, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
-    else fwd_kernel<G, C, AG_MEAN, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
+    if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
+    else if (ag == AG_AVG) fwd_kernel<G, C, AG_AVG, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
+    else fwd_kernel<G, C, AG_MEAN, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
   } else {
-    if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
-    else if (ag == AG_AVG) fwd_kernel<G, C, AG_AVG, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
-    else fwd_kernel<G, C, AG_MEAN, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul);
+    if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
+    else if (ag == AG_AVG) fwd_kernel<G, C, AG_AVG, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
+    else fwd_kernel<G, C, AG_MEAN, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
   }
 }
 

@@ -335,6 +335,42 @@ def test_host_step_matches_device_step(ffemb, oracle, torch_cuda):
         assert torch.equal(a[t], b[t]), t
 
 
+def test_host_steps_in_flight_together_match_sequential_steps(ffemb, oracle, torch_cuda):
+    """HostStep.submit / wait: four steps with different batches, two in flight at any time (device
+    buffers double buffered) == the same four steps one after the other on the device, bit for bit;
+    every step's pooled outputs are those of the table state it ran on."""
+    torch = torch_cuda
+    rows, bags, D, B, K = [7, 30000, 977], [2, 3, 9], 64, 5000, 4
+    Ws, idxs, gs = [], [], []
+    for t, (R, L) in enumerate(zip(rows, bags)):
+        W = make_inputs(R, D, L, B, seed=500 + t)[0]
+        Ws.append(W)
+        idxs.append([make_inputs(R, D, L, B, seed=600 + 10 * k + t)[1] for k in range(K)])
+        gs.append([make_inputs(R, D, L, B, seed=700 + 10 * k + t)[2] for k in range(K)])
+    a = [dev(torch, w) for w in Ws]
+    ca = ffemb.EmbeddingCollection(a, bags)
+    seq_out = []
+    for k in range(K):
+        di = [dev(torch, idxs[t][k]) for t in range(len(rows))]
+        seq_out.append([o.cpu().numpy() for o in ca.forward(di)])
+        ca.backward_sgd(di, [dev(torch, gs[t][k]) for t in range(len(rows))], 0.01)
+    b = [dev(torch, w) for w in Ws]
+    hs = ffemb.HostStep(ffemb.EmbeddingCollection(b, bags), B)
+    assert hs.depth == 2
+    h_idx = [[torch.from_numpy(idxs[t][k]).pin_memory() for t in range(len(rows))] for k in range(K)]
+    h_g = [[torch.from_numpy(gs[t][k]).pin_memory() for t in range(len(rows))] for k in range(K)]
+    h_out = [[torch.empty((B, D)).pin_memory() for _ in rows] for k in range(K)]
+    tickets = [hs.submit(h_idx[k], h_g[k], h_out[k], 0.01) for k in range(K)]
+    for k in tickets:
+        hs.wait(k)
+    for k in range(K):
+        for t in range(len(rows)):
+            assert np.array_equal(h_out[k][t].numpy(), seq_out[k][t]), (k, t)
+    for t in range(len(rows)):
+        assert torch.equal(a[t], b[t]), t
+    assert np.array_equal(seq_out[0][1], oracle.forward(idxs[1][0], Ws[1]))
+
+
 def test_linearity_and_roundtrip_at_full_size(ffemb, torch_cuda):
     """Size-independent properties at BASELINE config-2 scale (26 tables, D=16, B=16384) without
     the CPU oracle: (1) forward of bag-1 indices is a pure gather; (2) with lr = 1 and
