@@ -94,6 +94,7 @@ def lib():
     L.ffemb_backward_workspace.argtypes = [i64, i64, i64]
     L.ffemb_backward_workspace.restype = sz
     L.ffemb_backward_path.argtypes = [i64, i64, i64, i64]
+    L.ffemb_load_sparse_inputs.argtypes = [tp, i32, vp, i64, vp, i64, i64, vp]
     L.ffemb_check_indices.argtypes = [vp, i64, i64, vp, vp]
     L.ffemb_profile_enable.argtypes = [i32]
     L.ffemb_profile_collect.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_int64)]
@@ -105,7 +106,7 @@ def lib():
     return L
 
 
-PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small", "exchange"]
+PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small", "exchange", "input"]
 
 
 def profile_enable(on=True):

@@ -103,6 +103,7 @@ static int pack(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t 
     }
   }
   tb.row_base[num_tables] = rows;
+  tb.og_stride = D;
   return FFEMB_OK;
 }
 
@@ -325,6 +326,26 @@ int ffemb_backward_path(int64_t R, int64_t L, int64_t D, int64_t B) { return bac
 
 size_t ffemb_backward_workspace(int64_t num_lookups, int64_t total_rows, int64_t D) {
   return backward_workspace_bytes(num_lookups, total_rows, D);
+}
+
+int ffemb_load_sparse_inputs(const ffemb_table_t *tables, int num_tables, const int64_t *full,
+                             int64_t row_len, const int32_t *sample_ids, int64_t first_sample,
+                             int64_t B, ffemb_stream_t stream) {
+  if (!tables || num_tables < 0 || num_tables > FFEMB_MAX_TABLES || row_len <= 0 || row_len >= (1ll << 31) ||
+      B < 0 || first_sample < 0 || (B > 0 && !full)) {
+    set_error("load_sparse_inputs: invalid arguments (tables=%p num_tables=%d row_len=%lld B=%lld)",
+              (const void *)tables, num_tables, (long long)row_len, (long long)B);
+    return FFEMB_EINVAL;
+  }
+  for (int t = 0; t < num_tables; t++) {
+    const ffemb_table_t &x = tables[t];
+    if (x.L < 0 || x.reserved < 0 || (int64_t)x.reserved + x.L > row_len || (B > 0 && x.L > 0 && !x.idx)) {
+      set_error("load_sparse_inputs: table %d: columns [%d, %d) outside a row of %lld, or no destination", t,
+                x.reserved, x.reserved + x.L, (long long)row_len);
+      return FFEMB_EINVAL;
+    }
+  }
+  return launch_load_sparse(tables, num_tables, full, row_len, sample_ids, first_sample, B, (cudaStream_t)stream);
 }
 
 int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int64_t *bad_count,

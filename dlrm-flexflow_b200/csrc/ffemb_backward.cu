@@ -152,7 +152,7 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
           if (LEVEL1) {
             const uint32_t t = ev / B;
             const uint32_t b = ev - t * B;
-            gp = tb.t[t].out + (int64_t)b * D;
+            gp = tb.t[t].out + (int64_t)b * tb.og_stride;
             if (aggr != FFEMB_AGGR_SUM) scale[u] = (float)tb.t[t].L;
             if (eend[u]) wp[u] = tb.t[t].table + (int64_t)(ek[u] - tb.row_base[t]) * D;
           } else {
@@ -300,7 +300,7 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
       const uint32_t v = vals[p];
       const bool is_end = (p + 1 == n) || (keys[p + 1] != k);
       const uint32_t t = v >> BAG_BITS, b = v & BAG_MASK;
-      d.gp = tb.t[t].out + (int64_t)b * D;
+      d.gp = tb.t[t].out + (int64_t)b * tb.og_stride;
       if (is_end) d.wp = tb.t[t].table + (int64_t)((uint64_t)k - tb.row_base[t]) * D;
       if ((flags & 1) && is_end) prefetch_l2_bulk(d.wp, D * 4);
       if (flags & 2) prefetch_l2_bulk(d.gp, D * 4);
@@ -647,10 +647,12 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     auto go = [&](auto kern, size_t sm) {
       kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], flags, split);
     };
-    // gathers that hit L2 (the usual case): the cp.async ring variant, 4 entries ahead (measured on
-    // cfg3: 1.36 -> 1.22 ms; 8 stages: 1.26); gathers that miss (pipe): the register-pipelined one
-    // (cfg5: 13.9 ms against 14.6 for the ring).  FFEMB_R1_RING=0|4|8 overrides (tuning aid).
-    int ring = pipe ? 0 : 4;
+    // D <= 128: the cp.async ring variant, 4 entries ahead (measured: cfg3 1.36 -> 1.22 ms against the
+    // register double buffer; cfg5, whose gathers miss L2, 11.4 ms against 14.5 for the register-
+    // pipelined variant and 14.2 for an 8-deep ring).  D > 128 (several fragments per lane): the
+    // register variants — pipelined when one table's output-grad exceeds L2 (gathers miss), lean
+    // otherwise.  FFEMB_R1_RING=0|4|8 / FFEMB_R1_PIPE override (tuning aids).
+    int ring = 4;
     if (const char *e = getenv("FFEMB_R1_RING")) ring = atoi(e);
     if (C == 1 && ring > 0) {
       auto gor = [&](auto kern, int S) {
@@ -735,6 +737,7 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
   TableBatch tb, ts;
   memset(&tb, 0, sizeof(tb));
   memset(&ts, 0, sizeof(ts));
+  tb.og_stride = ts.og_stride = tb_all.og_stride;
   int n_tiny = 0;
   for (int pass = 1; pass <= 2; pass++) {  // tiny tables first, then small ones
     for (int t = 0; t < tb_all.num_tables; t++) {
@@ -796,7 +799,7 @@ bwd_atomic_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int a
   for (int c = 0; c < C; c++) {
     g[c] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (sl + c * G < D4) {
-      g[c] = ldg_row(td.out + b * (int64_t)D + 4 * (sl + c * G));
+      g[c] = ldg_row(td.out + b * tb.og_stride + 4 * (sl + c * G));
       if (aggr != FFEMB_AGGR_SUM) g[c] = f4_div(g[c], (float)L);
     }
   }
@@ -823,7 +826,7 @@ bwd_atomic_generic_kernel(const __grid_constant__ TableBatch tb, int D, int64_t 
   const int64_t bag = (int64_t)blockIdx.x * (kThreads / 32) + warp;
   if (bag >= B) return;
   for (int d = lane; d < D; d += 32) {
-    float g = td.out[bag * (int64_t)D + d];
+    float g = td.out[bag * tb.og_stride + d];
     if (aggr != FFEMB_AGGR_SUM) g = g / (float)L;
     for (int j = 0; j < L; j++)
       atomicAdd(td.table + __ldg(td.idx + bag * (int64_t)L + j) * (int64_t)D + d, g);

@@ -94,15 +94,24 @@ struct ChunkStage {
   int64_t *is;         // [2][chb][L]
   int64_t b0, b1;      // bag range of this CTA
   int chb, D, L, nthreads;
+  int64_t ogs;         // floats between consecutive output-grad rows (D, or the Concat row width)
   __device__ __forceinline__ int bags(int k) const {
     return (int)min((int64_t)chb, b1 - (b0 + (int64_t)k * chb));
   }
   __device__ __forceinline__ void issue(int k, int buf) const {
     const int64_t bb = b0 + (int64_t)k * chb;
     const int nb = bags(k);
-    const float *gsrc = g + bb * (int64_t)D;
+    const float *gsrc = g + bb * ogs;
     float *gdst = gs + (size_t)buf * chb * D;
-    for (int i = threadIdx.x; i < nb * (D >> 2); i += nthreads) cp_async16(gdst + 4 * i, gsrc + 4 * i);
+    if (ogs == D) {  // plain [B][D] buffer: one contiguous stretch
+      for (int i = threadIdx.x; i < nb * (D >> 2); i += nthreads) cp_async16(gdst + 4 * i, gsrc + 4 * i);
+    } else {         // column block of a wider matrix: D contiguous floats per row
+      const int D4 = D >> 2;
+      for (int i = threadIdx.x; i < nb * D4; i += nthreads) {
+        const int r = i / D4, c4 = i - r * D4;
+        cp_async16(gdst + 4 * i, gsrc + r * ogs + 4 * c4);
+      }
+    }
     const int64_t *isrc = idx + bb * (int64_t)L;
     int64_t *idst = is + (size_t)buf * chb * L;
     for (int i = threadIdx.x; i < nb * L; i += nthreads) cp_async8(idst + i, isrc + i);
@@ -132,7 +141,7 @@ bwd_tiny_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, float *
   const bool own = sl < (D >> 2);
   const float Lf = (float)L, Linv = __frcp_rn(Lf);
   ChunkStage st;
-  st.g = td.out; st.idx = td.idx; st.D = D; st.L = L; st.chb = kTinyChunk; st.nthreads = kTinyThreads;
+  st.g = td.out; st.idx = td.idx; st.D = D; st.L = L; st.ogs = tb.og_stride; st.chb = kTinyChunk; st.nthreads = kTinyThreads;
   st.b0 = c * bpc; st.b1 = min(B, st.b0 + bpc);
   st.gs = reinterpret_cast<float *>(smem_raw);
   st.is = reinterpret_cast<int64_t *>(st.gs + 2 * kTinyChunk * D);
@@ -236,7 +245,7 @@ bwd_small_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, float 
   const float Lf = (float)L, Linv = __frcp_rn(Lf);
   const uint32_t magic = (uint32_t)((0x100000000ull + (uint32_t)L - 1) / (uint32_t)L);  // e / L, e < 2^16
   ChunkStage st;
-  st.g = td.out; st.idx = td.idx; st.D = D; st.L = L; st.chb = small_chunk_bags(L); st.nthreads = kSmallThreads;
+  st.g = td.out; st.idx = td.idx; st.D = D; st.L = L; st.ogs = tb.og_stride; st.chb = small_chunk_bags(L); st.nthreads = kSmallThreads;
   st.b0 = c * bpc; st.b1 = min(B, st.b0 + bpc);
   float *acc = reinterpret_cast<float *>(smem_raw);                         // [R][D]
   st.gs = acc + (size_t)R * D;                                              // [2][chb][D]

@@ -38,6 +38,10 @@ struct TableBatch {
   uint64_t row_base[FFEMB_MAX_TABLES + 1];  // first global row id of each table (bwd keys)
   uint32_t cta_base[FFEMB_MAX_TABLES + 1];  // first CTA of each table in the flat forward grid
   int32_t num_tables;
+  // floats between consecutive rows of the output-grad buffers (bwd).  D: plain [B][D] buffers;
+  // larger: td.out points at the table's column block inside a wider row-major matrix — the
+  // gradient of the Concat output (ffemb_backward_sgd_concat)
+  int64_t og_stride;
 };
 
 // Where pooled rows go.  npeers == 0: td.out + b*D (plain).  Else the fused exchange: sample b
@@ -76,6 +80,8 @@ enum { STAGE_ALL = 0, STAGE_SORT = 1, STAGE_APPLY = 2 };
 int launch_backward_sorted(const TableBatch &tb, int64_t D, int64_t B, int aggr, float lr,
                            ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s,
                            int stage = STAGE_ALL);
+int launch_load_sparse(const ffemb_table_t *tables, int num_tables, const int64_t *full, int64_t row_len,
+                       const int32_t *sample_ids, int64_t first_sample, int64_t B, cudaStream_t s);
 size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t D);
 // tables whose whole gradient fits on chip (ffemb_backward_small.cu)
 int backward_path(int64_t R, int64_t L, int64_t D, int64_t B);  // 0 sorted, 1 tiny, 2 small

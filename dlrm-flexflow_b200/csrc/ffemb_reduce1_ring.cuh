@@ -58,7 +58,7 @@ reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__
       const uint32_t v = vals[p];
       const bool is_end = (p + 1 == n) || (keys[p + 1] != k);
       const uint32_t t = v >> BAG_BITS, b = v & BAG_MASK;
-      d.gp = tb.t[t].out + (int64_t)b * D;
+      d.gp = tb.t[t].out + (int64_t)b * tb.og_stride;
       if (is_end) d.wp = tb.t[t].table + (int64_t)((uint64_t)k - tb.row_base[t]) * D;
     }
     wd[e] = d;

@@ -219,3 +219,38 @@ class EmbeddingCollection:
             sub = C.cast(C.byref(arr, s * C.sizeof(ffemb_table_t)), C.POINTER(ffemb_table_t))
             check(lib().ffemb_backward_dense_batched(sub, e - s, self.dim, batch, self.aggr,
                                                      ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
+
+
+def load_sparse_inputs(full, bags, batch, first_sample=0, sample_ids=None, cols=None, outs=None, stream=None):
+    """DataLoader::load_sparse_input for ALL tables in one launch
+    (/root/reference/examples/cpp/DLRM/dlrm.cu:19-58, dlrm.cc:482-520; ffemb_load_sparse_inputs).
+
+    full: int64 [num_samples][row_len] — a CUDA tensor, or a pinned CPU tensor (the reference keeps
+    the dataset in zero-copy host memory; the kernel then reads it over PCIe itself).
+    bags[t]: bag width of table t; cols[t]: first column of its block (default: blocks back to back,
+    the reference's my_input_idx * in_dim).  Returns the per-table [batch][L] CUDA index tensors."""
+    if full.dtype != torch.int64 or full.dim() != 2 or not full.is_contiguous():
+        raise ValueError("full must be a contiguous int64 [num_samples][row_len] tensor")
+    if not full.is_cuda and not full.is_pinned():
+        raise ValueError("a host-side dataset must be pinned (zero-copy) memory")
+    dev = torch.device("cuda", torch.cuda.current_device()) if not full.is_cuda else full.device
+    T = len(bags)
+    if cols is None:
+        cols, c = [], 0
+        for l in bags:
+            cols.append(c)
+            c += int(l)
+    if outs is None:
+        outs = [torch.empty((batch, int(l)), dtype=torch.int64, device=dev) for l in bags]
+    arr = (ffemb_table_t * T)()
+    for t in range(T):
+        arr[t].idx, arr[t].L, arr[t].reserved = outs[t].data_ptr(), int(bags[t]), int(cols[t])
+    ids = None
+    if sample_ids is not None:
+        ids = _req(sample_ids, torch.int32, "sample_ids").data_ptr()
+    for s in range(0, T, B.FFEMB_MAX_TABLES):
+        e = min(T, s + B.FFEMB_MAX_TABLES)
+        sub = C.cast(C.byref(arr, s * C.sizeof(ffemb_table_t)), C.POINTER(ffemb_table_t))
+        check(lib().ffemb_load_sparse_inputs(sub, e - s, full.data_ptr(), int(full.shape[1]), ids,
+                                             int(first_sample), int(batch), _stream_ptr(stream)))
+    return outs

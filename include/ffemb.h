@@ -189,6 +189,25 @@ FFEMB_API size_t ffemb_backward_workspace(int64_t num_lookups, int64_t total_row
  * accumulators), 2 = "small" (whole [R][D] gradient in shared memory).  All are deterministic.  */
 FFEMB_API int ffemb_backward_path(int64_t R, int64_t L, int64_t D, int64_t B);
 
+/* ---- sparse-input delivery: replaces DataLoader::load_sparse_input ------------------------
+ * examples/cpp/DLRM/dlrm.cu:19-58, run by the reference once per table and step
+ * (DataLoader::next_batch, examples/cpp/DLRM/dlrm.cc:482-520): a pinned staging allocation, a host
+ * gather loop, a synchronous cudaMemcpy, cudaFreeHost and cudaDeviceSynchronize.  Here ONE launch
+ * cuts the index batches of all tables out of the sample-major dataset
+ *     full[sample][row_len]  (int64; the reference's full_sparse_input, `row_len` =
+ *                             num_sparse_inputs * in_dim there)
+ * `full` is any device-accessible pointer: device memory, or the reference's own placement —
+ * zero-copy (mapped pinned) host memory, dlrm.cc:505-509 — which the kernel then reads over PCIe
+ * itself, coalesced.  Batch sample i is dataset row sample_ids[i] (device-accessible int32, the
+ * reference's SampleIdxs::idxs, examples/cpp/DLRM/dlrm.h:17-21), or first_sample + i when
+ * sample_ids is NULL (the reference only ever fills consecutive ids, dlrm.cc:497-498).
+ * Per table: tables[t].idx = DESTINATION [B][L] (written), tables[t].L = bag width (in_dim),
+ * tables[t].reserved = first column of the table's block inside a sample row (the reference's
+ * my_input_idx * in_dim); out / table / R are ignored.  Column blocks must not overlap.        */
+FFEMB_API int ffemb_load_sparse_inputs(const ffemb_table_t *tables, int num_tables, const int64_t *full,
+                             int64_t row_len, const int32_t *sample_ids, int64_t first_sample,
+                             int64_t B, ffemb_stream_t stream);
+
 /* ---- debug aid (not on the timed path) -----------------------------------------------------
  * Writes the number of indices outside [0, R) to *bad_count (device int64).                   */
 FFEMB_API int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int64_t *bad_count,
@@ -209,7 +228,8 @@ FFEMB_API int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int6
 #define FFEMB_PHASE_ATOMIC 5    /* atomic comparison backward */
 #define FFEMB_PHASE_SMALL 6     /* bag-major backward of tables whose gradient fits on chip */
 #define FFEMB_PHASE_EXCHANGE 7  /* output-grad push over peer memory */
-#define FFEMB_NUM_PHASES 8
+#define FFEMB_PHASE_INPUT 8     /* sparse-input delivery (ffemb_load_sparse_inputs) */
+#define FFEMB_NUM_PHASES 9
 FFEMB_API int ffemb_profile_enable(int on);
 FFEMB_API int ffemb_profile_collect(float *ms_per_phase, int64_t *launches_per_phase);
 FFEMB_API int64_t ffemb_launch_count(void);

@@ -233,6 +233,22 @@ void oracle_concat_backward(const float *out_grad, float *const *in_grads,
   }
 }
 
+/* ---- DataLoader::load_sparse_input: examples/cpp/DLRM/dlrm.cu:19-58 (the host loop :38-45) ----
+ * batch[i*in_dim + j] = full[idxs[i] * num_sparse_inputs*in_dim + my_input_idx*in_dim + j], generalised
+ * to a per-table column block [col, col + width) of a sample row of row_len int64 (the reference
+ * has col = my_input_idx*in_dim, width = in_dim, row_len = num_sparse_inputs*in_dim); idxs == NULL
+ * means the consecutive ids first_sample + i that DataLoader::next_batch fills
+ * (examples/cpp/DLRM/dlrm.cc:497-498).                                                         */
+void oracle_load_sparse_input(const int64_t *full, int64_t row_len, int64_t col, int64_t width,
+                              const int32_t *idxs, int64_t first_sample, int64_t B, int64_t *batch) {
+  for (int64_t i = 0; i < B; i++) {
+    int64_t row = idxs ? (int64_t)idxs[i] : first_sample + i;
+    int64_t full_offset = row * row_len + col;
+    int64_t batch_offset = i * width;
+    for (int64_t j = 0; j < width; j++) batch[batch_offset + j] = full[full_offset + j];
+  }
+}
+
 /* Number of distinct rows touched (U in the algorithmic-bytes formula).
  * Sort-and-count; scratch is allocated here.                                                 */
 static int cmp_i64(const void *a, const void *b) {

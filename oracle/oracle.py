@@ -67,6 +67,8 @@ def lib():
         L.oracle_route_rows.argtypes = [_i64p, _i64, _i64, _i64, _i64p, _i64p, _i64p]
         L.oracle_count_unique.argtypes = [_i64p, _i64]
         L.oracle_count_unique.restype = _i64
+        L.oracle_load_sparse_input.argtypes = [_i64p, _i64, _i64, _i64, C.c_void_p, _i64, _i64, _i64p]
+        L.oracle_load_sparse_input.restype = None
         L.oracle_concat_forward.argtypes = [_f32p, C.POINTER(C.c_void_p), _i64p, _i64, _i64]
         L.oracle_concat_forward.restype = None
         L.oracle_concat_backward.argtypes = [_f32p, C.POINTER(C.c_void_p), _i64p, _i64, _i64]
@@ -160,6 +162,19 @@ def route_rows(idx_flat, R, G):
     local = np.empty(n, np.int64)
     _chk(lib().oracle_route_rows(idx_flat, n, R, G, offsets, perm, local))
     return offsets, perm, local
+
+
+def load_sparse_input(full, col, width, batch, first_sample=0, sample_ids=None):
+    """DataLoader::load_sparse_input (examples/cpp/DLRM/dlrm.cu:19-58): the [batch][width] index
+    tensor of one table cut out of the sample-major dataset full [num_samples][row_len]."""
+    full = np.ascontiguousarray(full, np.int64)
+    out = np.empty((batch, width), np.int64)
+    ids = None
+    if sample_ids is not None:
+        ids = np.ascontiguousarray(sample_ids, np.int32)
+    lib().oracle_load_sparse_input(full, full.shape[1], col, width,
+                                   ids.ctypes.data if ids is not None else None, first_sample, batch, out)
+    return out
 
 
 def count_unique(idx):
@@ -282,6 +297,8 @@ def _bind_gpu(L):
         L.ffref_gpu_sgd_task.restype = None
         L.ffref_gpu_set_workspace.argtypes = [_vp, C.c_size_t]
         L.ffref_gpu_set_workspace.restype = None
+        if hasattr(L, "ffref_gpu_load_sparse_input"):  # not in the drop-in library
+            L.ffref_gpu_load_sparse_input.argtypes = [_vp, _i64, _int, _int, _int, _int, _int, _vp]
     return L
 
 

@@ -18,6 +18,9 @@
  */
 #include "model.h"
 #include "cuda_helper.h"
+#ifndef FFEMB_DROPIN
+#include "dlrm.h" /* examples/cpp/DLRM: DataLoader, SampleIdxs (only in libffref_gpu.so) */
+#endif
 
 #include <cstdio>
 #include <cstdlib>
@@ -185,6 +188,34 @@ void ffref_gpu_backward_kernel(const int64_t *idx, const float *outgrad, float *
   Embedding::backward_kernel(idx, outgrad, Wgrad, L, D, B, (AggrMode)aggr, B * D,
                              (cudaStream_t)stream);
 }
+
+#ifndef FFEMB_DROPIN
+/* DataLoader::load_sparse_input (examples/cpp/DLRM/dlrm.cu:19-58) as DataLoader::next_batch launches
+ * it for table `my_input_idx` (examples/cpp/DLRM/dlrm.cc:482-520): regions[0] = the full dataset
+ * [num_samples][num_sparse_inputs*in_dim] in HOST memory (zero-copy there; the task reads it on the
+ * host), regions[1] = the table's batch input [B][in_dim] in device memory; task->args = the int
+ * hash num_sparse_inputs*MAX_NUM_EMB + my_input_idx; local_args = SampleIdxs with consecutive ids
+ * from first_sample.  B <= MAX_NUM_SAMPLES (65536, dlrm.h:17).                                  */
+int ffref_gpu_load_sparse_input(const int64_t *full_host, int64_t num_samples, int num_sparse_inputs,
+                                int in_dim, int my_input_idx, int first_sample, int B,
+                                int64_t *batch_dev) {
+  if (B > MAX_NUM_SAMPLES) return 1;
+  TaskFrame f;
+  f.add((void *)full_host, (Legion::coord_t)num_sparse_inputs * in_dim, num_samples);
+  f.add((void *)batch_dev, in_dim, B);
+  int hash = num_sparse_inputs * MAX_NUM_EMB + my_input_idx;
+  SampleIdxs *meta = new SampleIdxs;
+  meta->num_samples = B;
+  for (int i = 0; i < B; i++) meta->idxs[i] = first_sample + i;
+  f.task.args = &hash;
+  f.task.arglen = sizeof(hash);
+  f.task.local_args = meta;
+  f.task.local_arglen = sizeof(SampleIdxs);
+  DataLoader::load_sparse_input(&f.task, f.regions, NULL, &f.runtime);
+  delete meta;
+  return 0;
+}
+#endif
 
 /* ZeroInitializer::init_task (src/runtime/initializer_kernel.cu:209-241) over one region —
  * what Op::zero_grad launches on the weight-grad every step (src/runtime/model.cc:466-490).

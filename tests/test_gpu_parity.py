@@ -452,3 +452,60 @@ def test_dropin_task_bodies_match_reference_task_bodies(oracle, torch_cuda, R, D
         a, b = Wours.cpu().numpy(), Wref.cpu().numpy()
         assert np.array_equal(a[single], b[single])
         assert np.all(np.abs(a - b) <= 2 * table_tol(W) * np.maximum(1, np.sqrt(cnt))[:, None])
+
+
+# ---------------------------------------------------------------------------------------------
+# sparse-input delivery: DataLoader::load_sparse_input, all tables in one launch
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("where", ["device", "zero_copy_host"])
+def test_load_sparse_inputs_vs_oracle_ragged(ffemb, oracle, torch_cuda, where):
+    """Ragged bag widths, gaps between column blocks, tables listed out of column order, explicit
+    sample ids — bit-exact against the restated host loop of dlrm.cu:38-45."""
+    torch = torch_cuda
+    rng = np.random.default_rng(7)
+    N, B = 5000, 1777
+    bags, cols, row_len = [3, 1, 20, 1, 7], [40, 0, 5, 39, 26], 50   # columns 1..4, 25, 33..38, 43.. unused
+    full = rng.integers(0, 1 << 40, (N, row_len), dtype=np.int64)
+    tfull = torch.from_numpy(full).cuda() if where == "device" else torch.from_numpy(full).pin_memory()
+    outs = ffemb.load_sparse_inputs(tfull, bags, B, first_sample=1234, cols=cols)
+    torch.cuda.synchronize()
+    for t in range(len(bags)):
+        assert np.array_equal(outs[t].cpu().numpy(), oracle.load_sparse_input(full, cols[t], bags[t], B, 1234)), t
+    ids = rng.permutation(N)[:B].astype(np.int32)
+    outs = ffemb.load_sparse_inputs(tfull, bags, B, sample_ids=torch.from_numpy(ids).cuda(), cols=cols)
+    torch.cuda.synchronize()
+    for t in range(len(bags)):
+        assert np.array_equal(outs[t].cpu().numpy(),
+                              oracle.load_sparse_input(full, cols[t], bags[t], B, sample_ids=ids)), t
+    assert ffemb.load_sparse_inputs(tfull, bags, 0, cols=cols)[0].shape == (0, 3)   # empty batch
+
+
+def test_load_sparse_inputs_vs_reference_task(ffemb, oracle, torch_cuda):
+    """Against the reference's own DataLoader::load_sparse_input (examples/cpp/DLRM/dlrm.cu, compiled
+    unmodified into oracle/_ref/libffref_gpu.so) run once per table, as DataLoader::next_batch does."""
+    if not oracle.ref_gpu_available() or not hasattr(oracle.ref_gpu(), "ffref_gpu_load_sparse_input"):
+        pytest.skip("oracle/_ref/libffref_gpu.so without the data-loader task")
+    torch = torch_cuda
+    rng = np.random.default_rng(11)
+    N, T, in_dim, B, first = 9000, 26, 4, 4096, 4000
+    full = rng.integers(0, 10_000_000, (N, T * in_dim), dtype=np.int64)
+    pinned = torch.from_numpy(full).pin_memory()
+    ours = ffemb.load_sparse_inputs(pinned, [in_dim] * T, B, first_sample=first)
+    torch.cuda.synchronize()
+    for t in range(T):
+        ref = torch.empty((B, in_dim), dtype=torch.int64, device="cuda")
+        rc = oracle.ref_gpu().ffref_gpu_load_sparse_input(pinned.data_ptr(), N, T, in_dim, t, first, B, ref.data_ptr())
+        assert rc == 0
+        torch.cuda.synchronize()
+        assert torch.equal(ours[t], ref), t
+
+
+def test_load_sparse_inputs_errors(ffemb, torch_cuda):
+    torch = torch_cuda
+    full = torch.zeros((10, 8), dtype=torch.int64, device="cuda")
+    with pytest.raises(ffemb.FFEmbError):   # overlapping column blocks
+        ffemb.load_sparse_inputs(full, [4, 4], 5, cols=[0, 2])
+    with pytest.raises(ffemb.FFEmbError):   # block past the end of a sample row
+        ffemb.load_sparse_inputs(full, [4, 4], 5, cols=[0, 6])
+    with pytest.raises(ValueError):          # pageable host memory is not device-accessible
+        ffemb.load_sparse_inputs(torch.zeros((10, 8), dtype=torch.int64), [4], 5)
