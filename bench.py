@@ -133,24 +133,10 @@ class ClockSampler:
 # workload on the device
 # ---------------------------------------------------------------------------------------------
 def placement(wl, world, kind):
-    """table -> rank.  modulo = the reference's strategy generator (t % G,
-    examples/cpp/DLRM/strategies/dlrm_strategy.cc:252-256); balanced = greedy by lookups."""
-    T = wl.num_tables
-    if kind == "modulo" or world == 1:
-        return [t % world for t in range(T)]
-    # per-lookup cost classes measured on one B200 (profiles/r1_notes.md): rows from HBM and a row
-    # read-modify-write per lookup (big tables) > L2-resident tables through the sorted path > tables
-    # whose gradient fits on chip; + a per-bag term for the pooled-row write / output-grad read
-    def cost(t):
-        bytes_ = wl.rows[t] * wl.dim * 4
-        per = 1.0 if bytes_ > (64 << 20) else (0.25 if wl.rows[t] <= 16 or (bytes_ <= (80 << 10) and wl.bags[t] >= 8) else 0.55)
-        return wl.bags[t] * per + 0.6
-    load, mem, own = [0.0] * world, [0.0] * world, [0] * T
-    for t in sorted(range(T), key=lambda t: -cost(t)):
-        cands = sorted(range(world), key=lambda g: (load[g], mem[g]))
-        g = next((g for g in cands if mem[g] + wl.rows[t] * wl.dim * 4 < 150e9), cands[0])
-        own[t], load[g], mem[g] = g, load[g] + cost(t), mem[g] + wl.rows[t] * wl.dim * 4
-    return own
+    """table -> rank (sharding.place_tables).  modulo = the reference's strategy generator (t % G,
+    examples/cpp/DLRM/strategies/dlrm_strategy.cc:252-256); balanced = greedy by measured cost."""
+    pkg = importlib.import_module("dlrm-flexflow_b200")
+    return pkg.sharding.place_tables(wl.rows, wl.bags, wl.dim, world, kind)
 
 
 def zipf_indices(torch, gen, rows, shape, alpha, table_id, dev):

@@ -90,6 +90,8 @@ def lib():
     L.ffemb_backward_sgd_batched.argtypes = [tp, i32, i64, i64, i32, f32, vp, sz, vp]
     L.ffemb_backward_prepare.argtypes = [tp, i32, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_sgd_prepared.argtypes = [tp, i32, i64, i64, i32, f32, vp, sz, vp]
+    L.ffemb_forward_concat.argtypes = [tp, i32, i64, i64, i32, vp, i64, vp]
+    L.ffemb_backward_sgd_concat.argtypes = [tp, i32, i64, i64, i32, f32, vp, i64, i32, vp, sz, vp]
     L.ffemb_backward_dense_batched.argtypes = [tp, i32, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_workspace.argtypes = [i64, i64, i64]
     L.ffemb_backward_workspace.restype = sz

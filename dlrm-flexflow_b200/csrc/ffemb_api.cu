@@ -280,6 +280,41 @@ int ffemb_backward_sgd_prepared(const ffemb_table_t *tables, int num_tables, int
                                 (cudaStream_t)stream, STAGE_APPLY);
 }
 
+int ffemb_forward_concat(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B, int aggr,
+                         float *x, int64_t row_stride, ffemb_stream_t stream) {
+  ffemb_exchange_t ex;
+  memset(&ex, 0, sizeof(ex));
+  ex.peer_x[0] = x;
+  ex.num_peers = 1;
+  ex.batch_per_peer = B > 0 ? B : 1;
+  ex.row_stride = row_stride;
+  return ffemb_forward_exchange(tables, num_tables, D, B, aggr, &ex, stream);
+}
+
+int ffemb_backward_sgd_concat(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                              int aggr, float lr, const float *dx, int64_t row_stride, int prepared,
+                              void *workspace, size_t workspace_bytes, ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack(tables, num_tables, D, B, aggr, tb, /*need_out=*/false);
+  if (rc) return rc;
+  if ((B > 0 && !dx) || row_stride < D || row_stride % 4 != 0 || (uintptr_t)dx % 16 != 0) {
+    set_error("backward_sgd_concat: dx must be 16-byte aligned, row_stride >= D and a multiple of 4 "
+              "(dx=%p row_stride=%lld D=%lld)", (const void *)dx, (long long)row_stride, (long long)D);
+    return FFEMB_EINVAL;
+  }
+  for (int t = 0; t < num_tables; t++) {
+    if (tables[t].reserved < 0 || tables[t].reserved % 4 != 0 || (int64_t)tables[t].reserved + D > row_stride) {
+      set_error("backward_sgd_concat: table %d column offset %d (must be a multiple of 4, inside a row of %lld)",
+                t, tables[t].reserved, (long long)row_stride);
+      return FFEMB_EINVAL;
+    }
+    tb.t[t].out = const_cast<float *>(dx) + tables[t].reserved;
+  }
+  tb.og_stride = row_stride;
+  return launch_backward_sorted(tb, D, B, aggr, lr, APPLY_SGD, workspace, workspace_bytes,
+                                (cudaStream_t)stream, prepared ? STAGE_APPLY : STAGE_ALL);
+}
+
 int ffemb_backward_dense_batched(const ffemb_table_t *tables, int num_tables, int64_t D,
                                  int64_t B, int aggr, void *workspace, size_t workspace_bytes,
                                  ffemb_stream_t stream) {

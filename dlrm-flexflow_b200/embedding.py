@@ -209,6 +209,44 @@ class EmbeddingCollection:
             check(fn(sub, e - s, self.dim, batch, self.aggr, float(lr), ws.data_ptr(), ws.numel(),
                      _stream_ptr(stream)))
 
+    # ---- straight into / out of the Concat tensors (one GPU; ffemb_forward_concat / _backward_sgd_concat)
+    def _concat_descs(self, indices, batch, cols):
+        T = len(self.weights)
+        if T > B.FFEMB_MAX_TABLES:
+            raise ValueError("the Concat-direct calls take at most 64 tables")
+        arr = (ffemb_table_t * T)()
+        for t in range(T):
+            _req(indices[t], torch.int64, "indices")
+            if tuple(indices[t].shape) != (batch, self.bags[t]):
+                raise ValueError(f"table {t}: expected indices [{batch}][{self.bags[t]}]")
+            arr[t].idx, arr[t].out, arr[t].table = indices[t].data_ptr(), None, self.weights[t].data_ptr()
+            arr[t].R, arr[t].L, arr[t].reserved = int(self.weights[t].shape[0]), self.bags[t], int(cols[t])
+        return arr
+
+    def forward_concat(self, indices, x, cols=None, stream=None):
+        """Pooled rows stored straight into the Concat output x [B][row_stride]
+        (/root/reference/src/ops/concat.cu:211-251): table t at columns [cols[t], cols[t] + D)."""
+        batch = int(indices[0].shape[0])
+        _req(x, torch.float32, "x")
+        cols = [t * self.dim for t in range(len(self.weights))] if cols is None else cols
+        arr = self._concat_descs(indices, batch, cols)
+        check(lib().ffemb_forward_concat(arr, len(self.weights), self.dim, batch, self.aggr, x.data_ptr(),
+                                         int(x.shape[1]), _stream_ptr(stream)))
+        return x
+
+    def backward_sgd_concat(self, indices, dx, lr, cols=None, stream=None, prepared=False):
+        """Backward + SGD reading every table's output-grad in place from the gradient of the Concat
+        output dx [B][row_stride] (replaces the add_with_stride pass of concat.cu:325-366 and the
+        zero-fill of the per-table output-grad regions)."""
+        batch = int(indices[0].shape[0])
+        _req(dx, torch.float32, "dx")
+        cols = [t * self.dim for t in range(len(self.weights))] if cols is None else cols
+        arr = self._concat_descs(indices, batch, cols)
+        ws = self._workspaces(batch)[0]
+        check(lib().ffemb_backward_sgd_concat(arr, len(self.weights), self.dim, batch, self.aggr, float(lr),
+                                              dx.data_ptr(), int(dx.shape[1]), int(prepared), ws.data_ptr(),
+                                              ws.numel(), _stream_ptr(stream)))
+
     def backward_dense(self, indices, out_grads, weight_grads, stream=None):
         batch = int(indices[0].shape[0])
         arr = self._descs(indices, out_grads, weight_grads, batch)

@@ -71,3 +71,123 @@ class TableWisePlan:
     def recv_counts(self, rank):
         lo, hi = batch_block(self.batch, self.world, rank)
         return [len(self.owned(g)) * (hi - lo) * self.dim for g in range(self.world)]
+
+
+# ---------------------------------------------------------------------------------------------
+# Strategy files: the reference's TEXT format, as its loader parses it
+# (/root/reference/src/runtime/strategy.cc:95-146) and its writer emits it (:147-189):
+#   <number of ops>
+#   per op:  <name>  <device_type: 0 GPU | 1 CPU>  <nDims>  <dim[0] .. dim[nDims-1]>
+#            <number of device ids = prod(dims)>  <device ids ...>
+# whitespace-separated.  dim[0] is the fastest (feature) dimension, dim[nDims-1] the sample
+# dimension (/root/reference/src/runtime/model.cc:726-736).  A table placed whole on one GPU is
+# "embedding<i>" with a [1,1] grid (examples/cpp/DLRM/strategies/dlrm_strategy.cc:97-117,252-256;
+# the data loader keys on the same names, examples/cpp/DLRM/dlrm.cc:489).
+# ---------------------------------------------------------------------------------------------
+DEVICE_GPU, DEVICE_CPU = 0, 1
+
+
+@dataclass
+class ParallelConfig:
+    """/root/reference/include/config.h:47-73."""
+    device_type: int
+    dims: List[int]
+    device_ids: List[int]
+
+    def num_parts(self):
+        n = 1
+        for d in self.dims:
+            n *= d
+        return n
+
+
+def write_strategy(path, strategies):
+    """strategies: {op name: ParallelConfig}.  Same token stream as save_strategies_to_file
+    (ops in name order, like the std::map it iterates)."""
+    with open(path, "w") as f:
+        f.write(f"{len(strategies)}\n")
+        for name in sorted(strategies):
+            c = strategies[name]
+            if c.device_type not in (DEVICE_GPU, DEVICE_CPU):
+                raise ValueError("Unsupported Device Type")          # strategy.cc:172-174
+            if len(c.device_ids) != c.num_parts():
+                raise ValueError(f"{name}: {c.num_parts()} parts but {len(c.device_ids)} device ids")
+            f.write(f"{name}\n{c.device_type}\n{len(c.dims)}\n")
+            f.write("".join(f"{d}\t" for d in c.dims) + "\n")
+            f.write(f"{c.num_parts()}\n")
+            f.write("".join(f"{d}\t" for d in c.device_ids) + "\n")
+
+
+def read_strategy(path):
+    """-> {op name: ParallelConfig}; the checks of load_strategies_from_file (device type known,
+    device id count == prod(dims) or 0, no op twice) raise ValueError here (asserts there)."""
+    tok = open(path).read().split()
+    pos = 0
+
+    def nxt():
+        nonlocal pos
+        if pos >= len(tok):
+            raise ValueError("strategy file ends early")
+        pos += 1
+        return tok[pos - 1]
+
+    out = {}
+    for _ in range(int(nxt())):
+        name, dev, nd = nxt(), int(nxt()), int(nxt())
+        if dev not in (DEVICE_GPU, DEVICE_CPU):
+            raise ValueError("Unsupported Device Type")
+        dims = [int(nxt()) for _ in range(nd)]
+        n_ids = int(nxt())
+        cfg = ParallelConfig(dev, dims, [])
+        if n_ids not in (0, cfg.num_parts()):
+            raise ValueError(f"{name}: {n_ids} device ids for {cfg.num_parts()} parts")
+        cfg.device_ids = [int(nxt()) for _ in range(n_ids)]
+        if name in out:
+            raise ValueError(f"{name} listed twice")
+        out[name] = cfg
+    return out
+
+
+def tablewise_strategy(owner, world):
+    """The DLRM strategy for a table placement: embedding<i> whole on GPU owner[i] ([1,1] grid),
+    concat data-parallel over all GPUs (dlrm_strategy.cc:252-262)."""
+    s = {f"embedding{i}": ParallelConfig(DEVICE_GPU, [1, 1], [int(g)]) for i, g in enumerate(owner)}
+    s["concat"] = ParallelConfig(DEVICE_GPU, [1, world], list(range(world)))
+    return s
+
+
+def owners_from_strategy(strategies, num_tables):
+    """Table owners out of a strategy: every embedding<i> must be a [1,1] grid on a GPU — the
+    operator forbids anything else (/root/reference/src/ops/embedding.cu:84-85)."""
+    own = []
+    for i in range(num_tables):
+        c = strategies.get(f"embedding{i}")
+        if c is None:
+            raise KeyError(f"embedding{i} is not in the strategy")
+        if c.device_type != DEVICE_GPU or c.num_parts() != 1 or len(c.device_ids) != 1:
+            raise ValueError(f"embedding{i}: only a whole table on one GPU is a table-wise placement")
+        own.append(c.device_ids[0])
+    return own
+
+
+def place_tables(rows, bags, dim, world, kind="balanced", hbm_bytes=150e9):
+    """table -> rank.  modulo: the reference generator's i % G.  balanced: greedy longest-processing-
+    time by a per-table cost in the classes measured on one B200 (profiles/r1_notes.md): rows from
+    HBM plus a row read-modify-write per lookup (tables >> L2) > L2-resident tables through the
+    sorted path > tables whose gradient fits on chip; plus a per-bag term for the pooled-row write /
+    output-grad read; ties and capacity (hbm_bytes per GPU) by bytes."""
+    T = len(rows)
+    if kind == "modulo" or world == 1:
+        return [t % world for t in range(T)]
+
+    def cost(t):
+        b = rows[t] * dim * 4
+        per = 1.0 if b > (64 << 20) else (0.25 if rows[t] <= 16 or (b <= (80 << 10) and bags[t] >= 8) else 0.55)
+        return bags[t] * per + 0.6
+
+    load, mem, own = [0.0] * world, [0.0] * world, [0] * T
+    for t in sorted(range(T), key=lambda t: -cost(t)):
+        cands = sorted(range(world), key=lambda g: (load[g], mem[g]))
+        g = next((g for g in cands if mem[g] + rows[t] * dim * 4 < hbm_bytes), cands[0])
+        own[t], load[g], mem[g] = g, load[g] + cost(t), mem[g] + rows[t] * dim * 4
+    return own

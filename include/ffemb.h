@@ -180,6 +180,26 @@ FFEMB_API int ffemb_backward_dense_batched(const ffemb_table_t *tables, int num_
                                  int64_t B, int aggr, void *workspace, size_t workspace_bytes,
                                  ffemb_stream_t stream);
 
+/* ---- straight into / out of the Concat operator's tensors (one GPU) ----------------
+ * The reference's DLRM feeds every pooled output through Concat (interaction "cat",
+ * examples/cpp/DLRM/dlrm.cc:49-61): forward copies each [B][D] input into its column block of the
+ * [B][row_stride] output, one copy_with_stride launch per input (src/ops/concat.cu:211-251);
+ * backward adds each column block of the output's gradient into the input's zero-filled gradient
+ * region, one add_with_stride launch per input (src/ops/concat.cu:325-366; the zero-fill is
+ * Op::zero_grad, src/runtime/model.cc:481-488).  These two entry points remove both passes for the
+ * embedding inputs: forward_concat stores pooled row (b, t) at x[b*row_stride + tables[t].reserved
+ * + d] (it is ffemb_forward_exchange with one peer); backward_sgd_concat reads table t's
+ * output-grad rows in place at dx[b*row_stride + tables[t].reserved + d] — no per-table [B][D]
+ * output / output-grad buffer exists.  tables[t].reserved = column offset in floats (a multiple of
+ * 4), tables[t].out is ignored; x / dx 16-byte aligned, row_stride a multiple of 4.  prepared != 0:
+ * ffemb_backward_prepare already ran on this workspace.  Results are bit-identical to
+ * ffemb_forward_batched / ffemb_backward_sgd_batched on separate buffers.                         */
+FFEMB_API int ffemb_forward_concat(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                         int aggr, float *x, int64_t row_stride, ffemb_stream_t stream);
+FFEMB_API int ffemb_backward_sgd_concat(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                              int aggr, float lr, const float *dx, int64_t row_stride, int prepared,
+                              void *workspace, size_t workspace_bytes, ffemb_stream_t stream);
+
 /* Bytes of scratch the sorted backward needs for `num_lookups` = sum_t B*L_t lookups over
  * tables holding `total_rows` = sum_t R_t rows of D floats.  0 on invalid arguments.         */
 FFEMB_API size_t ffemb_backward_workspace(int64_t num_lookups, int64_t total_rows, int64_t D);

@@ -235,6 +235,24 @@ def ref_cpu(ndebug=False):
     return _ref_cpu[ndebug]
 
 
+def ref_strategy_load_op(path, name):
+    """The reference's load_strategies_from_file + lookup of op `name` (src/runtime/strategy.cc:
+    95-146) -> (device_type, dims, device_ids)."""
+    L = ref_cpu()
+    out = (C.c_int * 1100)()
+    n = L.ffref_strategy_load_op(path.encode(), name.encode(), out, 1100)
+    if n < 0:
+        raise KeyError(f"{name}: reference loader returned {n}")
+    nd = out[1]
+    return out[0], list(out[2:2 + nd]), list(out[2 + nd:n])
+
+
+def ref_strategy_save_tablewise(path, num_tables, G):
+    """The DLRM generator's table-wise strategy written by the reference's save_strategies_to_file."""
+    rc = ref_cpu().ffref_strategy_save_tablewise(path.encode(), num_tables, G)
+    assert rc == 0
+
+
 def ref_cpu_forward_task(idx, W, ndebug=False):
     """Embedding::forward_task_cpu (src/ops/embedding.cc:377-415); bag size must be 1."""
     W = np.ascontiguousarray(W, np.float32)

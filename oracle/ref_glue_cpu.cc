@@ -15,6 +15,8 @@
 #include "model.h"
 
 #include <chrono>
+#include <map>
+#include <string>
 #include <thread>
 
 /* defined (non-static) in the reference translation unit */
@@ -105,6 +107,52 @@ double ffref_cpu_run_tables(int T, const int64_t *const *idx, float *const *out,
   for (auto &w : workers) w.join();
   auto t1 = std::chrono::steady_clock::now();
   return std::chrono::duration<double>(t1 - t0).count();
+}
+
+/* ---- strategy files: src/runtime/strategy.cc:95-189 (declared in include/config.h) --------
+ * ffref_strategy_load_op: the reference's load_strategies_from_file on `file`, then the entry of
+ * op `name` (keyed by FFConfig::get_hash_id, strategy.cc:20-26).  out = {device_type, nDims,
+ * dim[0..nDims), device_ids[0..num_parts)}; returns the number of ints written, -1 when the file
+ * does not load, -2 when the op is not in it.                                                 */
+int ffref_strategy_load_op(const char *file, const char *name, int *out, int max_out) {
+  std::map<MappingTagID, ParallelConfig> strategies;
+  if (!load_strategies_from_file(file, strategies)) return -1;
+  std::map<MappingTagID, ParallelConfig>::const_iterator it = strategies.find(FFConfig::get_hash_id(name));
+  if (it == strategies.end()) return -2;
+  const ParallelConfig &c = it->second;
+  int n = 1, k = 0;
+  for (int j = 0; j < c.nDims; j++) n *= c.dim[j];
+  if (2 + c.nDims + n > max_out) return -3;
+  out[k++] = (int)c.device_type;
+  out[k++] = c.nDims;
+  for (int j = 0; j < c.nDims; j++) out[k++] = c.dim[j];
+  for (int j = 0; j < n; j++) out[k++] = c.device_ids[j];
+  return k;
+}
+
+/* ffref_strategy_save_tablewise: the strategy the reference's DLRM generator describes
+ * (examples/cpp/DLRM/strategies/dlrm_strategy.cc:97-117,252-256: "embedding<i>" whole on GPU
+ * i % G with a [1,1] grid; "concat" data-parallel over the G GPUs) written by the reference's own
+ * save_strategies_to_file (strategy.cc:147-189).                                               */
+int ffref_strategy_save_tablewise(const char *file, int num_tables, int G) {
+  std::map<std::string, ParallelConfig> strategies;
+  for (int i = 0; i < num_tables; i++) {
+    ParallelConfig c;
+    c.device_type = ParallelConfig::GPU;
+    c.nDims = 2;
+    c.dim[0] = 1;
+    c.dim[1] = 1;
+    c.device_ids[0] = i % G;
+    strategies["embedding" + std::to_string(i)] = c;
+  }
+  ParallelConfig c;
+  c.device_type = ParallelConfig::GPU;
+  c.nDims = 2;
+  c.dim[0] = 1;
+  c.dim[1] = G;
+  for (int g = 0; g < G; g++) c.device_ids[g] = g;
+  strategies["concat"] = c;
+  return save_strategies_to_file(file, strategies) ? 0 : -1;
 }
 
 int ffref_cpu_asserts_enabled(void) {

@@ -509,3 +509,62 @@ def test_load_sparse_inputs_errors(ffemb, torch_cuda):
         ffemb.load_sparse_inputs(full, [4, 4], 5, cols=[0, 6])
     with pytest.raises(ValueError):          # pageable host memory is not device-accessible
         ffemb.load_sparse_inputs(torch.zeros((10, 8), dtype=torch.int64), [4], 5)
+
+
+# ---------------------------------------------------------------------------------------------
+# Concat-direct: pooled rows into, output-grads out of, the Concat tensors in place
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("aggr", [21, 22])
+@pytest.mark.parametrize("D,B", [(64, 3000), (128, 9000), (16, 777)])
+def test_concat_direct_matches_separate_buffers_and_oracle_layout(ffemb, oracle, torch_cuda, D, B, aggr):
+    """forward_concat == oracle.concat_forward of the per-table pooled outputs (the layout of
+    src/ops/concat.cu:211-251, the dense bottom-MLP block in front); backward_sgd_concat on the Concat
+    gradient == backward_sgd on the column blocks copied out (what add_with_stride into zeroed
+    regions produces, concat.cu:325-366): bit-identical tables.  Mix of tiny / small / sorted paths."""
+    torch = torch_cuda
+    rows, bags = [5, 100000, 33, 20000, 977], [1, 3, 20, 2, 9]
+    T = len(rows)
+    Ws, idxs = [], []
+    for t, (R, L) in enumerate(zip(rows, bags)):
+        W, idx, _ = make_inputs(R, D, L, B, seed=800 + t)
+        Ws.append(W), idxs.append(idx)
+    rng = np.random.default_rng(5)
+    dense = rng.uniform(-1, 1, (B, D)).astype(np.float32)          # x(b): bottom-MLP output, column block 0
+    stride = (1 + T) * D + 8                                        # + padding columns nobody owns
+    cols = [(1 + t) * D for t in range(T)]
+    dx = rng.uniform(-1, 1, (B, stride)).astype(np.float32)
+    didx = [dev(torch, i) for i in idxs]
+    # separate buffers (the reference's structure)
+    a = [dev(torch, w) for w in Ws]
+    ca = ffemb.EmbeddingCollection(a, bags, aggr)
+    outs = ca.forward(didx)
+    ca.backward_sgd(didx, [dev(torch, dx[:, c:c + D]) for c in cols], 0.01)
+    # Concat-direct
+    b = [dev(torch, w) for w in Ws]
+    cb = ffemb.EmbeddingCollection(b, bags, aggr)
+    x = torch.full((B, stride), 7.0, device="cuda")
+    x[:, :D] = dev(torch, dense)
+    cb.forward_concat(didx, x, cols)
+    cb.backward_sgd_concat(didx, dev(torch, dx), 0.01, cols)
+    torch.cuda.synchronize()
+    want = oracle.concat_forward([dense] + [o.cpu().numpy() for o in outs])
+    got = x.cpu().numpy()
+    assert np.array_equal(got[:, :(1 + T) * D], want)
+    assert np.all(got[:, (1 + T) * D:] == 7.0)                      # padding untouched
+    assert np.array_equal(outs[1].cpu().numpy(), oracle.forward(idxs[1], Ws[1], aggr))
+    for t in range(T):
+        assert torch.equal(a[t], b[t]), t
+
+
+def test_concat_direct_errors(ffemb, torch_cuda):
+    torch = torch_cuda
+    W = [torch.zeros((10, 16), device="cuda")]
+    coll = ffemb.EmbeddingCollection(W, [1])
+    idx = [torch.zeros((8, 1), dtype=torch.int64, device="cuda")]
+    dx = torch.zeros((8, 32), device="cuda")
+    with pytest.raises(ffemb.FFEmbError):
+        coll.backward_sgd_concat(idx, dx, 0.01, cols=[20])      # block past the end of a row
+    with pytest.raises(ffemb.FFEmbError):
+        coll.backward_sgd_concat(idx, dx, 0.01, cols=[2])       # 16-byte fragments must stay aligned
+    with pytest.raises(ffemb.FFEmbError):
+        coll.forward_concat(idx, dx, cols=[20])

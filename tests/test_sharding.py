@@ -76,3 +76,64 @@ def test_synth_configs(ffemb):
     top = np.bincount(idx.reshape(-1)).max() / idx.size
     assert top > 0.02
     assert np.array_equal(idx, ffemb.synth.gen_indices(small, 0))  # seeded
+
+
+# ---- strategy files: the reference's text format -------------------------------
+def _golden_strategy():
+    import os
+    return os.path.join(os.path.dirname(__file__), "golden", "dlrm_tablewise_26x8.strategy")
+
+
+def test_strategy_reader_parses_the_reference_writers_file(ffemb):
+    """tests/golden/dlrm_tablewise_26x8.strategy was written by the reference's own
+    save_strategies_to_file (tests/golden/make_strategy_golden.py): 26 tables, table i whole on
+    GPU i % 8, concat data-parallel."""
+    S = ffemb.sharding
+    st = S.read_strategy(_golden_strategy())
+    assert len(st) == 27
+    assert S.owners_from_strategy(st, 26) == [i % 8 for i in range(26)] == S.place_tables([1] * 26, [1] * 26, 128, 8, "modulo")
+    assert st["concat"].dims == [1, 8] and st["concat"].device_ids == list(range(8))
+    assert all(st[f"embedding{i}"].dims == [1, 1] and st[f"embedding{i}"].device_type == S.DEVICE_GPU for i in range(26))
+
+
+def test_strategy_writer_emits_the_reference_writers_bytes(ffemb, tmp_path):
+    S = ffemb.sharding
+    p = str(tmp_path / "s.strategy")
+    S.write_strategy(p, S.tablewise_strategy([i % 8 for i in range(26)], 8))
+    assert open(p).read() == open(_golden_strategy()).read()
+    assert S.read_strategy(p) == S.read_strategy(_golden_strategy())
+
+
+def test_strategy_writer_is_read_by_the_reference_loader(ffemb, oracle, tmp_path):
+    """A cost-balanced placement written by the product, parsed by the reference's own
+    load_strategies_from_file (oracle/_ref, src/runtime/strategy.cc:95-146)."""
+    import pytest
+    if not oracle.ref_cpu_available():
+        pytest.skip("oracle/_ref/libffref_cpu.so not built (needs /root/reference)")
+    S = ffemb.sharding
+    wl = ffemb.synth.config(3)
+    own = S.place_tables(wl.rows, wl.bags, wl.dim, 8, "balanced")
+    assert sorted(set(own)) == list(range(8))
+    p = str(tmp_path / "balanced.strategy")
+    S.write_strategy(p, S.tablewise_strategy(own, 8))
+    for i, g in enumerate(own):
+        assert oracle.ref_strategy_load_op(p, f"embedding{i}") == (S.DEVICE_GPU, [1, 1], [g])
+    assert oracle.ref_strategy_load_op(p, "concat") == (S.DEVICE_GPU, [1, 8], list(range(8)))
+    assert S.owners_from_strategy(S.read_strategy(p), wl.num_tables) == own
+
+
+def test_strategy_errors(ffemb, tmp_path):
+    import pytest
+    S = ffemb.sharding
+    p = tmp_path / "bad.strategy"
+    p.write_text("1\nembedding0\n7\n2\n1\t1\t\n1\n0\t\n")          # unknown device type
+    with pytest.raises(ValueError):
+        S.read_strategy(str(p))
+    p.write_text("1\nembedding0\n0\n2\n1\t2\t\n1\n0\t\n")          # 2 parts, 1 device id
+    with pytest.raises(ValueError):
+        S.read_strategy(str(p))
+    p.write_text("1\nembedding0\n0\n2\n1\t2\t\n2\n0\t1\t\n")       # a table split over two GPUs
+    with pytest.raises(ValueError):
+        S.owners_from_strategy(S.read_strategy(str(p)), 1)
+    with pytest.raises(KeyError):
+        S.owners_from_strategy({}, 1)
