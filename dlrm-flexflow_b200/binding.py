@@ -28,6 +28,11 @@ class ffemb_table_t(C.Structure):
                 ("R", C.c_int64), ("L", C.c_int32), ("reserved", C.c_int32)]
 
 
+class ffemb_sgd_t(C.Structure):
+    _fields_ = [("lr", C.c_float), ("weight_decay", C.c_float), ("momentum", C.c_float),
+                ("nesterov", C.c_int32)]
+
+
 class ffemb_exchange_t(C.Structure):
     _fields_ = [("peer_x", C.c_void_p * FFEMB_MAX_PEERS), ("num_peers", C.c_int32),
                 ("reserved", C.c_int32), ("batch_per_peer", C.c_int64), ("row_stride", C.c_int64)]
@@ -90,6 +95,10 @@ def lib():
     L.ffemb_backward_sgd_batched.argtypes = [tp, i32, i64, i64, i32, f32, vp, sz, vp]
     L.ffemb_backward_prepare.argtypes = [tp, i32, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_sgd_prepared.argtypes = [tp, i32, i64, i64, i32, f32, vp, sz, vp]
+    L.ffemb_sgd_touched_words.argtypes = [i64]
+    L.ffemb_sgd_touched_words.restype = i64
+    L.ffemb_backward_sgdx_batched.argtypes = [tp, i32, i64, i64, i32, C.POINTER(ffemb_sgd_t), C.POINTER(vp),
+                                              C.POINTER(vp), vp, sz, vp]
     L.ffemb_forward_concat.argtypes = [tp, i32, i64, i64, i32, vp, i64, vp]
     L.ffemb_backward_sgd_concat.argtypes = [tp, i32, i64, i64, i32, f32, vp, i64, i32, vp, sz, vp]
     L.ffemb_backward_dense_batched.argtypes = [tp, i32, i64, i64, i32, vp, sz, vp]
@@ -108,7 +117,7 @@ def lib():
     return L
 
 
-PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small", "exchange", "input"]
+PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small", "exchange", "input", "dense"]
 
 
 def profile_enable(on=True):

@@ -280,6 +280,41 @@ int ffemb_backward_sgd_prepared(const ffemb_table_t *tables, int num_tables, int
                                 (cudaStream_t)stream, STAGE_APPLY);
 }
 
+int64_t ffemb_sgd_touched_words(int64_t R) { return R <= 0 ? 0 : (R + 31) / 32; }
+
+int ffemb_backward_sgdx_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                                int aggr, const ffemb_sgd_t *opt, float *const *V,
+                                uint32_t *const *touched, void *workspace, size_t workspace_bytes,
+                                ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack(tables, num_tables, D, B, aggr, tb);
+  if (rc) return rc;
+  if (!opt || !touched || opt->momentum < 0.f || (opt->momentum > 0.f && !V)) {
+    set_error("backward_sgdx: optimizer arguments missing (opt=%p V=%p touched=%p)", (const void *)opt,
+              (const void *)V, (const void *)touched);
+    return FFEMB_EINVAL;
+  }
+  OptArgs o;
+  memset(&o, 0, sizeof(o));
+  o.lr = opt->lr;
+  o.wd = opt->weight_decay;
+  o.mom = opt->momentum;
+  o.nesterov = opt->nesterov;
+  for (int t = 0; t < num_tables; t++) {
+    if (tables[t].R <= 0) continue;
+    if (!touched[t] || (uintptr_t)touched[t] % 4 != 0 ||
+        (o.mom > 0.f && (!V[t] || (uintptr_t)V[t] % 16 != 0))) {
+      set_error("backward_sgdx: table %d needs a touched bitmap%s", t,
+                o.mom > 0.f ? " and a 16-byte aligned momentum buffer" : "");
+      return FFEMB_EINVAL;
+    }
+    o.V[t] = o.mom > 0.f ? V[t] : nullptr;
+    o.touched[t] = touched[t];
+  }
+  return launch_backward_sorted(tb, D, B, aggr, o.lr, APPLY_SGDX, workspace, workspace_bytes,
+                                (cudaStream_t)stream, STAGE_ALL, &o);
+}
+
 int ffemb_forward_concat(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B, int aggr,
                          float *x, int64_t row_stride, ffemb_stream_t stream) {
   ffemb_exchange_t ex;

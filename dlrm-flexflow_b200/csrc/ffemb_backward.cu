@@ -103,7 +103,8 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
                                             const uint32_t *vals,
                                             const float *rows_in, int64_t n, int64_t tile, int CH,
                                             bool active, int D, uint32_t B, int aggr, float lr,
-                                            K *keys_out, float *rows_out, int sub, int sl) {
+                                            K *keys_out, float *rows_out, int sub, int sl,
+                                            const OptArgs *oa = nullptr) {
   constexpr K INV = KeyTraits<K>::INV;
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
   const int D4 = D >> 2;
@@ -139,6 +140,7 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
       bool eend[UNR];
       float *wp[UNR];
       float scale[UNR];
+      int et[UNR];
 #pragma unroll
       for (int u = 0; u < UNR; u++) {
         const int src = sub * G + jj + u;
@@ -147,11 +149,13 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
         eend[u] = __shfl_sync(0xffffffffu, (int)is_end, src) != 0;
         wp[u] = nullptr;
         scale[u] = 1.0f;
+        et[u] = 0;
         if (jj + u < G && ek[u] != INV) {
           const float *gp;
           if (LEVEL1) {
             const uint32_t t = ev / B;
             const uint32_t b = ev - t * B;
+            et[u] = (int)t;
             gp = tb.t[t].out + (int64_t)b * tb.og_stride;
             if (aggr != FFEMB_AGGR_SUM) scale[u] = (float)tb.t[t].L;
             if (eend[u]) wp[u] = tb.t[t].table + (int64_t)(ek[u] - tb.row_base[t]) * D;
@@ -159,6 +163,7 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
             gp = rows_in + (p0 + jj + u) * (int64_t)D;
             if (eend[u]) {
               const int t = find_table(tb, (uint64_t)ek[u]);
+              et[u] = t;
               wp[u] = tb.t[t].table + (int64_t)((uint64_t)ek[u] - tb.row_base[t]) * D;
             }
           }
@@ -209,6 +214,9 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
                 if (MODE == APPLY_SGD) {  // W -= lr*gt, contracted like the reference's FFMA
                   o.x = fmaf(-acc[c].x, lr, o.x); o.y = fmaf(-acc[c].y, lr, o.y);
                   o.z = fmaf(-acc[c].z, lr, o.z); o.w = fmaf(-acc[c].w, lr, o.w);
+                } else if (MODE == APPLY_SGDX) {
+                  o = sgdx_fragment(oa, et[u], tb.t[et[u]].table, wp[u] + 4 * (sl + c * G), o, acc[c],
+                                    (uint64_t)ek[u] - tb.row_base[et[u]], sl == 0 && c == 0);
                 } else {
                   f4_add(o, acc[c]);
                 }
@@ -273,7 +281,7 @@ template <typename K, int G, int C, int MODE, bool AVG, bool PIPE>
 __global__ void __launch_bounds__(L1Threads<G>::value, 512 / L1Threads<G>::value)
 reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
                const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
-               float *rows_out, int flags, uint32_t split) {
+               float *rows_out, int flags, uint32_t split, const OptArgs *oa) {
   constexpr int THREADS = L1Threads<G>::value;
   constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
@@ -452,6 +460,11 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
                 if (MODE == APPLY_SGD) {  // W -= lr*gt, contracted like the reference's FFMA
                   o.x = fmaf(-acc[c].x, lr, o.x); o.y = fmaf(-acc[c].y, lr, o.y);
                   o.z = fmaf(-acc[c].z, lr, o.z); o.w = fmaf(-acc[c].w, lr, o.w);
+                } else if (MODE == APPLY_SGDX) {
+                  const uint64_t key = (uint64_t)keys[t0 + grp * UNR + u];
+                  const int t = find_table(tb, key);
+                  o = sgdx_fragment(oa, t, tb.t[t].table, wp[bf][u] + 4 * (sl + c * G), o, acc[c],
+                                    key - tb.row_base[t], sl == 0 && c == 0);
                 } else {
                   f4_add(o, acc[c]);
                 }
@@ -499,21 +512,21 @@ template <typename K, int G, int C, bool LEVEL1, int MODE>
 __global__ void __launch_bounds__(kThreads)
 reduce_level_kernel(const __grid_constant__ TableBatch tb, const K *keys, const uint32_t *vals,
                     const float *rows_in, int64_t n, int CH, int D, uint32_t B, int aggr, float lr,
-                    K *keys_out, float *rows_out) {
+                    K *keys_out, float *rows_out, const OptArgs *oa) {
   constexpr int SLOTS = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int sub = lane / G, sl = lane % G;
   const int64_t tile = ((int64_t)blockIdx.x * (kThreads / 32) + warp) * SLOTS + sub;
   const int64_t ntiles = (n + CH - 1) / CH;
   reduce_tile<K, G, C, LEVEL1, MODE>(tb, keys, vals, rows_in, n, tile, CH, tile < ntiles, D, B,
-                                     aggr, lr, keys_out, rows_out, sub, sl);
+                                     aggr, lr, keys_out, rows_out, sub, sl, oa);
 }
 
 // All remaining levels in ONE CTA: level i reads buffer (i&1), writes buffer ((i+1)&1).
 template <typename K, int G, int C, int MODE>
 __global__ void __launch_bounds__(kThreads)
 reduce_tail_kernel(const __grid_constant__ TableBatch tb, K *keys_a, float *rows_a, K *keys_b,
-                   float *rows_b, int64_t n, int CH, int D, float lr) {
+                   float *rows_b, int64_t n, int CH, int D, float lr, const OptArgs *oa) {
   constexpr int SLOTS = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int sub = lane / G, sl = lane % G;
@@ -526,7 +539,7 @@ reduce_tail_kernel(const __grid_constant__ TableBatch tb, K *keys_a, float *rows
     for (int64_t base = 0; base < ntiles; base += nslots) {
       const int64_t tile = base + slot;
       reduce_tile<K, G, C, false, MODE>(tb, kin, nullptr, rin, n, tile, CH, tile < ntiles, D, 1u,
-                                        FFEMB_AGGR_SUM, lr, kout, rout, sub, sl);
+                                        FFEMB_AGGR_SUM, lr, kout, rout, sub, sl, oa);
     }
     if (ntiles <= 1) break;
     __syncthreads();  // partial rows written by this CTA are visible to it after the barrier
@@ -596,15 +609,87 @@ static Carve carve(char *base, int64_t n, int64_t total_rows, int64_t D) {
   return c;
 }
 
+#ifndef FFEMB_BACKWARD_WIDE_TU  // (the 64-bit-key instantiations are a second translation unit, see the end)
+static constexpr size_t kOptBytes = (sizeof(OptArgs) + 255) & ~(size_t)255;  // device copy of OptArgs
 size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t D) {
   if (num_lookups <= 0 || total_rows <= 0 || D <= 0 || num_lookups >= (1ll << 31)) return 0;
-  return carve(nullptr, num_lookups, total_rows, D).total + small_partials_bound(D);
+  return carve(nullptr, num_lookups, total_rows, D).total + small_partials_bound(D) + kOptBytes;
 }
+
+// ---- APPLY_SGDX, second half: the rows the step did NOT touch ---------------------------------
+// sgd_update runs over every element of the table (optimizer_kernel.cu:23-41); with a zero gradient
+// that is gt = wd*W (+ momentum).  One warp per 32 rows = one word of the touched bitmap: rows whose
+// bit is set were updated by the sparse pass and are skipped; the word is cleared for the next step.
+// Streaming read-modify-write of W (and V): 8 (16) bytes per element, against the reference's 4 (zero
+// fill) + 12 (20) (sgd_update) + the atomics — and no dense gradient exists.
+template <int G>
+__global__ void __launch_bounds__(256)
+sgdx_untouched_kernel(float *__restrict__ W, float *__restrict__ V, uint32_t *__restrict__ touched,
+                      int64_t R, int D, float lr, float wd, float mom, int nesterov) {
+  constexpr int SLOTS = 32 / G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane / G, sl = lane % G;
+  const int D4 = D >> 2;
+  const uint64_t pol = policy_evict_first();
+  const int64_t nwords = (R + 31) >> 5;
+  for (int64_t w0 = (int64_t)blockIdx.x * 8 + warp; w0 < nwords; w0 += (int64_t)gridDim.x * 8) {
+    const uint32_t bits = touched[w0];
+    __syncwarp();
+    if (lane == 0 && bits) touched[w0] = 0u;
+    for (int r0 = 0; r0 < 32; r0 += SLOTS) {
+      const int64_t row = w0 * 32 + r0 + sub;
+      if (row >= R || ((bits >> (r0 + sub)) & 1u)) continue;
+      for (int c4 = sl; c4 < D4; c4 += G) {
+        float *wp = W + row * (int64_t)D + 4 * c4;
+        float4 w = ld_row_hint(wp, pol), v = make_float4(0.f, 0.f, 0.f, 0.f);
+        float *vp = nullptr;
+        if (mom > 0.0f) {
+          vp = V + row * (int64_t)D + 4 * c4;
+          v = ld_row_hint(vp, pol);
+        }
+        float4 o;
+        o.x = sgdx_elem(w.x, 0.0f, v.x, lr, wd, mom, nesterov != 0);
+        o.y = sgdx_elem(w.y, 0.0f, v.y, lr, wd, mom, nesterov != 0);
+        o.z = sgdx_elem(w.z, 0.0f, v.z, lr, wd, mom, nesterov != 0);
+        o.w = sgdx_elem(w.w, 0.0f, v.w, lr, wd, mom, nesterov != 0);
+        st_row_hint(wp, o, pol);
+        if (vp) st_row_hint(vp, v, pol);
+      }
+    }
+  }
+}
+
+static int launch_sgdx_untouched(const TableBatch &tb, int D, const OptArgs &o, cudaStream_t s) {
+  int launches = 0;
+  for (int t = 0; t < tb.num_tables; t++) launches += tb.t[t].R > 0;
+  if (!launches) return FFEMB_OK;
+  ProfScope prof(FFEMB_PHASE_DENSE, launches, s);
+  const int D4 = D / 4;
+  for (int t = 0; t < tb.num_tables; t++) {
+    const int64_t R = tb.t[t].R;
+    if (R <= 0) continue;
+    const int64_t nwords = (R + 31) / 32;
+    const unsigned grid = (unsigned)((nwords + 7) / 8 < 148 * 8 ? (nwords + 7) / 8 : 148 * 8);
+    auto go = [&](auto kern) {
+      kern<<<grid, 256, 0, s>>>(tb.t[t].table, o.V[t], o.touched[t], R, D, o.lr, o.wd, o.mom, o.nesterov);
+    };
+    if (D4 <= 1) go(sgdx_untouched_kernel<1>);
+    else if (D4 <= 2) go(sgdx_untouched_kernel<2>);
+    else if (D4 <= 4) go(sgdx_untouched_kernel<4>);
+    else if (D4 <= 8) go(sgdx_untouched_kernel<8>);
+    else if (D4 <= 16) go(sgdx_untouched_kernel<16>);
+    else go(sgdx_untouched_kernel<32>);
+  }
+  return cuda_fail(cudaGetLastError(), "sgdx dense pass launch");
+}
+
+#endif  // !FFEMB_BACKWARD_WIDE_TU
 
 // ---- host driver -----------------------------------------------------------------------------
 template <typename K, int G, int C, int MODE>
 static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr, int64_t n,
-                      int64_t total_rows, const Carve &c, cudaStream_t s, int stage, int64_t n_stream) {
+                      int64_t total_rows, const Carve &c, cudaStream_t s, int stage, int64_t n_stream,
+                      const OptArgs *oa) {
   K *keys_a = (K *)c.keys_a, *keys_b = (K *)c.keys_b;
   int max_l = 1;
   for (int t = 0; t < tb.num_tables; t++) max_l = tb.t[t].L > max_l ? tb.t[t].L : max_l;
@@ -645,20 +730,21 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     if (const char *e = getenv("FFEMB_R1_PIPE")) pipe = atoi(e) != 0;
     const size_t sm_sum = EPC * sizeof(EntryDesc), sm_avg = EPC * (sizeof(EntryDesc) + sizeof(float2));
     auto go = [&](auto kern, size_t sm) {
-      kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], flags, split);
+      kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], flags, split, oa);
     };
     // D <= 128: the cp.async ring variant, 4 entries ahead (measured: cfg3 1.36 -> 1.22 ms against the
     // register double buffer; cfg5, whose gathers miss L2, 11.4 ms against 14.5 for the register-
     // pipelined variant and 14.2 for an 8-deep ring).  D > 128 (several fragments per lane): the
     // register variants — pipelined when one table's output-grad exceeds L2 (gathers miss), lean
     // otherwise.  FFEMB_R1_RING=0|4|8 / FFEMB_R1_PIPE override (tuning aids).
+    bool pipe_done = false;
     int ring = 4;
     if (const char *e = getenv("FFEMB_R1_RING")) ring = atoi(e);
     if (C == 1 && ring > 0) {
       auto gor = [&](auto kern, int S) {
         const size_t sm = EPC * sizeof(EntryDesc) + (size_t)(T1 / 32) * S * 2 * 32 * 16;
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], split);
+        kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], split, oa);
       };
       if constexpr (C == 1) {
         const bool avg = aggr != FFEMB_AGGR_SUM;
@@ -666,11 +752,11 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
         else { if (avg) gor(reduce1_ring_kernel<K, G, MODE, true, 4>, 4); else gor(reduce1_ring_kernel<K, G, MODE, false, 4>, 4); }
       }
     } else if (aggr == FFEMB_AGGR_SUM) {
-      if (pipe) go(reduce1_kernel<K, G, C, MODE, false, true>, sm_sum);
-      else go(reduce1_kernel<K, G, C, MODE, false, false>, sm_sum);
+      if constexpr (MODE != APPLY_SGDX) { if (pipe) { go(reduce1_kernel<K, G, C, MODE, false, true>, sm_sum); pipe_done = true; } }
+      if (!pipe_done) go(reduce1_kernel<K, G, C, MODE, false, false>, sm_sum);
     } else {
-      if (pipe) go(reduce1_kernel<K, G, C, MODE, true, true>, sm_avg);
-      else go(reduce1_kernel<K, G, C, MODE, true, false>, sm_avg);
+      if constexpr (MODE != APPLY_SGDX) { if (pipe) { go(reduce1_kernel<K, G, C, MODE, true, true>, sm_avg); pipe_done = true; } }
+      if (!pipe_done) go(reduce1_kernel<K, G, C, MODE, true, false>, sm_avg);
     }
   }
   int64_t m = 2 * ntiles1;
@@ -685,35 +771,55 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
       reduce_level_kernel<K, G, C, false, MODE>
           <<<(unsigned)((tiles + slots_per_cta - 1) / slots_per_cta), kThreads, 0, s>>>(
               tb, pk[cur], nullptr, c.prows[cur], m, CH2, D, 1u, FFEMB_AGGR_SUM, lr, pk[cur ^ 1],
-              c.prows[cur ^ 1]);
+              c.prows[cur ^ 1], oa);
       m = 2 * tiles;
       cur ^= 1;
     }
     reduce_tail_kernel<K, G, C, MODE><<<1, kThreads, 0, s>>>(tb, pk[cur], c.prows[cur], pk[cur ^ 1],
-                                                            c.prows[cur ^ 1], m, CH2, D, lr);
+                                                            c.prows[cur ^ 1], m, CH2, D, lr, oa);
   }
   return cuda_fail(cudaGetLastError(), "sorted backward launch");
 }
 
 template <typename K, int MODE>
 static int dispatch_g(const TableBatch &tb, int D, int64_t B, int aggr, float lr, int64_t n,
-                      int64_t rows, const Carve &c, cudaStream_t s, int stage, int64_t n_stream) {
+                      int64_t rows, const Carve &c, cudaStream_t s, int stage, int64_t n_stream,
+                      const OptArgs *oa) {
   const int D4 = D / 4;
-  if (D4 <= 1) return run_sorted<K, 1, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
-  if (D4 <= 2) return run_sorted<K, 2, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
-  if (D4 <= 4) return run_sorted<K, 4, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
-  if (D4 <= 8) return run_sorted<K, 8, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
-  if (D4 <= 16) return run_sorted<K, 16, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
-  if (D4 <= 32) return run_sorted<K, 32, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
-  if (D4 <= 64) return run_sorted<K, 32, 2, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
-  return run_sorted<K, 32, 4, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream);
+  if (D4 <= 1) return run_sorted<K, 1, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
+  if (D4 <= 2) return run_sorted<K, 2, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
+  if (D4 <= 4) return run_sorted<K, 4, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
+  if (D4 <= 8) return run_sorted<K, 8, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
+  if (D4 <= 16) return run_sorted<K, 16, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
+  if (D4 <= 32) return run_sorted<K, 32, 1, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
+  if (D4 <= 64) return run_sorted<K, 32, 2, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
+  return run_sorted<K, 32, 4, MODE>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
 }
 
+// 64-bit keys (more than 2^32 - 1 rows on one GPU): the same templates instantiated in
+// ffemb_backward_wide.cu, which includes this file with FFEMB_BACKWARD_WIDE_TU defined — the two
+// halves then compile side by side.
+int dispatch_wide(const TableBatch &tb, int D, int64_t B, int aggr, float lr, int64_t n, int64_t rows,
+                  const Carve &c, cudaStream_t s, int stage, int64_t n_stream, const OptArgs *oa, int mode);
+#ifdef FFEMB_BACKWARD_WIDE_TU
+int dispatch_wide(const TableBatch &tb, int D, int64_t B, int aggr, float lr, int64_t n, int64_t rows,
+                  const Carve &c, cudaStream_t s, int stage, int64_t n_stream, const OptArgs *oa, int mode) {
+  if (mode == APPLY_SGD) return dispatch_g<uint64_t, APPLY_SGD>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
+  if (mode == APPLY_SGDX) return dispatch_g<uint64_t, APPLY_SGDX>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
+  return dispatch_g<uint64_t, APPLY_GRAD>(tb, D, B, aggr, lr, n, rows, c, s, stage, n_stream, oa);
+}
+#else
+
 int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int aggr, float lr,
-                           ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s, int stage) {
+                           ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s, int stage,
+                           const OptArgs *opt_host) {
   int64_t n_all = 0;
   for (int t = 0; t < tb_all.num_tables; t++) n_all += B * tb_all.t[t].L;
-  if (n_all == 0) return FFEMB_OK;
+  if (mode == APPLY_SGDX && (!opt_host || stage != STAGE_ALL)) {
+    set_error("general SGD update: optimizer arguments missing, or a split (prepared) call");
+    return FFEMB_EINVAL;
+  }
+  if (n_all == 0 && mode != APPLY_SGDX) return FFEMB_OK;
   if (D % 4 != 0 || D > 512) {
     set_error("sorted backward needs D %% 4 == 0 and D <= 512 (got %lld)", (long long)D);
     return FFEMB_EINVAL;
@@ -741,7 +847,7 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
   int n_tiny = 0;
   for (int pass = 1; pass <= 2; pass++) {  // tiny tables first, then small ones
     for (int t = 0; t < tb_all.num_tables; t++) {
-      if (tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) == pass) {
+      if (mode != APPLY_SGDX && tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) == pass) {
         ts.t[ts.num_tables++] = tb_all.t[t];
         n_tiny += pass == 1;
       }
@@ -749,14 +855,16 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
   }
   // key order: the tables far larger than L2 first, then the L2-resident ones (see mix_cta)
   uint64_t rows_l = 0, n = 0, n_stream = 0;
+  int src_table[FFEMB_MAX_TABLES];  // position in the caller's list of the k-th table in key order
   for (int pass = 0; pass < 2; pass++) {
     for (int t = 0; t < tb_all.num_tables; t++) {
-      if (tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) != 0) continue;
+      if (mode != APPLY_SGDX && tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) != 0) continue;
       const bool streams = tb_all.t[t].R * D * 4 > kStreamTableBytes;
       if (streams != (pass == 0)) continue;
       TableDesc &d = tb.t[tb.num_tables];
       d = tb_all.t[t];
       d.lookup_base = (uint32_t)n;
+      src_table[tb.num_tables] = t;
       tb.row_base[tb.num_tables++] = rows_l;
       rows_l += (uint64_t)d.R;
       n += (uint64_t)B * d.L;
@@ -770,14 +878,29 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
     const int rc = launch_backward_small(ts, n_tiny, D, B, aggr, lr, mode, (float *)((char *)ws + c.total), s);
     if (rc) return rc;
   }
-  if (n == 0) return FFEMB_OK;
-  if (wide_keys(rows)) {
-    return mode == APPLY_SGD
-               ? dispatch_g<uint64_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream)
-               : dispatch_g<uint64_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream);
+  if (mode == APPLY_SGDX) {
+    // optimizer arguments in key order of the tables, copied to the tail of the workspace (pageable
+    // source: the copy is staged before cudaMemcpyAsync returns)
+    OptArgs o = *opt_host;
+    for (int k = 0; k < tb.num_tables; k++) {
+      o.V[k] = opt_host->V[src_table[k]];
+      o.touched[k] = opt_host->touched[src_table[k]];
+    }
+    OptArgs *oa = (OptArgs *)((char *)ws + c.total + small_partials_bound(D));
+    cudaError_t e = cudaMemcpyAsync(oa, &o, sizeof(o), cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) return cuda_fail(e, "optimizer arguments upload");
+    int rc = FFEMB_OK;
+    if (n > 0)
+      rc = wide_keys(rows) ? dispatch_wide(tb, (int)D, B, aggr, o.lr, n, rows, c, s, stage, (int64_t)n_stream, oa, APPLY_SGDX)
+                           : dispatch_g<uint32_t, APPLY_SGDX>(tb, (int)D, B, aggr, o.lr, n, rows, c, s, stage, (int64_t)n_stream, oa);
+    if (rc) return rc;
+    return launch_sgdx_untouched(tb, (int)D, o, s);
   }
-  return mode == APPLY_SGD ? dispatch_g<uint32_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream)
-                           : dispatch_g<uint32_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream);
+  if (n == 0) return FFEMB_OK;
+  if (wide_keys(rows))
+    return dispatch_wide(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream, nullptr, (int)mode);
+  return mode == APPLY_SGD ? dispatch_g<uint32_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream, nullptr)
+                           : dispatch_g<uint32_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream, nullptr);
 }
 
 // ---- the atomic comparison: reference-equivalent unordered scatter ---------------------------
@@ -864,4 +987,5 @@ int launch_backward_atomic(const TableBatch &tb, int64_t D64, int64_t B, int agg
   return cuda_fail(cudaGetLastError(), "atomic backward launch");
 }
 
+#endif  // !FFEMB_BACKWARD_WIDE_TU
 }  // namespace ffemb

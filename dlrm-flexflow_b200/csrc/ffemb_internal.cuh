@@ -74,12 +74,52 @@ int launch_forward(const TableBatch &tb, int64_t D, int64_t B, int aggr, const O
 int launch_exchange_backward(const TableBatch &tb, int64_t D, const float *dx, int64_t n, int64_t first,
                              int64_t stride, cudaStream_t s);
 int launch_backward_atomic(const TableBatch &tb, int64_t D, int64_t B, int aggr, cudaStream_t s);
-enum ApplyMode { APPLY_SGD = 0, APPLY_GRAD = 1 };
+enum ApplyMode { APPLY_SGD = 0, APPLY_GRAD = 1, APPLY_SGDX = 2 };
+// APPLY_SGDX: the reference's full sgd_update (/root/reference/src/runtime/optimizer_kernel.cu:23-41:
+// weight decay, momentum, nesterov) on the rows a step touches; the rows it does not touch get the
+// same formula with a zero gradient in sgdx_untouched (ffemb_backward.cu).  Lives in device memory
+// (tail of the caller's workspace) so the kernels' parameter space stays as it is.
+struct OptArgs {
+  float lr, wd, mom;
+  int32_t nesterov;
+  float *V[FFEMB_MAX_TABLES];           // momentum buffer of table t ([R][D]); unused when mom == 0
+  uint32_t *touched[FFEMB_MAX_TABLES];  // bit r of table t: row r was updated by the sparse pass
+};
+// one element of sgd_update, contracted as nvcc contracts the reference (FFMA each):
+//   gt = WGrad + wd*W ; V = V*mom + gt ; gt = nesterov ? gt + mom*V : V ; W -= lr*gt
+__device__ __forceinline__ float sgdx_elem(float w, float g, float &v, float lr, float wd, float mom, bool nesterov) {
+  float gt = fmaf(wd, w, g);
+  if (mom > 0.0f) {
+    v = fmaf(v, mom, gt);
+    gt = nesterov ? fmaf(mom, v, gt) : v;
+  }
+  return fmaf(-lr, gt, w);
+}
+// the 16-byte fragment at wp (table row of table t, key = global row id): general update + mark the row
+__device__ __forceinline__ float4 sgdx_fragment(const OptArgs *oa, int t, const float *table, float *wp,
+                                                float4 w, float4 g, uint64_t local_row, bool mark) {
+  const float lr = oa->lr, wd = oa->wd, mom = oa->mom;
+  const bool nes = oa->nesterov != 0;
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  float *vp = nullptr;
+  if (mom > 0.0f) {
+    vp = oa->V[t] + (wp - table);
+    v = *reinterpret_cast<const float4 *>(vp);
+  }
+  float4 o;
+  o.x = sgdx_elem(w.x, g.x, v.x, lr, wd, mom, nes);
+  o.y = sgdx_elem(w.y, g.y, v.y, lr, wd, mom, nes);
+  o.z = sgdx_elem(w.z, g.z, v.z, lr, wd, mom, nes);
+  o.w = sgdx_elem(w.w, g.w, v.w, lr, wd, mom, nes);
+  if (vp) *reinterpret_cast<float4 *>(vp) = v;
+  if (mark) atomicOr(oa->touched[t] + (local_row >> 5), 1u << (local_row & 31));
+  return o;
+}
 // stage: the sort depends on the indices only, so it can be enqueued ahead of the output-grads
 enum { STAGE_ALL = 0, STAGE_SORT = 1, STAGE_APPLY = 2 };
 int launch_backward_sorted(const TableBatch &tb, int64_t D, int64_t B, int aggr, float lr,
                            ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s,
-                           int stage = STAGE_ALL);
+                           int stage = STAGE_ALL, const OptArgs *opt_host = nullptr);
 int launch_load_sparse(const ffemb_table_t *tables, int num_tables, const int64_t *full, int64_t row_len,
                        const int32_t *sample_ids, int64_t first_sample, int64_t B, cudaStream_t s);
 size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t D);

@@ -30,7 +30,7 @@ template <typename K, int G, int MODE, bool AVG, int S>
 __global__ void __launch_bounds__(L1Threads<G>::value)
 reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
                     const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
-                    float *rows_out, uint32_t split) {
+                    float *rows_out, uint32_t split, const OptArgs *oa) {
   constexpr int THREADS = L1Threads<G>::value;
   constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
   constexpr K INV = KeyTraits<K>::INV;
@@ -120,6 +120,10 @@ reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__
             if (MODE == APPLY_SGD) {  // W -= lr*gt, contracted like the reference's FFMA
               o.x = fmaf(-acc.x, lr, o.x); o.y = fmaf(-acc.y, lr, o.y);
               o.z = fmaf(-acc.z, lr, o.z); o.w = fmaf(-acc.w, lr, o.w);
+            } else if (MODE == APPLY_SGDX) {
+              const uint64_t key = (uint64_t)keys[t0 + e];
+              const int t = find_table(tb, key);
+              o = sgdx_fragment(oa, t, tb.t[t].table, d.wp + 4 * sl, o, acc, key - tb.row_base[t], sl == 0);
             } else {
               f4_add(o, acc);
             }

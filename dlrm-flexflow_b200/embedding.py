@@ -209,6 +209,32 @@ class EmbeddingCollection:
             check(fn(sub, e - s, self.dim, batch, self.aggr, float(lr), ws.data_ptr(), ws.numel(),
                      _stream_ptr(stream)))
 
+    def backward_sgdx(self, indices, out_grads, lr, weight_decay=0.0, momentum=0.0, nesterov=False,
+                      V=None, stream=None):
+        """Backward fused with the reference's full sgd_update (weight decay / momentum / nesterov,
+        /root/reference/src/runtime/optimizer_kernel.cu:23-41) — every row of every table changes.
+        V: momentum buffers ([R][D] per table, zero-initialised by the caller like
+        SGDOptimizer::init, src/runtime/optimizer.cc:50-87); required when momentum > 0."""
+        from .binding import ffemb_sgd_t
+        batch = int(indices[0].shape[0])
+        T = len(self.weights)
+        if T > B.FFEMB_MAX_TABLES:
+            raise ValueError("at most 64 tables per call")
+        arr = self._descs(indices, out_grads, self.weights, batch)
+        if not hasattr(self, "_touched"):
+            self._touched = [torch.zeros(max(1, int(lib().ffemb_sgd_touched_words(int(w.shape[0])))),
+                                         dtype=torch.int32, device=self.device) for w in self.weights]
+        opt = ffemb_sgd_t(float(lr), float(weight_decay), float(momentum), int(bool(nesterov)))
+        tp = (C.c_void_p * T)(*[t.data_ptr() for t in self._touched])
+        vp = None
+        if momentum > 0:
+            if V is None or len(V) != T:
+                raise ValueError("momentum > 0 needs one momentum buffer per table")
+            vp = (C.c_void_p * T)(*[_req(v, torch.float32, "V").data_ptr() for v in V])
+        ws = self._workspaces(batch)[0]
+        check(lib().ffemb_backward_sgdx_batched(arr, T, self.dim, batch, self.aggr, C.byref(opt), vp, tp,
+                                                ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
+
     # ---- straight into / out of the Concat tensors (one GPU; ffemb_forward_concat / _backward_sgd_concat)
     def _concat_descs(self, indices, batch, cols):
         T = len(self.weights)

@@ -180,6 +180,31 @@ FFEMB_API int ffemb_backward_dense_batched(const ffemb_table_t *tables, int num_
                                  int64_t B, int aggr, void *workspace, size_t workspace_bytes,
                                  ffemb_stream_t stream);
 
+/* ---- backward fused with the reference's FULL sgd_update ------------------------
+ * ffemb_backward_sgd* is exact only for momentum == weight_decay == 0; with either set, sgd_update
+ * (src/runtime/optimizer_kernel.cu:23-41) changes EVERY row every step:
+ *     gt = WGrad + weight_decay*W;  if (momentum > 0) { V = V*momentum + gt;
+ *     gt = nesterov ? gt + momentum*V : V; }   W -= lr*gt
+ * This entry point keeps those semantics without a dense gradient: rows the step touches get the
+ * formula with their summed gradient inside the sorted segmented reduction (and are marked in a
+ * bitmap), every other row gets it with WGrad = 0 in one streaming pass over W (and V) that also
+ * clears the bitmap.  HBM traffic 8 (16 with momentum) bytes per table element instead of the
+ * reference's 4 (zero-fill) + 12 (20), plus the atomics.  Same FFMA contraction as the reference's
+ * kernel, so single-lookup rows and untouched rows are bit-identical to it.
+ *   V[t]       : momentum buffer of table t, [R][D] floats (ignored when momentum == 0; the reference
+ *                allocates it zero-initialised, src/runtime/optimizer.cc:50-87)
+ *   touched[t] : ffemb_sgd_touched_words(R) 32-bit words, all zero on entry, all zero on return
+ * Every table goes through the sorted path; no split (prepare) form.                             */
+typedef struct ffemb_sgd {
+  float lr, weight_decay, momentum;
+  int32_t nesterov;
+} ffemb_sgd_t;
+FFEMB_API int64_t ffemb_sgd_touched_words(int64_t R);
+FFEMB_API int ffemb_backward_sgdx_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                                int aggr, const ffemb_sgd_t *opt, float *const *V,
+                                uint32_t *const *touched, void *workspace, size_t workspace_bytes,
+                                ffemb_stream_t stream);
+
 /* ---- straight into / out of the Concat operator's tensors (one GPU) ----------------
  * The reference's DLRM feeds every pooled output through Concat (interaction "cat",
  * examples/cpp/DLRM/dlrm.cc:49-61): forward copies each [B][D] input into its column block of the
@@ -249,7 +274,8 @@ FFEMB_API int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int6
 #define FFEMB_PHASE_SMALL 6     /* bag-major backward of tables whose gradient fits on chip */
 #define FFEMB_PHASE_EXCHANGE 7  /* output-grad push over peer memory */
 #define FFEMB_PHASE_INPUT 8     /* sparse-input delivery (ffemb_load_sparse_inputs) */
-#define FFEMB_NUM_PHASES 9
+#define FFEMB_PHASE_DENSE 9     /* general SGD: the pass over the rows a step did not touch */
+#define FFEMB_NUM_PHASES 10
 FFEMB_API int ffemb_profile_enable(int on);
 FFEMB_API int ffemb_profile_collect(float *ms_per_phase, int64_t *launches_per_phase);
 FFEMB_API int64_t ffemb_launch_count(void);

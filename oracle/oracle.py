@@ -130,6 +130,16 @@ def sgd_update(W, Wgrad, lr, weight_decay=0.0, use_fma=True):
     return W
 
 
+def sgd_update_full(W, Wgrad, V, lr, weight_decay=0.0, momentum=0.0, nesterov=False, use_fma=True):
+    """sgd_update with momentum (src/runtime/optimizer_kernel.cu:23-41). Returns (new W, new V)."""
+    W = np.array(W, np.float32, order="C", copy=True)
+    V = np.array(V, np.float32, order="C", copy=True)
+    Wgrad = np.ascontiguousarray(Wgrad, np.float32)
+    lib().oracle_sgd_update(W.size, lr, weight_decay, momentum, int(nesterov), Wgrad.reshape(-1),
+                            V.ctypes.data, W.reshape(-1), int(use_fma))
+    return W, V
+
+
 def reference_step(idx, outgrad, W, aggr=AGGR_SUM, lr=0.01, use_fma=True):
     """zero-fill -> embed_backward -> sgd_update: the table after one reference step."""
     W = np.array(W, np.float32, order="C", copy=True)
@@ -315,6 +325,10 @@ def _bind_gpu(L):
         L.ffref_gpu_sgd_task.restype = None
         L.ffref_gpu_set_workspace.argtypes = [_vp, C.c_size_t]
         L.ffref_gpu_set_workspace.restype = None
+        if hasattr(L, "ffref_gpu_sgd_task_full"):
+            L.ffref_gpu_sgd_task_full.argtypes = [_vp, _vp, _vp, _i64, _i64, C.c_double, C.c_double,
+                                                  C.c_double, _int]
+            L.ffref_gpu_sgd_task_full.restype = None
         if hasattr(L, "ffref_gpu_load_sparse_input"):  # not in the drop-in library
             L.ffref_gpu_load_sparse_input.argtypes = [_vp, _i64, _int, _int, _int, _int, _int, _vp]
     return L

@@ -239,4 +239,18 @@ void ffref_gpu_sgd_task(const float *Wgrad, float *W, int64_t d0, int64_t d1, do
   SGDOptimizer::ps_update_task(&f.task, f.regions, NULL, &f.runtime);
 }
 
+/* The same task with the optimizer's momentum / nesterov / weight decay: with momentum > 0 the task
+ * takes a third region, the momentum buffer V (src/runtime/optimizer_kernel.cu:49-56,84-90).      */
+void ffref_gpu_sgd_task_full(const float *Wgrad, float *W, float *V, int64_t d0, int64_t d1, double lr,
+                             double weight_decay, double momentum, int nesterov) {
+  TaskFrame f;
+  f.add((void *)Wgrad, d0, d1);
+  f.add((void *)W, d0, d1);
+  if (momentum > 0.0) f.add((void *)V, d0, d1);
+  SGDOptimizer opt(NULL, lr, momentum, nesterov != 0, weight_decay);
+  f.task.args = &opt;
+  f.task.arglen = sizeof(opt);
+  SGDOptimizer::ps_update_task(&f.task, f.regions, NULL, &f.runtime);
+}
+
 }  /* extern "C" */

@@ -568,3 +568,85 @@ def test_concat_direct_errors(ffemb, torch_cuda):
         coll.backward_sgd_concat(idx, dx, 0.01, cols=[2])       # 16-byte fragments must stay aligned
     with pytest.raises(ffemb.FFEmbError):
         coll.forward_concat(idx, dx, cols=[20])
+
+
+# ---------------------------------------------------------------------------------------------
+# full sgd_update fused with the backward: weight decay / momentum / nesterov
+# ---------------------------------------------------------------------------------------------
+SGDX_CASES = [  # weight_decay, momentum, nesterov
+    (1e-3, 0.0, False), (0.0, 0.9, False), (1e-3, 0.9, False), (5e-4, 0.8, True), (0.0, 0.0, False)]
+
+
+@pytest.mark.parametrize("wd,mom,nesterov", SGDX_CASES)
+@pytest.mark.parametrize("aggr", [21, 22])
+def test_backward_sgdx_two_steps_vs_reference_optimizer(ffemb, oracle, torch_cuda, wd, mom, nesterov, aggr):
+    """Two consecutive steps (the second sees the first one's momentum) against the oracle's
+    zero-fill -> embed_backward -> sgd_update restatement, and — where oracle/_ref is built — against
+    the reference's own SGDOptimizer::ps_update_task fed with the reference's own embed_backward:
+    rows with at most one lookup and rows never touched are BIT-IDENTICAL (same FFMA contraction);
+    repeated rows within 1e-6 (summation order of the gradient).  The touched bitmap returns zero."""
+    torch = torch_cuda
+    D, B, lr = 64, 3000, 0.05
+    rows, bags = [5, 60000, 977, 33], [1, 2, 7, 20]
+    T = len(rows)
+    Ws = [make_inputs(R, D, L, B, seed=900 + t)[0] for t, (R, L) in enumerate(zip(rows, bags))]
+    steps = [[make_inputs(R, D, L, B, seed=910 + 10 * k + t)[1:] for t, (R, L) in enumerate(zip(rows, bags))]
+             for k in range(2)]
+    dW = [dev(torch, w) for w in Ws]
+    dV = [torch.zeros_like(w) for w in dW]
+    coll = ffemb.EmbeddingCollection(dW, bags, aggr)
+    oW = [w.copy() for w in Ws]
+    oV = [np.zeros_like(w) for w in Ws]
+    have_ref = oracle.ref_gpu_available() and hasattr(oracle.ref_gpu(), "ffref_gpu_sgd_task_full")
+    rW = [dev(torch, w) for w in Ws]
+    rV = [torch.zeros_like(w) for w in rW]
+    multi = [np.zeros(R, bool) for R in rows]
+    for k in range(2):
+        idxs = [steps[k][t][0] for t in range(T)]
+        gs = [steps[k][t][1] for t in range(T)]
+        coll.backward_sgdx([dev(torch, i) for i in idxs], [dev(torch, g) for g in gs], lr, wd, mom, nesterov,
+                           V=dV if mom > 0 else None)
+        for t in range(T):
+            grad = oracle.backward_dense(idxs[t], gs[t], rows[t], aggr)
+            oW[t], oV[t] = oracle.sgd_update_full(oW[t], grad, oV[t], lr, wd, mom, nesterov)
+            multi[t] |= np.bincount(idxs[t].reshape(-1), minlength=rows[t]) > 1
+            if have_ref:
+                rg = torch.zeros_like(rW[t])
+                oracle.ref_gpu().ffref_gpu_backward_task(dev(torch, idxs[t]).data_ptr(), dev(torch, gs[t]).data_ptr(),
+                                                         rg.data_ptr(), bags[t], D, B, rows[t], aggr)
+                oracle.ref_gpu().ffref_gpu_sgd_task_full(rg.data_ptr(), rW[t].data_ptr(), rV[t].data_ptr(), D, rows[t],
+                                                         lr, wd, mom, int(nesterov))
+        torch.cuda.synchronize()
+    for t in range(T):
+        got, gotV = dW[t].cpu().numpy(), dV[t].cpu().numpy()
+        once = ~multi[t]
+        assert np.array_equal(got[once], oW[t][once]), t
+        tol = REL_TOL * max(np.abs(oW[t]).max(), 1e-30) * 4
+        assert np.all(np.abs(got - oW[t]) <= tol), t
+        if mom > 0:
+            assert np.array_equal(gotV[once], oV[t][once]), t
+            assert np.all(np.abs(gotV - oV[t]) <= REL_TOL * np.abs(oV[t]).max() * 4), t
+        if have_ref:
+            ref = rW[t].cpu().numpy()
+            assert np.array_equal(got[once], ref[once]), t
+            assert np.all(np.abs(got - ref) <= tol), t
+        assert int(coll._touched[t].abs().sum().item()) == 0, t
+
+
+def test_backward_sgdx_plain_settings_match_the_fused_sgd_path(ffemb, torch_cuda):
+    """weight_decay = momentum = 0: the general path == ffemb_backward_sgd_batched on single-lookup
+    rows bit for bit (untouched rows get W -= lr*0, a bit-identical no-op)."""
+    torch = torch_cuda
+    D, B = 128, 2000
+    rows, bags = [50000, 7], [1, 3]
+    Ws, idxs, gs = [], [], []
+    for t, (R, L) in enumerate(zip(rows, bags)):
+        W, idx, g = make_inputs(R, D, L, B, seed=950 + t)
+        Ws.append(W), idxs.append(dev(torch, idx)), gs.append(dev(torch, g))
+    a, b = [dev(torch, w) for w in Ws], [dev(torch, w) for w in Ws]
+    ffemb.EmbeddingCollection(a, bags).backward_sgd(idxs, gs, 0.01)
+    ffemb.EmbeddingCollection(b, bags).backward_sgdx(idxs, gs, 0.01)
+    torch.cuda.synchronize()
+    cnt = np.bincount(idxs[0].cpu().numpy().reshape(-1), minlength=rows[0])
+    assert np.array_equal(a[0].cpu().numpy()[cnt <= 1], b[0].cpu().numpy()[cnt <= 1])
+    assert torch.allclose(a[1], b[1], rtol=1e-6, atol=1e-8)
