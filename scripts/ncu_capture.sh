@@ -8,7 +8,7 @@ mkdir -p gpurun_out
 CMD="python bench.py --rows-cap 4000000 --steps 2 --warmup 1 --no-e2e --no-cpu"
 $CMD > gpurun_out/${TAG}_plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain.log; exit 1; }
 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
-ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:"fwd_kernel|reduce1_kernel|keygen_kernel|reduce_level_kernel|reduce_tail_kernel|bwd_small" -c 8 -o gpurun_out/${TAG}_full $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
+ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:"fwd_kernel|reduce1_|keygen_kernel|reduce_level_kernel|reduce_tail_kernel|bwd_small|bwd_tiny|small_apply" -c 11 -o gpurun_out/${TAG}_full $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
 ncu -i gpurun_out/${TAG}_full.ncu-rep --page raw --csv > gpurun_out/${TAG}_full_raw.csv 2>/dev/null
 tail -1 gpurun_out/${TAG}_plain.log | cut -c1-300; tail -3 gpurun_out/${TAG}_ncu2.log; wc -l gpurun_out/${TAG}_launches.csv
 # cfg5 (Zipf, AVG, bag 64) forward only, full size: which unit bounds it under hot-row skew
