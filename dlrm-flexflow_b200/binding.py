@@ -33,6 +33,11 @@ class ffemb_sgd_t(C.Structure):
                 ("nesterov", C.c_int32)]
 
 
+class ffemb_adam_t(C.Structure):
+    _fields_ = [("alpha_t", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float),
+                ("weight_decay", C.c_float), ("epsilon", C.c_float)]
+
+
 class ffemb_exchange_t(C.Structure):
     _fields_ = [("peer_x", C.c_void_p * FFEMB_MAX_PEERS), ("num_peers", C.c_int32),
                 ("reserved", C.c_int32), ("batch_per_peer", C.c_int64), ("row_stride", C.c_int64)]
@@ -99,6 +104,8 @@ def lib():
     L.ffemb_sgd_touched_words.restype = i64
     L.ffemb_backward_sgdx_batched.argtypes = [tp, i32, i64, i64, i32, C.POINTER(ffemb_sgd_t), C.POINTER(vp),
                                               C.POINTER(vp), vp, sz, vp]
+    L.ffemb_backward_adam_batched.argtypes = [tp, i32, i64, i64, i32, C.POINTER(ffemb_adam_t), C.POINTER(vp),
+                                              C.POINTER(vp), C.POINTER(vp), vp, sz, vp]
     L.ffemb_forward_concat.argtypes = [tp, i32, i64, i64, i32, vp, i64, vp]
     L.ffemb_backward_sgd_concat.argtypes = [tp, i32, i64, i64, i32, f32, vp, i64, i32, vp, sz, vp]
     L.ffemb_backward_dense_batched.argtypes = [tp, i32, i64, i64, i32, vp, sz, vp]

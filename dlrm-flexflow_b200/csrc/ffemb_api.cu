@@ -315,6 +315,41 @@ int ffemb_backward_sgdx_batched(const ffemb_table_t *tables, int num_tables, int
                                 (cudaStream_t)stream, STAGE_ALL, &o);
 }
 
+int ffemb_backward_adam_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                                int aggr, const ffemb_adam_t *opt, float *const *M, float *const *V,
+                                uint32_t *const *touched, void *workspace, size_t workspace_bytes,
+                                ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack(tables, num_tables, D, B, aggr, tb);
+  if (rc) return rc;
+  if (!opt || !touched || !M || !V) {
+    set_error("backward_adam: optimizer arguments missing (opt=%p M=%p V=%p touched=%p)", (const void *)opt,
+              (const void *)M, (const void *)V, (const void *)touched);
+    return FFEMB_EINVAL;
+  }
+  OptArgs o;
+  memset(&o, 0, sizeof(o));
+  o.adam = 1;
+  o.alpha_t = opt->alpha_t;
+  o.beta1 = opt->beta1;
+  o.beta2 = opt->beta2;
+  o.wd = opt->weight_decay;
+  o.eps = opt->epsilon;
+  for (int t = 0; t < num_tables; t++) {
+    if (tables[t].R <= 0) continue;
+    if (!touched[t] || (uintptr_t)touched[t] % 4 != 0 || !M[t] || !V[t] ||
+        ((uintptr_t)M[t] | (uintptr_t)V[t]) % 16 != 0) {
+      set_error("backward_adam: table %d needs a touched bitmap and 16-byte aligned M and V buffers", t);
+      return FFEMB_EINVAL;
+    }
+    o.M[t] = M[t];
+    o.V[t] = V[t];
+    o.touched[t] = touched[t];
+  }
+  return launch_backward_sorted(tb, D, B, aggr, 0.f, APPLY_SGDX, workspace, workspace_bytes,
+                                (cudaStream_t)stream, STAGE_ALL, &o);
+}
+
 int ffemb_forward_concat(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B, int aggr,
                          float *x, int64_t row_stride, ffemb_stream_t stream) {
   ffemb_exchange_t ex;

@@ -624,8 +624,9 @@ size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t
 // fill) + 12 (20) (sgd_update) + the atomics — and no dense gradient exists.
 template <int G>
 __global__ void __launch_bounds__(256)
-sgdx_untouched_kernel(float *__restrict__ W, float *__restrict__ V, uint32_t *__restrict__ touched,
-                      int64_t R, int D, float lr, float wd, float mom, int nesterov) {
+sgdx_untouched_kernel(float *__restrict__ W, float *__restrict__ V, float *__restrict__ M,
+                      uint32_t *__restrict__ touched, int64_t R, int D, float lr, float wd, float mom,
+                      int nesterov, int adam, float alpha_t, float beta1, float beta2, float eps) {
   constexpr int SLOTS = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int sub = lane / G, sl = lane % G;
@@ -642,6 +643,19 @@ sgdx_untouched_kernel(float *__restrict__ W, float *__restrict__ V, uint32_t *__
       for (int c4 = sl; c4 < D4; c4 += G) {
         float *wp = W + row * (int64_t)D + 4 * c4;
         float4 w = ld_row_hint(wp, pol), v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (adam) {  // adam_update with a zero gradient: M and V decay, W moves by alpha_t*M/(sqrt(V)+eps)
+          float *mp = M + row * (int64_t)D + 4 * c4, *vq = V + row * (int64_t)D + 4 * c4;
+          float4 m = ld_row_hint(mp, pol), o;
+          v = ld_row_hint(vq, pol);
+          o.x = adam_elem(w.x, 0.0f, m.x, v.x, alpha_t, beta1, beta2, wd, eps);
+          o.y = adam_elem(w.y, 0.0f, m.y, v.y, alpha_t, beta1, beta2, wd, eps);
+          o.z = adam_elem(w.z, 0.0f, m.z, v.z, alpha_t, beta1, beta2, wd, eps);
+          o.w = adam_elem(w.w, 0.0f, m.w, v.w, alpha_t, beta1, beta2, wd, eps);
+          st_row_hint(wp, o, pol);
+          st_row_hint(mp, m, pol);
+          st_row_hint(vq, v, pol);
+          continue;
+        }
         float *vp = nullptr;
         if (mom > 0.0f) {
           vp = V + row * (int64_t)D + 4 * c4;
@@ -671,7 +685,8 @@ static int launch_sgdx_untouched(const TableBatch &tb, int D, const OptArgs &o, 
     const int64_t nwords = (R + 31) / 32;
     const unsigned grid = (unsigned)((nwords + 7) / 8 < 148 * 8 ? (nwords + 7) / 8 : 148 * 8);
     auto go = [&](auto kern) {
-      kern<<<grid, 256, 0, s>>>(tb.t[t].table, o.V[t], o.touched[t], R, D, o.lr, o.wd, o.mom, o.nesterov);
+      kern<<<grid, 256, 0, s>>>(tb.t[t].table, o.V[t], o.M[t], o.touched[t], R, D, o.lr, o.wd, o.mom, o.nesterov,
+                                o.adam, o.alpha_t, o.beta1, o.beta2, o.eps);
     };
     if (D4 <= 1) go(sgdx_untouched_kernel<1>);
     else if (D4 <= 2) go(sgdx_untouched_kernel<2>);
@@ -835,7 +850,7 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
     return FFEMB_EINVAL;
   }
   const size_t need = backward_workspace_bytes(n_all, (int64_t)tb_all.row_base[tb_all.num_tables], D);
-  if (!ws || ((uintptr_t)ws & 255) || ws_bytes < need) {
+  if (n_all > 0 && (!ws || ((uintptr_t)ws & 255) || ws_bytes < need)) {
     set_error("workspace: need %zu bytes, 256-byte aligned (got %zu at %p)", need, ws_bytes, ws);
     return FFEMB_EWORKSPACE;
   }
@@ -884,15 +899,17 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
     OptArgs o = *opt_host;
     for (int k = 0; k < tb.num_tables; k++) {
       o.V[k] = opt_host->V[src_table[k]];
+      o.M[k] = opt_host->M[src_table[k]];
       o.touched[k] = opt_host->touched[src_table[k]];
     }
-    OptArgs *oa = (OptArgs *)((char *)ws + c.total + small_partials_bound(D));
-    cudaError_t e = cudaMemcpyAsync(oa, &o, sizeof(o), cudaMemcpyHostToDevice, s);
-    if (e != cudaSuccess) return cuda_fail(e, "optimizer arguments upload");
     int rc = FFEMB_OK;
-    if (n > 0)
+    if (n > 0) {  // (an empty batch has no sparse pass; every row still gets the zero-gradient update)
+      OptArgs *oa = (OptArgs *)((char *)ws + c.total + small_partials_bound(D));
+      cudaError_t e = cudaMemcpyAsync(oa, &o, sizeof(o), cudaMemcpyHostToDevice, s);
+      if (e != cudaSuccess) return cuda_fail(e, "optimizer arguments upload");
       rc = wide_keys(rows) ? dispatch_wide(tb, (int)D, B, aggr, o.lr, n, rows, c, s, stage, (int64_t)n_stream, oa, APPLY_SGDX)
                            : dispatch_g<uint32_t, APPLY_SGDX>(tb, (int)D, B, aggr, o.lr, n, rows, c, s, stage, (int64_t)n_stream, oa);
+    }
     if (rc) return rc;
     return launch_sgdx_untouched(tb, (int)D, o, s);
   }

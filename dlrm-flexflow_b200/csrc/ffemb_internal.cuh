@@ -82,9 +82,26 @@ enum ApplyMode { APPLY_SGD = 0, APPLY_GRAD = 1, APPLY_SGDX = 2 };
 struct OptArgs {
   float lr, wd, mom;
   int32_t nesterov;
-  float *V[FFEMB_MAX_TABLES];           // momentum buffer of table t ([R][D]); unused when mom == 0
+  int32_t adam;                         // 0: sgd_update; 1: adam_update (optimizer_kernel.cu:206-226)
+  float alpha_t, beta1, beta2, eps;     // Adam: alpha_t is the bias-corrected step of AdamOptimizer::next
+  float *V[FFEMB_MAX_TABLES];           // SGD: momentum buffer ([R][D], unused when mom == 0); Adam: V
+  float *M[FFEMB_MAX_TABLES];           // Adam: first moment
   uint32_t *touched[FFEMB_MAX_TABLES];  // bit r of table t: row r was updated by the sparse pass
 };
+// one element of adam_update, operation for operation as nvcc compiles the reference
+// (SASS of oracle/_ref/optimizer_kernel_cu.o): gt = FFMA(W, wd, g); t1 = gt*(1-b1); t2 = gt*(1-b2);
+// gg = gt*t2; M = FFMA(M, b1, t1); V = FFMA(V, b2, gg); W = W - (M*alpha_t) / (sqrtf(V) + eps)
+// with IEEE sqrt and division.  Intrinsics: nothing here may be re-contracted.
+__device__ __forceinline__ float adam_elem(float w, float g, float &m, float &v, float alpha_t, float b1,
+                                           float b2, float wd, float eps) {
+  const float gt = __fmaf_rn(w, wd, g);
+  const float t1 = __fmul_rn(gt, __fadd_rn(-b1, 1.0f));
+  const float t2 = __fmul_rn(gt, __fadd_rn(-b2, 1.0f));
+  const float gg = __fmul_rn(gt, t2);
+  m = __fmaf_rn(m, b1, t1);
+  v = __fmaf_rn(v, b2, gg);
+  return __fadd_rn(w, -__fdiv_rn(__fmul_rn(m, alpha_t), __fadd_rn(__fsqrt_rn(v), eps)));
+}
 // one element of sgd_update, contracted as nvcc contracts the reference (FFMA each):
 //   gt = WGrad + wd*W ; V = V*mom + gt ; gt = nesterov ? gt + mom*V : V ; W -= lr*gt
 __device__ __forceinline__ float sgdx_elem(float w, float g, float &v, float lr, float wd, float mom, bool nesterov) {
@@ -98,6 +115,19 @@ __device__ __forceinline__ float sgdx_elem(float w, float g, float &v, float lr,
 // the 16-byte fragment at wp (table row of table t, key = global row id): general update + mark the row
 __device__ __forceinline__ float4 sgdx_fragment(const OptArgs *oa, int t, const float *table, float *wp,
                                                 float4 w, float4 g, uint64_t local_row, bool mark) {
+  if (oa->adam) {
+    const float a = oa->alpha_t, b1 = oa->beta1, b2 = oa->beta2, wd = oa->wd, eps = oa->eps;
+    float *mp = oa->M[t] + (wp - table), *vp = oa->V[t] + (wp - table);
+    float4 m = *reinterpret_cast<const float4 *>(mp), v = *reinterpret_cast<const float4 *>(vp), o;
+    o.x = adam_elem(w.x, g.x, m.x, v.x, a, b1, b2, wd, eps);
+    o.y = adam_elem(w.y, g.y, m.y, v.y, a, b1, b2, wd, eps);
+    o.z = adam_elem(w.z, g.z, m.z, v.z, a, b1, b2, wd, eps);
+    o.w = adam_elem(w.w, g.w, m.w, v.w, a, b1, b2, wd, eps);
+    *reinterpret_cast<float4 *>(mp) = m;
+    *reinterpret_cast<float4 *>(vp) = v;
+    if (mark) atomicOr(oa->touched[t] + (local_row >> 5), 1u << (local_row & 31));
+    return o;
+  }
   const float lr = oa->lr, wd = oa->wd, mom = oa->mom;
   const bool nes = oa->nesterov != 0;
   float4 v = make_float4(0.f, 0.f, 0.f, 0.f);

@@ -235,6 +235,28 @@ class EmbeddingCollection:
         check(lib().ffemb_backward_sgdx_batched(arr, T, self.dim, batch, self.aggr, C.byref(opt), vp, tp,
                                                 ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
 
+    def backward_adam(self, indices, out_grads, alpha_t, M, V, beta1=0.9, beta2=0.999, weight_decay=0.0,
+                      epsilon=1e-8, stream=None):
+        """Backward fused with the reference's adam_update
+        (/root/reference/src/runtime/optimizer_kernel.cu:206-226).  alpha_t: the bias-corrected step
+        of this iteration (AdamOptimizer::next); M, V: [R][D] moment buffers per table."""
+        from .binding import ffemb_adam_t
+        batch = int(indices[0].shape[0])
+        T = len(self.weights)
+        if T > B.FFEMB_MAX_TABLES or len(M) != T or len(V) != T:
+            raise ValueError("one M and one V buffer per table, at most 64 tables per call")
+        arr = self._descs(indices, out_grads, self.weights, batch)
+        if not hasattr(self, "_touched"):
+            self._touched = [torch.zeros(max(1, int(lib().ffemb_sgd_touched_words(int(w.shape[0])))),
+                                         dtype=torch.int32, device=self.device) for w in self.weights]
+        opt = ffemb_adam_t(float(alpha_t), float(beta1), float(beta2), float(weight_decay), float(epsilon))
+        tp = (C.c_void_p * T)(*[t.data_ptr() for t in self._touched])
+        mp = (C.c_void_p * T)(*[_req(m, torch.float32, "M").data_ptr() for m in M])
+        vp = (C.c_void_p * T)(*[_req(v, torch.float32, "V").data_ptr() for v in V])
+        ws = self._workspaces(batch)[0]
+        check(lib().ffemb_backward_adam_batched(arr, T, self.dim, batch, self.aggr, C.byref(opt), mp, vp, tp,
+                                                ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
+
     # ---- straight into / out of the Concat tensors (one GPU; ffemb_forward_concat / _backward_sgd_concat)
     def _concat_descs(self, indices, batch, cols):
         T = len(self.weights)

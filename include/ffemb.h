@@ -205,6 +205,23 @@ FFEMB_API int ffemb_backward_sgdx_batched(const ffemb_table_t *tables, int num_t
                                 uint32_t *const *touched, void *workspace, size_t workspace_bytes,
                                 ffemb_stream_t stream);
 
+/* The same for AdamOptimizer (src/runtime/optimizer_kernel.cu:206-226; the reference's Adam is not
+ * lazy either — with a zero gradient M and V still decay and W still moves):
+ *     gt = WGrad + weight_decay*W;  M = beta1*M + (1-beta1)*gt;  V = beta2*V + (1-beta2)*gt*gt;
+ *     W -= alpha_t * M / (sqrt(V) + epsilon)
+ * alpha_t is the bias-corrected step the host advances once per iteration (AdamOptimizer::next,
+ * src/runtime/optimizer.cc:248-254).  M[t], V[t]: [R][D] floats, zero-initialised by the caller
+ * (AdamOptimizer::init).  Operation-for-operation the reference kernel's SASS (which products are
+ * fused, IEEE sqrt and division), so single-lookup and untouched rows are bit-identical to it.
+ * 24 bytes per table element per step (W, M, V read + written) — the semantics' minimum.          */
+typedef struct ffemb_adam {
+  float alpha_t, beta1, beta2, weight_decay, epsilon;
+} ffemb_adam_t;
+FFEMB_API int ffemb_backward_adam_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                                int aggr, const ffemb_adam_t *opt, float *const *M, float *const *V,
+                                uint32_t *const *touched, void *workspace, size_t workspace_bytes,
+                                ffemb_stream_t stream);
+
 /* ---- straight into / out of the Concat operator's tensors (one GPU) ----------------
  * The reference's DLRM feeds every pooled output through Concat (interaction "cat",
  * examples/cpp/DLRM/dlrm.cc:49-61): forward copies each [B][D] input into its column block of the

@@ -131,6 +131,32 @@ void oracle_sgd_update(int64_t count, float lr, float weight_decay, float moment
   }
 }
 
+/* ---- adam_update: src/runtime/optimizer_kernel.cu:206-226 -----------------------------------
+ *   gt = WGrad[i] + weight_decay*W[i]; mt = beta1*M[i] + (1-beta1)*gt;
+ *   vt = beta2*V[i] + (1-beta2)*gt*gt; M[i] = mt; V[i] = vt; W[i] -= alpha_t*mt/(sqrt(vt)+epsilon)
+ * Rounding follows the SASS nvcc emits for the reference object (cuobjdump of
+ * oracle/_ref/optimizer_kernel_cu.o): gt = FFMA(W, wd, WGrad); t1 = gt*(1-beta1); t2 = gt*(1-beta2);
+ * gg = gt*t2; mt = FFMA(M, beta1, t1); vt = FFMA(V, beta2, gg); num = mt*alpha_t;
+ * W = W - num / (sqrtf(vt) + epsilon) with IEEE sqrt and division, (1-beta) formed in fp32.      */
+void oracle_adam_update(int64_t count, float alpha_t, float beta1, float beta2, float weight_decay,
+                        float epsilon, const float *WGrad, float *M, float *V, float *W) {
+  volatile float omb1 = 1.0f - beta1, omb2 = 1.0f - beta2;
+  for (int64_t i = 0; i < count; i++) {
+    float gt = fmaf(W[i], weight_decay, WGrad[i]);
+    volatile float t1 = gt * omb1;
+    volatile float t2 = gt * omb2;
+    volatile float gg = gt * t2;
+    float mt = fmaf(M[i], beta1, t1);
+    float vt = fmaf(V[i], beta2, gg);
+    M[i] = mt;
+    V[i] = vt;
+    volatile float num = mt * alpha_t;
+    volatile float den = sqrtf(vt) + epsilon;
+    volatile float q = num / den;
+    W[i] = W[i] - q;
+  }
+}
+
 /* One reference training step of one table, as FFModel runs it:
  * zero_gradients (model.cc:1993-1996) -> Embedding::backward -> SGDOptimizer::update.
  * Wgrad is caller-provided scratch of R*D floats.                                             */

@@ -54,6 +54,8 @@ def lib():
         L.oracle_embed_backward_f64.argtypes = [_i64p, _f32p, _f64p, _i64, _i64, _i64, _int, _i64]
         L.oracle_sgd_update.argtypes = [_i64, _f32, _f32, _f32, _int, _f32p, C.c_void_p, _f32p, _int]
         L.oracle_sgd_update.restype = None
+        L.oracle_adam_update.argtypes = [_i64, _f32, _f32, _f32, _f32, _f32, _f32p, _f32p, _f32p, _f32p]
+        L.oracle_adam_update.restype = None
         L.oracle_reference_step.argtypes = [_i64p, _f32p, _f32p, _f32p, _i64, _i64, _i64, _i64,
                                             _int, _f32, _int]
         L.oracle_table_owner.argtypes = [_i64, _i64]
@@ -138,6 +140,26 @@ def sgd_update_full(W, Wgrad, V, lr, weight_decay=0.0, momentum=0.0, nesterov=Fa
     lib().oracle_sgd_update(W.size, lr, weight_decay, momentum, int(nesterov), Wgrad.reshape(-1),
                             V.ctypes.data, W.reshape(-1), int(use_fma))
     return W, V
+
+
+def adam_update(W, Wgrad, M, V, alpha_t, beta1=0.9, beta2=0.999, weight_decay=0.0, epsilon=1e-8):
+    """adam_update (src/runtime/optimizer_kernel.cu:206-226). Returns (new W, new M, new V)."""
+    W, M, V = (np.array(x, np.float32, order="C", copy=True) for x in (W, M, V))
+    Wgrad = np.ascontiguousarray(Wgrad, np.float32)
+    lib().oracle_adam_update(W.size, alpha_t, beta1, beta2, weight_decay, epsilon, Wgrad.reshape(-1),
+                             M.reshape(-1), V.reshape(-1), W.reshape(-1))
+    return W, M, V
+
+
+def adam_alpha_t(alpha, beta1, beta2, step):
+    """AdamOptimizer::next (src/runtime/optimizer.cc:248-254) applied `step` times, in double like there."""
+    b1t = b2t = 1.0
+    a = alpha
+    for _ in range(step):
+        b1t *= beta1
+        b2t *= beta2
+        a = alpha * np.sqrt(1 - b2t) / (1 - b1t)
+    return float(a)
 
 
 def reference_step(idx, outgrad, W, aggr=AGGR_SUM, lr=0.01, use_fma=True):
@@ -329,6 +351,10 @@ def _bind_gpu(L):
             L.ffref_gpu_sgd_task_full.argtypes = [_vp, _vp, _vp, _i64, _i64, C.c_double, C.c_double,
                                                   C.c_double, _int]
             L.ffref_gpu_sgd_task_full.restype = None
+        if hasattr(L, "ffref_gpu_adam_task"):
+            L.ffref_gpu_adam_task.argtypes = [_vp, _vp, _vp, _vp, _i64, _i64, C.c_double, C.c_double,
+                                              C.c_double, C.c_double, C.c_double]
+            L.ffref_gpu_adam_task.restype = None
         if hasattr(L, "ffref_gpu_load_sparse_input"):  # not in the drop-in library
             L.ffref_gpu_load_sparse_input.argtypes = [_vp, _i64, _int, _int, _int, _int, _int, _vp]
     return L

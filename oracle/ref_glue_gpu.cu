@@ -81,6 +81,14 @@ SGDOptimizer::SGDOptimizer(const FFModel *_model, double _lr, double _momentum, 
                            double _weight_decay)
     : Optimizer(_model), lr(_lr), momentum(_momentum), nesterov(_nesterov),
       weight_decay(_weight_decay) {}
+AdamOptimizer::AdamOptimizer(const FFModel *_model, double _alpha, double _beta1, double _beta2,
+                             double _weight_decay, double _epsilon)
+    : Optimizer(_model), alpha(_alpha), beta1(_beta1), beta2(_beta2), weight_decay(_weight_decay),
+      epsilon(_epsilon), alpha_t(_alpha), beta1_t(1.0f), beta2_t(1.0f) {}
+void AdamOptimizer::init(void) {}
+void AdamOptimizer::next(void) {}
+void AdamOptimizer::update(const Parameter *) { FFREF_DEAD("AdamOptimizer::update"); }
+void AdamOptimizer::set_weight_decay(double w) { weight_decay = w; }
 void SGDOptimizer::init(void) {}
 void SGDOptimizer::next(void) {}
 void SGDOptimizer::update(const Parameter *) { FFREF_DEAD("SGDOptimizer::update"); }
@@ -251,6 +259,24 @@ void ffref_gpu_sgd_task_full(const float *Wgrad, float *W, float *V, int64_t d0,
   f.task.args = &opt;
   f.task.arglen = sizeof(opt);
   SGDOptimizer::ps_update_task(&f.task, f.regions, NULL, &f.runtime);
+}
+
+/* AdamOptimizer::ps_update_task (src/runtime/optimizer_kernel.cu:228-290): regions = weight-grad,
+ * weight, V, M; alpha_t as AdamOptimizer::next left it (passed in).                              */
+void ffref_gpu_adam_task(const float *Wgrad, float *W, float *V, float *M, int64_t d0, int64_t d1,
+                         double alpha_t, double beta1, double beta2, double weight_decay, double epsilon) {
+  TaskFrame f;
+  f.add((void *)Wgrad, d0, d1);
+  f.add((void *)W, d0, d1);
+  f.add((void *)V, d0, d1);
+  f.add((void *)M, d0, d1);
+  AdamOptimizer *opt = new AdamOptimizer(NULL, alpha_t, beta1, beta2, weight_decay, epsilon);
+  opt->alpha_t = alpha_t;
+  f.task.args = opt;
+  f.task.arglen = sizeof(AdamOptimizer);
+  AdamOptimizer::ps_update_task(&f.task, f.regions, NULL, &f.runtime);
+  cudaDeviceSynchronize(); /* the task reads *opt only on the host, but keep the frame alive anyway */
+  delete opt;
 }
 
 }  /* extern "C" */

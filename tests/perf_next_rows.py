@@ -126,7 +126,32 @@ def row_f3(T=8, R=1_000_000, D=64, B=2048, L=1):
     return res
 
 
+def row_f3_adam(T=8, R=1_000_000, D=64, B=2048, L=1):
+    g = torch.Generator(device="cuda").manual_seed(3)
+    W = [torch.empty((R, D), device="cuda").uniform_(-0.001, 0.001, generator=g) for _ in range(T)]
+    M, V = [torch.zeros_like(w) for w in W], [torch.zeros_like(w) for w in W]
+    idx = [torch.randint(0, R, (B, L), device="cuda", generator=g) for _ in range(T)]
+    og = [torch.empty((B, D), device="cuda").uniform_(-1, 1, generator=g) for _ in range(T)]
+    coll = pkg.EmbeddingCollection(W, [L] * T, 21)
+    ours = timed(lambda: coll.backward_adam(idx, og, 1e-3, M, V, 0.9, 0.999, 1e-4, 1e-8))
+    res = {"row": "f3 adam_update fused", "workload": f"cfg1 shape: {T} x {R} x {D}, batch {B}, weight decay 1e-4",
+           "ours_ms": round(ours, 3), "ours_gbs": round(24 * T * R * D / ours / 1e6, 1)}
+    if O.ref_gpu_available() and hasattr(O.ref_gpu(), "ffref_gpu_adam_task"):
+        Lr = O.ref_gpu()
+        G = [torch.zeros_like(w) for w in W]
+
+        def ref():
+            for t in range(T):
+                Lr.ffref_gpu_zero_task(G[t].data_ptr(), D, R)
+                Lr.ffref_gpu_backward_task(idx[t].data_ptr(), og[t].data_ptr(), G[t].data_ptr(), L, D, B, R, 21)
+                Lr.ffref_gpu_adam_task(G[t].data_ptr(), W[t].data_ptr(), V[t].data_ptr(), M[t].data_ptr(), D, R,
+                                       1e-3, 0.9, 0.999, 1e-4, 1e-8)
+        rm = timed(ref)
+        res.update({"reference_kernels_on_b200_ms": round(rm, 3), "speedup_vs_reference_kernels": round(rm / ours, 2)})
+    return res
+
+
 if __name__ == "__main__":
     torch.cuda.set_device(0)
-    for fn in (row_f1, row_f2, row_f3):
+    for fn in (row_f1, row_f2, row_f3, row_f3_adam):
         print(json.dumps(fn()), flush=True)

@@ -650,3 +650,75 @@ def test_backward_sgdx_plain_settings_match_the_fused_sgd_path(ffemb, torch_cuda
     cnt = np.bincount(idxs[0].cpu().numpy().reshape(-1), minlength=rows[0])
     assert np.array_equal(a[0].cpu().numpy()[cnt <= 1], b[0].cpu().numpy()[cnt <= 1])
     assert torch.allclose(a[1], b[1], rtol=1e-6, atol=1e-8)
+
+
+@pytest.mark.parametrize("wd", [0.0, 1e-3])
+@pytest.mark.parametrize("aggr", [21, 22])
+def test_backward_adam_two_steps_vs_reference_optimizer(ffemb, oracle, torch_cuda, wd, aggr):
+    """adam_update fused with the backward: two consecutive steps (alpha_t advanced like
+    AdamOptimizer::next) against the oracle's restatement and the reference's own
+    AdamOptimizer::ps_update_task fed with the reference's own embed_backward.  Rows with at most one
+    lookup per step and rows never touched are BIT-IDENTICAL in W, M and V; repeated rows within 1e-6
+    of the step size."""
+    torch = torch_cuda
+    D, B, alpha, b1, b2, eps = 64, 3000, 0.001, 0.9, 0.999, 1e-8
+    rows, bags = [5, 60000, 977], [1, 2, 7]
+    T = len(rows)
+    Ws = [make_inputs(R, D, L, B, seed=1000 + t)[0] for t, (R, L) in enumerate(zip(rows, bags))]
+    steps = [[make_inputs(R, D, L, B, seed=1010 + 10 * k + t)[1:] for t, (R, L) in enumerate(zip(rows, bags))]
+             for k in range(2)]
+    dW = [dev(torch, w) for w in Ws]
+    dM, dV = [torch.zeros_like(w) for w in dW], [torch.zeros_like(w) for w in dW]
+    coll = ffemb.EmbeddingCollection(dW, bags, aggr)
+    oW, oM, oV = [w.copy() for w in Ws], [np.zeros_like(w) for w in Ws], [np.zeros_like(w) for w in Ws]
+    have_ref = oracle.ref_gpu_available() and hasattr(oracle.ref_gpu(), "ffref_gpu_adam_task")
+    rW = [dev(torch, w) for w in Ws]
+    rM, rV = [torch.zeros_like(w) for w in rW], [torch.zeros_like(w) for w in rW]
+    multi = [np.zeros(R, bool) for R in rows]
+    for k in range(2):
+        a_t = np.float32(oracle.adam_alpha_t(alpha, b1, b2, k + 1))
+        idxs = [steps[k][t][0] for t in range(T)]
+        gs = [steps[k][t][1] for t in range(T)]
+        coll.backward_adam([dev(torch, i) for i in idxs], [dev(torch, g) for g in gs], a_t, dM, dV, b1, b2, wd, eps)
+        for t in range(T):
+            grad = oracle.backward_dense(idxs[t], gs[t], rows[t], aggr)
+            oW[t], oM[t], oV[t] = oracle.adam_update(oW[t], grad, oM[t], oV[t], a_t, b1, b2, wd, eps)
+            multi[t] |= np.bincount(idxs[t].reshape(-1), minlength=rows[t]) > 1
+            if have_ref:
+                rg = torch.zeros_like(rW[t])
+                oracle.ref_gpu().ffref_gpu_backward_task(dev(torch, idxs[t]).data_ptr(), dev(torch, gs[t]).data_ptr(),
+                                                         rg.data_ptr(), bags[t], D, B, rows[t], aggr)
+                oracle.ref_gpu().ffref_gpu_adam_task(rg.data_ptr(), rW[t].data_ptr(), rV[t].data_ptr(), rM[t].data_ptr(),
+                                                     D, rows[t], float(a_t), b1, b2, wd, eps)
+        torch.cuda.synchronize()
+    for t in range(T):
+        got, gM, gV = dW[t].cpu().numpy(), dM[t].cpu().numpy(), dV[t].cpu().numpy()
+        once = ~multi[t]
+        if have_ref:   # the reference's own kernel is the authority for the rounding
+            assert np.array_equal(got[once], rW[t].cpu().numpy()[once]), t
+            assert np.array_equal(gM[once], rM[t].cpu().numpy()[once]), t
+            assert np.array_equal(gV[once], rV[t].cpu().numpy()[once]), t
+            assert np.all(np.abs(got - rW[t].cpu().numpy()) <= 2 * alpha * 1e-3 + REL_TOL * np.abs(got).max()), t
+        assert np.array_equal(got[once], oW[t][once]), t
+        assert np.array_equal(gM[once], oM[t][once]) and np.array_equal(gV[once], oV[t][once]), t
+        assert np.all(np.abs(gM - oM[t]) <= REL_TOL * max(np.abs(oM[t]).max(), 1e-30) * 4), t
+        assert int(coll._touched[t].abs().sum().item()) == 0, t
+
+
+def test_general_optimizers_on_an_empty_batch_still_update_every_row(ffemb, oracle, torch_cuda):
+    """The reference's sgd_update / adam_update run over the whole table whatever the batch holds
+    (optimizer_kernel.cu:23-41,206-226): with no lookups at all every row still decays."""
+    torch = torch_cuda
+    R, D = 1000, 32
+    W = make_inputs(R, D, 1, 8, seed=1100)[0]
+    idx = [torch.zeros((0, 3), dtype=torch.int64, device="cuda")]
+    g = [torch.zeros((0, D), device="cuda")]
+    dW, dV = [dev(torch, W)], [torch.full((R, D), 0.25, device="cuda")]
+    ffemb.EmbeddingCollection(dW, [3]).backward_sgdx(idx, g, 0.1, 1e-2, 0.9, True, V=dV)
+    wantW, wantV = oracle.sgd_update_full(W, np.zeros_like(W), np.full_like(W, 0.25), 0.1, 1e-2, 0.9, True)
+    assert np.array_equal(dW[0].cpu().numpy(), wantW) and np.array_equal(dV[0].cpu().numpy(), wantV)
+    dW, dM, dV = [dev(torch, W)], [torch.full((R, D), 0.5, device="cuda")], [torch.full((R, D), 0.125, device="cuda")]
+    ffemb.EmbeddingCollection(dW, [3]).backward_adam(idx, g, 1e-3, dM, dV, 0.9, 0.999, 1e-2, 1e-8)
+    wW, wM, wV = oracle.adam_update(W, np.zeros_like(W), np.full_like(W, 0.5), np.full_like(W, 0.125), 1e-3, 0.9, 0.999, 1e-2, 1e-8)
+    assert np.array_equal(dW[0].cpu().numpy(), wW)
+    assert np.array_equal(dM[0].cpu().numpy(), wM) and np.array_equal(dV[0].cpu().numpy(), wV)
