@@ -23,7 +23,7 @@
 
 namespace ffemb {
 
-enum { AG_SUM = 0, AG_AVG = 1, AG_MEAN = 2 };
+enum { AG_SUM = 0, AG_AVG = 1, AG_MEAN = 2, AG_AVG_P2 = 3 };  // AG_AVG_P2: AVG, every bag width a power of two
 static constexpr int kThreads = 256;
 
 __device__ __forceinline__ void f4_add(float4 &a, const float4 &b) {
@@ -48,7 +48,12 @@ __device__ __forceinline__ float avg_div(float a, float d, float r, bool pow2) {
   if (fabsf(a) < 7.9e-31f) q = a / d;
   return q;
 }
-__device__ __forceinline__ void f4_avg_div(float4 &a, float d, float r, bool pow2) {
+// The general form is NOT inlined: the pipelined walk is unrolled 64 lookups deep, and the residual
+// correction + fallback per element made the AVG kernel 268 KB of code — it then ran out of the
+// instruction cache (ncu: icc hit rate 54 %, "no instruction" the top stall, profiles/r1_notes.md).
+// One call per 16-byte fragment keeps the walk small; power-of-two bag widths (AG_AVG_P2, decided
+// per launch) need no call at all.
+__device__ __noinline__ void f4_avg_div(float4 &a, float d, float r, bool pow2) {
   a.x = avg_div(a.x, d, r, pow2); a.y = avg_div(a.y, d, r, pow2);
   a.z = avg_div(a.z, d, r, pow2); a.w = avg_div(a.w, d, r, pow2);
 }
@@ -152,6 +157,7 @@ __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const f
         for (int c = 0; c < C; c++) {
           f4_add(acc[c], v[bf][u][c]);
           if (AG == AG_AVG) f4_avg_div(acc[c], Lf, Lr, Lpow2);  // the in-loop divide of embedding.cu:186
+          if (AG == AG_AVG_P2) f4_mul(acc[c], Lr);              // ... exact for a power-of-two width
         }
         if (--rem == 0) {  // last lookup of the bag: store the pooled row
 #pragma unroll
@@ -339,6 +345,8 @@ static void launch_vec2(const TableBatch &tb, int D, int64_t B, int ag, int targ
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
   int64_t stream_bytes = kStreamBytes;
   if (const char *e = getenv("FFEMB_STREAM_MB")) stream_bytes = atoll(e) << 20;  // tuning aid
+  bool p2 = true;  // AVG: every bag width a power of two -> the in-loop divide is one exact multiply
+  for (int t = 0; t < tb.num_tables; t++) p2 = p2 && (tb.t[t].L & (tb.t[t].L - 1)) == 0;
   int64_t l1_bytes = kL1Bytes;
   if (const char *e = getenv("FFEMB_L1_KB")) l1_bytes = atoll(e) << 10;  // tuning aid
   // CTA -> work item permutation: odd-ish multiplier near the golden ratio of the grid, coprime with it
@@ -353,10 +361,12 @@ static void launch_vec2(const TableBatch &tb, int D, int64_t B, int ag, int targ
   }
   if (om.npeers == 0) {
     if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
+    else if (ag == AG_AVG && p2) fwd_kernel<G, C, AG_AVG_P2, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
     else if (ag == AG_AVG) fwd_kernel<G, C, AG_AVG, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
     else fwd_kernel<G, C, AG_MEAN, UNR, FULL, false><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
   } else {
     if (ag == AG_SUM) fwd_kernel<G, C, AG_SUM, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
+    else if (ag == AG_AVG && p2) fwd_kernel<G, C, AG_AVG_P2, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
     else if (ag == AG_AVG) fwd_kernel<G, C, AG_AVG, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
     else fwd_kernel<G, C, AG_MEAN, UNR, FULL, true><<<ctas, kThreads, 0, s>>>(tb, D, B, target, stream_bytes, om, pmul, l1_bytes);
   }
