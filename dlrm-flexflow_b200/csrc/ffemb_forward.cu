@@ -23,6 +23,9 @@
 
 namespace ffemb {
 
+#ifndef FFEMB_FWD_KBIG
+#define FFEMB_FWD_KBIG 2  // row numbers per lane and chunk for G >= 16 (1 halves the unrolled walk: measured 0.830 vs 0.822 ms on cfg3, 6.27 vs 5.89 on cfg5)
+#endif
 enum { AG_SUM = 0, AG_AVG = 1, AG_MEAN = 2, AG_AVG_P2 = 3 };  // AG_AVG_P2: AVG, every bag width a power of two
 static constexpr int kThreads = 256;
 
@@ -66,7 +69,7 @@ __device__ __noinline__ void f4_avg_div(float4 &a, float d, float r, bool pow2) 
 // UNR..2*UNR independent 16-byte loads per lane in flight without a bubble at bag or chunk
 // boundaries.  The adds stay strictly sequential in j per output element (embedding.cu:180-188),
 // and a bag's pooled row is stored the moment its last lookup has been added.
-template <int G> struct FwdCfg { static constexpr int K = G >= 16 ? 2 : (G >= 4 ? 4 : (G == 2 ? 8 : 16)); };
+template <int G> struct FwdCfg { static constexpr int K = G >= 16 ? FFEMB_FWD_KBIG : (G >= 4 ? 4 : (G == 2 ? 8 : 16)); };
 static constexpr int kFwdTargetMax = 128;            // lookups per slot when there is plenty of work
 static constexpr int64_t kStreamBytes = 64ll << 20;  // tables above this do not try to stay in L2
 static constexpr int64_t kL1Bytes = 128ll << 10;     // tables up to this are read through L1
