@@ -475,19 +475,27 @@ def run_e2e(torch, pkg, args, wl, dw, ex, fx, dist, dev, barrier, total_lookups)
     if ex is not None:
         return None  # the NCCL comparison form has no host-buffer API
     have = dw.coll is not None
-    h_idx = [[b.cpu().pin_memory() for b in bs[:2]] for bs in dw.idx] if have else []
+    hs = pkg.HostStep(dw.coll, wl.batch, exchange=fx)
     if fx is None:
-        # two host buffer sets: consecutive steps are in flight together (HostStep.submit / wait)
-        h_g = [[g.cpu().pin_memory() for g in dw.outgrad] for _ in range(2)]
-        h_out = [[torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in dw.out] for _ in range(2)]
+        # two pinned host buffer sets laid out like HostStep's device slabs (one copy per kind and step);
+        # consecutive steps are in flight together (HostStep.submit / wait)
+        sets = [hs.host_buffers() for _ in range(2)]
+        for k, (hi, hg, ho) in enumerate(sets):
+            for t in range(len(hi)):
+                hi[t].copy_(dw.idx[t][k % len(dw.idx[t])])
+                hg[t].copy_(dw.outgrad[t])
+        torch.cuda.synchronize()
+        h_idx = [[sets[0][0][t], sets[1][0][t]] for t in range(len(sets[0][0]))]
+        h_g = [sets[0][1], sets[1][1]]
+        h_out = [sets[0][2], sets[1][2]]
         h2d = sum(x[0].numel() * 8 for x in h_idx) + sum(x.numel() * 4 for x in h_g[0])
         d2h = sum(x.numel() * 4 for x in h_out[0])
     else:
+        h_idx = [[b.cpu().pin_memory() for b in bs[:2]] for bs in dw.idx] if have else []
         h_g = [fx.dx.cpu().pin_memory()] * 2
         h_out = [torch.empty(fx.x.shape, dtype=fx.x.dtype).pin_memory()] * 2
         h2d = sum(x[0].numel() * 8 for x in h_idx) + h_g[0].numel() * 4
         d2h = h_out[0].numel() * 4
-    hs = pkg.HostStep(dw.coll, wl.batch, exchange=fx)
     stream = torch.cuda.current_stream()
 
     def submit(k):
@@ -517,7 +525,8 @@ def run_e2e(torch, pkg, args, wl, dw, ex, fx, dist, dev, barrier, total_lookups)
     return {"value": total_lookups / (ms / steps * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
             "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
             "api": "HostStep.submit/wait: 3 streams (H2D / compute / D2H), pinned host buffers, device "
-                   f"buffers x{hs.depth} so consecutive steps' copies run back to back",
+                   f"buffers x{hs.depth} so consecutive steps' copies run back to back; host buffers laid out like "
+                   "the device slabs: one copy per kind and step",
             "h2d_gbs": round(h2d / (ms / steps * 1e-3) / 1e9, 1), "d2h_gbs": round(d2h / (ms / steps * 1e-3) / 1e9, 1)}
 
 

@@ -34,15 +34,93 @@ class HostStep:
         ev = lambda: [torch.cuda.Event() for _ in range(self.depth)]
         # per buffer set: indices landed / grads landed / forward done / D2H done / backward done
         self.ev_idx, self.ev_g, self.ev_fwd, self.ev_out, self.ev_done = ev(), ev(), ev(), ev(), ev()
+        # device side: one slab per kind and buffer set, the per-table tensors are views of it — when the
+        # caller's host tensors are views of one slab too (slab_like), a step moves each kind with ONE
+        # copy instead of one per table (configs 1/2 are copy-launch-bound: 78 copies -> 3)
         self.d_idx, self.d_g, self.d_out = [], [], []
+        self.slab_idx, self.slab_g, self.slab_out = [], [], []
         f32 = dict(dtype=torch.float32, device=dev)
         for _ in range(self.depth):
-            self.d_idx.append([torch.empty((self.B, l), dtype=torch.int64, device=dev) for l in coll.bags]
-                              if coll is not None else [])
+            if coll is not None:
+                slab, views = self._slab([(self.B, l) for l in coll.bags], torch.int64, dev)
+            else:
+                slab, views = None, []
+            self.slab_idx.append(slab)
+            self.d_idx.append(views)
             if exchange is None:
-                self.d_g.append([torch.empty((self.B, coll.dim), **f32) for _ in coll.bags])
-                self.d_out.append([torch.empty((self.B, coll.dim), **f32) for _ in coll.bags])
+                for dst_s, dst_v in ((self.slab_g, self.d_g), (self.slab_out, self.d_out)):
+                    slab, views = self._slab([(self.B, coll.dim)] * len(coll.bags), torch.float32, dev)
+                    dst_s.append(slab)
+                    dst_v.append(views)
         self.ticket = 0
+
+    @staticmethod
+    def _slab(shapes, dtype, device, pin=False):
+        """One flat buffer + per-table views (each view 16-byte aligned: sizes are padded to 16 bytes)."""
+        esz = torch.empty((), dtype=dtype).element_size()
+        pad = max(1, 16 // esz)
+        offs, n = [], 0
+        for shp in shapes:
+            offs.append(n)
+            k = 1
+            for d in shp:
+                k *= int(d)
+            n += (k + pad - 1) // pad * pad
+        slab = torch.empty(max(n, 1), dtype=dtype, device=device)
+        if pin:
+            slab = slab.pin_memory()
+        views = []
+        for shp, o in zip(shapes, offs):
+            k = 1
+            for d in shp:
+                k *= int(d)
+            views.append(slab[o:o + k].view(*shp))
+        return slab, views
+
+    def host_buffers(self):
+        """Pinned host tensors laid out like the device slabs: (h_idx, h_grad, h_out) lists of per-table
+        views; a step on them moves each kind with a single copy."""
+        coll = self.coll
+        _, hi = self._slab([(self.B, l) for l in coll.bags], torch.int64, "cpu", pin=True)
+        _, hg = self._slab([(self.B, coll.dim)] * len(coll.bags), torch.float32, "cpu", pin=True)
+        _, ho = self._slab([(self.B, coll.dim)] * len(coll.bags), torch.float32, "cpu", pin=True)
+        return hi, hg, ho
+
+    @staticmethod
+    def _span(views, slab):
+        """(first pointer, elements) when `views` tile one contiguous region laid out like `slab`'s
+        views, else None."""
+        if slab is None or not views or not isinstance(views, (list, tuple)):
+            return None
+        esz = views[0].element_size()
+        pad = max(1, 16 // esz)
+        p = views[0].data_ptr()
+        for v in views:
+            if not v.is_contiguous() or v.data_ptr() != p:
+                return None
+            p += (v.numel() + pad - 1) // pad * pad * esz
+        return views[0].data_ptr(), (p - views[0].data_ptr()) // esz
+
+    @staticmethod
+    def _copy(dst_views, dst_slab, src_views, src_slab_like, to_host=False):
+        """Per-table copies, or one copy when the host side is laid out like the device slab."""
+        host_views, dev_slab = (dst_views, src_slab_like) if to_host else (src_views, dst_slab)
+        span = HostStep._span(host_views, dev_slab)
+        if span is not None and span[1] <= dev_slab.numel():
+            n = span[1]
+            try:
+                flat = torch.as_strided(host_views[0], (n,), (1,))   # the contiguous host region the views tile
+            except RuntimeError:
+                flat = None                                           # not one storage: per-table copies
+            if flat is not None:
+                if to_host:
+                    flat.copy_(dev_slab[:n], non_blocking=True)
+                else:
+                    dev_slab[:n].copy_(flat, non_blocking=True)
+                return 1
+        for d, h in zip(dst_views, src_views):
+            d.copy_(h, non_blocking=True)
+        return len(dst_views)
 
     def submit(self, h_idx, h_grad, h_out, lr):
         """Enqueue one step (see step()); returns a ticket for wait().  Does not block: the host
@@ -53,12 +131,10 @@ class HostStep:
         d_idx = self.d_idx[s]
         with torch.cuda.stream(self.s_in):
             self.s_in.wait_event(self.ev_done[s])  # the step that last used this buffer set is done
-            for d, h in zip(d_idx, h_idx):
-                d.copy_(h, non_blocking=True)
+            self._copy(d_idx, self.slab_idx[s], h_idx, None)
             self.ev_idx[s].record(self.s_in)
             if fx is None:
-                for d, h in zip(self.d_g[s], h_grad):
-                    d.copy_(h, non_blocking=True)
+                self._copy(self.d_g[s], self.slab_g[s], h_grad, None)
             else:
                 fx.dx.copy_(h_grad, non_blocking=True)
             self.ev_g[s].record(self.s_in)
@@ -72,8 +148,7 @@ class HostStep:
         with torch.cuda.stream(self.s_out):
             self.s_out.wait_event(self.ev_fwd[s])
             if fx is None:
-                for h, d in zip(h_out, self.d_out[s]):
-                    h.copy_(d, non_blocking=True)
+                self._copy(h_out, None, self.d_out[s], self.slab_out[s], to_host=True)
             else:
                 h_out.copy_(fx.x, non_blocking=True)
             self.ev_out[s].record(self.s_out)

@@ -371,6 +371,33 @@ def test_host_steps_in_flight_together_match_sequential_steps(ffemb, oracle, tor
     assert np.array_equal(seq_out[0][1], oracle.forward(idxs[1][0], Ws[1]))
 
 
+def test_host_step_single_copy_layout(ffemb, oracle, torch_cuda):
+    """HostStep.host_buffers(): pinned host tensors laid out like the device slabs move with ONE copy
+    per kind (configs 1/2 are copy-launch-bound); same results as per-table host tensors."""
+    torch = torch_cuda
+    rows, bags, D, B = [7, 30000, 977], [2, 3, 9], 16, 1001   # odd sizes: views are padded to 16 bytes
+    Ws, idxs, gs = [], [], []
+    for t, (R, L) in enumerate(zip(rows, bags)):
+        W, idx, g = make_inputs(R, D, L, B, seed=1200 + t)
+        Ws.append(W), idxs.append(idx), gs.append(g)
+    a = [dev(torch, w) for w in Ws]
+    ffemb.EmbeddingCollection(a, bags).backward_sgd([dev(torch, i) for i in idxs], [dev(torch, g) for g in gs], 0.01)
+    b = [dev(torch, w) for w in Ws]
+    hs = ffemb.HostStep(ffemb.EmbeddingCollection(b, bags), B)
+    hi, hg, ho = hs.host_buffers()
+    assert all(x.is_pinned() for x in hi + hg + ho)
+    assert hs._span(hi, hs.slab_idx[0]) is not None and hs._span(hg, hs.slab_g[0]) is not None
+    assert hs._copy(hs.d_idx[0], hs.slab_idx[0], hi, None) == 1                      # one copy for all tables
+    assert hs._copy(hs.d_idx[0], hs.slab_idx[0], [torch.from_numpy(i).pin_memory() for i in idxs], None) == 3
+    for t in range(len(rows)):
+        hi[t].copy_(torch.from_numpy(idxs[t]))
+        hg[t].copy_(torch.from_numpy(gs[t]))
+    hs.step(hi, hg, ho, 0.01)
+    for t in range(len(rows)):
+        assert np.array_equal(ho[t].numpy(), oracle.forward(idxs[t], Ws[t])), t
+        assert torch.equal(a[t], b[t]), t
+
+
 def test_linearity_and_roundtrip_at_full_size(ffemb, torch_cuda):
     """Size-independent properties at BASELINE config-2 scale (26 tables, D=16, B=16384) without
     the CPU oracle: (1) forward of bag-1 indices is a pure gather; (2) with lr = 1 and
