@@ -396,23 +396,30 @@ def run_rowwise(args, torch, pkg, dist, wl, rank, world, dev):
     NVLink inside the kernel); backward = all-gather of indices + output-grads, local sort/reduce/SGD."""
     lo, hi = pkg.sharding.batch_block(wl.batch, world, rank)
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
-    tabs, idx, og, out = [], [], [], []
-    for t in range(wl.num_tables):
-        rw = pkg.exchange.RowWiseTable(wl.rows[t], wl.dim, wl.bags[t], wl.batch, rank, world, dev, wl.aggr)
+    T, D = wl.num_tables, wl.dim
+    rc = pkg.exchange.RowWiseCollection(wl.rows, D, wl.bags, wl.batch, rank, world, dev, wl.aggr)
+    for t in range(T):
         a = (1.0 / wl.rows[t]) ** 0.5
-        rw.shard[:rw.local_rows].uniform_(-a, a, generator=g)
-        tabs.append(rw)
-        idx.append([torch.randint(0, wl.rows[t], (hi - lo, wl.bags[t]), dtype=torch.int64, device=dev, generator=g)
-                    for _ in range(args.pool)])
-        og.append(torch.empty((hi - lo, wl.dim), device=dev).uniform_(-1, 1, generator=g))
-        out.append(torch.empty((hi - lo, wl.dim), device=dev))
+        rc.shards[t][:rc.local_rows[t]].uniform_(-a, a, generator=g)
+    # this rank's samples: sample-major index batches [B_h][sum L] (the data loader's layout) and the
+    # per-table [B_h][L] tensors cut out of them once (ffemb_load_sparse_inputs)
+    idx_sm, idx = [], []
+    for _ in range(args.pool):
+        cols = [torch.randint(0, wl.rows[t], (hi - lo, wl.bags[t]), dtype=torch.int64, device=dev, generator=g)
+                for t in range(T)]
+        sm = torch.cat(cols, dim=1).contiguous()
+        idx_sm.append(sm)
+        idx.append(pkg.load_sparse_inputs(sm, wl.bags, hi - lo))
+    dx = torch.empty((hi - lo, T * D), device=dev).uniform_(-1, 1, generator=g)
+    out = [torch.empty((hi - lo, D), device=dev) for _ in range(T)]
+    tabs = [rc]
     stream = torch.cuda.current_stream()
+    torch.cuda.synchronize()
+    dist.barrier()
 
     def step(k):
-        for t, rw in enumerate(tabs):
-            rw.forward(idx[t][k % args.pool], out[t])
-        for t, rw in enumerate(tabs):
-            rw.backward_sgd(idx[t][k % args.pool], og[t], wl.lr)
+        rc.forward(idx[k % args.pool], out)
+        rc.backward_sgd(idx_sm[k % args.pool], dx, wl.lr)
 
     def barrier():
         dist.barrier()
@@ -446,9 +453,10 @@ def run_rowwise(args, torch, pkg, dist, wl, rank, world, dev):
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl.name, "tables": wl.num_tables, "dim": D, "batch": wl.batch, "bags": wl.bags,
-                       "rows_total": int(sum(wl.rows)), "table_bytes_per_gpu": int(sum(r.shard.numel() * 4 for r in tabs)),
+                       "rows_total": int(sum(wl.rows)), "table_bytes_per_gpu": int(sum(sh.numel() * 4 for sh in rc.shards)),
                        "lookups_per_step": n, "parallelism": f"row-wise x{world}: remote gathers over NVLink in the "
-                       "forward kernel; all-gather (NCCL) + local deterministic backward",
+                       "forward kernels; per step ONE all-gather (NCCL) of the sample-major indices and ONE of "
+                       "the interaction-input gradients, then one local deterministic backward for all tables",
                        "cache": "tables far larger than L2, random rows"},
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "step (launch/latency-bound at 64K lookups per table)",

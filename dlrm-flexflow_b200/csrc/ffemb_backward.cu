@@ -36,7 +36,15 @@
 namespace ffemb {
 
 static constexpr int kThreads = 256;
-static constexpr int CH1 = 64;  // level-1 tile (sorted lookups per slot)
+// level-1 tile (sorted lookups per slot).  FFEMB_CH1_WIDE (rows of >= 64 floats, where a slot is half a
+// warp or more) is a tuning aid: 128 halves the partial rows the upper levels walk (cfg3 reduce_up
+// 0.120 -> 0.093 ms) but the longer serial walk costs level 1 as much (1.175 -> 1.188 ms; cfg5
+// 11.8 -> 12.3 ms), so it stays at 64.
+#ifndef FFEMB_CH1_WIDE
+#define FFEMB_CH1_WIDE 64
+#endif
+template <int G> struct Ch1 { static constexpr int value = G >= 16 ? FFEMB_CH1_WIDE : 64; };
+static inline int ch1_of(int64_t D) { return D / 4 > 8 ? FFEMB_CH1_WIDE : 64; }
 static constexpr int CH2 = 32;  // level-k tile (partial rows per slot)
 static constexpr int kSmallLevel = 1 << 8;   // <= this many partial slots: finish in one CTA (a CTA walks 8 tiles at a time, ~6 us a round)
 static constexpr int64_t kStreamTableBytes = 64ll << 20;  // tables above this do not stay in L2
@@ -283,6 +291,7 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
                const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
                float *rows_out, int flags, uint32_t split, const OptArgs *oa) {
   constexpr int THREADS = L1Threads<G>::value;
+  constexpr int CH1 = Ch1<G>::value;
   constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
   constexpr int NG = CH1 / UNR;
@@ -557,7 +566,7 @@ struct Levels {
   int count;            // number of partial buffers
   int64_t slots[8];     // partial slots of level i output (2 * tiles)
 };
-static Levels plan_levels(int64_t n) {
+static Levels plan_levels(int64_t n, int CH1) {
   Levels lv;
   lv.count = 0;
   int64_t m = 2 * ((n + CH1 - 1) / CH1);
@@ -599,7 +608,7 @@ static Carve carve(char *base, int64_t n, int64_t total_rows, int64_t D) {
   c.cub_bytes = tmp;
   c.cub_tmp = take(tmp);
   // partial buffers ping-pong: level 1 output is the largest; level 2 output the second largest
-  const Levels lv = plan_levels(n);
+  const Levels lv = plan_levels(n, ch1_of(D));
   const int64_t s0 = lv.slots[0], s1 = lv.count > 1 ? lv.slots[1] : 2;
   c.pkeys[0] = take((size_t)s0 * ksz);
   c.prows[0] = (float *)take((size_t)s0 * D * 4);
@@ -726,6 +735,7 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
   if (stage == STAGE_SORT) return cuda_fail(cudaGetLastError(), "sort launch");
 
   constexpr int SLOTS = 32 / G;
+  constexpr int CH1 = Ch1<G>::value;
   const int64_t slots_per_cta = (int64_t)(kThreads / 32) * SLOTS;
   const int64_t ntiles1 = (n + CH1 - 1) / CH1;
   K *pk0 = (K *)c.pkeys[0], *pk1 = (K *)c.pkeys[1];

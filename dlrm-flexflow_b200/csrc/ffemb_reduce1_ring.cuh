@@ -32,6 +32,7 @@ reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__
                     const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
                     float *rows_out, uint32_t split, const OptArgs *oa) {
   constexpr int THREADS = L1Threads<G>::value;
+  constexpr int CH1 = Ch1<G>::value;
   constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
   constexpr K INV = KeyTraits<K>::INV;
   extern __shared__ __align__(16) unsigned char smem_raw[];

@@ -242,3 +242,88 @@ class RowWiseTable:
                                            self.shard[self.rps].data_ptr(), self.D, _stream_ptr(stream)))
         self.coll.backward_sgd([self.idx_local], [self.g_full[:self.B]], lr, stream=stream)
         self.h.barrier(channel=0)  # shards are consistent before anyone's next forward reads them
+
+
+class RowWiseCollection:
+    """Several row-wise sharded tables driven together (BASELINE config 4: 8 x 100M x 128).
+
+    RowWiseTable costs two collectives and a full launch sequence per table; at 64K lookups per table
+    that is pure latency.  Here one step of ALL tables is
+      forward     : one remote-gather launch per table (rows read from the owners' shards over NVLink);
+      backward_sgd: ONE all-gather of the ranks' sample-major index batches [B_h][sum L] and ONE of
+                    their interaction-input gradients [B_h][T*D] (the layouts the data loader and the
+                    Concat gradient have anyway), then ffemb_load_sparse_inputs cuts every table's
+                    [B][L] out of the gathered batch, rowwise_localize points foreign rows at the
+                    scratch row, and ONE ffemb_backward_sgd_concat reads every table's output-grads in
+                    place from the gathered gradient: one keygen / sort / segmented sum for all tables.
+    Shard map, forward arithmetic and results are RowWiseTable's (bit-identical forward)."""
+
+    def __init__(self, rows, dim, bags, batch, rank, world, device, aggr=21, group=None):
+        import torch.distributed._symmetric_memory as symm
+        from .embedding import EmbeddingCollection
+        from .sharding import rows_per_shard, shard_rows
+        self.rows, self.D, self.bags, self.B = [int(r) for r in rows], int(dim), [int(l) for l in bags], int(batch)
+        self.T = len(self.rows)
+        self.rank, self.world, self.device, self.aggr = rank, world, device, int(aggr)
+        self.group = group if group is not None else dist.group.WORLD
+        self.rps = [rows_per_shard(r, world) for r in self.rows]
+        self.local_rows = [shard_rows(r, world, rank) for r in self.rows]
+        self.ext = (self.B + world - 1) // world
+        self.lo, self.hi = batch_block(self.B, world, rank)
+        self.shards, self.handles = [], []
+        for t in range(self.T):
+            s = symm.empty((self.rps[t] + 1, self.D), dtype=torch.float32, device=device)  # + scratch row
+            self.handles.append(symm.rendezvous(s, self.group))
+            s.zero_()
+            self.shards.append(s)
+        self.sumL = sum(self.bags)
+        i64, f32 = dict(dtype=torch.int64, device=device), dict(dtype=torch.float32, device=device)
+        self._pad_i = torch.zeros((self.ext, self.sumL), **i64)
+        self._pad_g = torch.zeros((self.ext, self.T * self.D), **f32)
+        self.idx_full = torch.zeros((world * self.ext, self.sumL), **i64)
+        self.g_full = torch.zeros((world * self.ext, self.T * self.D), **f32)
+        self.idx_glob = [torch.empty((self.B, l), **i64) for l in self.bags]
+        self.idx_local = [torch.empty((self.B, l), **i64) for l in self.bags]
+        self.coll = EmbeddingCollection(self.shards, self.bags, self.aggr)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=self.group)
+
+    def load_rows(self, full_tables):
+        for t, full in enumerate(full_tables):
+            lo = self.rank * self.rps[t]
+            self.shards[t][:self.local_rows[t]].copy_(full[lo:lo + self.local_rows[t]])
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+
+    def forward(self, idx_list, outs=None, stream=None):
+        """idx_list[t]: int64 [B_h][L_t] global row ids of this rank's samples -> pooled [B_h][D] per table."""
+        import ctypes as C
+        from .binding import check, lib
+        from .embedding import _stream_ptr
+        n = int(idx_list[0].shape[0])
+        if outs is None:
+            outs = [torch.empty((n, self.D), dtype=torch.float32, device=self.device) for _ in range(self.T)]
+        for t in range(self.T):
+            ptrs = (C.c_void_p * self.world)(*[int(p) for p in self.handles[t].buffer_ptrs])
+            check(lib().ffemb_forward_rowwise(idx_list[t].data_ptr(), outs[t].data_ptr(), ptrs, self.world,
+                                              self.rps[t], self.bags[t], self.D, n, self.aggr, _stream_ptr(stream)))
+        return outs
+
+    def backward_sgd(self, idx_sm, dx, lr, stream=None):
+        """idx_sm: int64 [B_h][sum L] — this rank's samples, sample-major (table t's bag at columns
+        [sum_{s<t} L_s, +L_t)); dx: [B_h][T*D] — the gradient of its interaction input (table t's
+        block at columns [t*D, +D)).  Updates this rank's shards of every table."""
+        from .binding import check, lib
+        from .embedding import _stream_ptr, load_sparse_inputs
+        n = self.hi - self.lo
+        self._pad_i[:n].copy_(idx_sm)
+        self._pad_g[:n].copy_(dx)
+        dist.all_gather_into_tensor(self.idx_full, self._pad_i, group=self.group)  # also orders every
+        dist.all_gather_into_tensor(self.g_full, self._pad_g, group=self.group)    # rank's forward first
+        load_sparse_inputs(self.idx_full, self.bags, self.B, outs=self.idx_glob, stream=stream)
+        for t in range(self.T):
+            check(lib().ffemb_rowwise_localize(self.idx_glob[t].data_ptr(), self.idx_local[t].data_ptr(),
+                                               self.B * self.bags[t], self.rps[t], self.rank,
+                                               self.shards[t][self.rps[t]].data_ptr(), self.D, _stream_ptr(stream)))
+        self.coll.backward_sgd_concat(self.idx_local, self.g_full, lr, stream=stream)
+        self.handles[0].barrier(channel=0)  # shards are consistent before anyone's next forward reads them

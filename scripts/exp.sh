@@ -1,2 +1,7 @@
-python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "host_step" 2>&1 | tail -3
-for w in 1 2 3; do python bench.py --workload $w --steps 20 --warmup 5 --no-cpu 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('cfg$w', round(d['ms_per_step'],3), d['e2e'])"; done
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+B="python bench.py --steps 20 --warmup 5 --no-e2e --no-cpu --no-overlap"
+ph() { python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', round(d['ms_per_step'],3), d['roofline']['phases_ms_per_step'])"; }
+$B | ph cfg3
+$B | ph cfg3
+$B --workload 5 --steps 5 --warmup 2 | ph cfg5
+$B --workload 1 | ph cfg1
