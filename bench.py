@@ -342,7 +342,9 @@ def main():
     # dominant kernel = the longest phase that moves algorithmic bytes (sort / keygen / upper levels are
     # overhead phases: no bytes are credited to them, and at N > 1 the sort's span is stretched by the
     # exchange it runs under)
-    cand = {k: v for k, v in kernel_phases.items() if alg.get(k, 0) > 0 and k not in ("keygen", "exchange")}
+    # ("small" is excluded too: those kernels are forked onto a side stream and run UNDER the sort / level 1,
+    # so their event span is not busy time)
+    cand = {k: v for k, v in kernel_phases.items() if alg.get(k, 0) > 0 and k in ("forward", "reduce1", "atomic")}
     dom = max(cand, key=cand.get) if cand else (max(kernel_phases, key=kernel_phases.get) if kernel_phases else "forward")
     dom_ms = kernel_phases.get(dom, ms_step)
     achieved = alg.get(dom, 0) / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0

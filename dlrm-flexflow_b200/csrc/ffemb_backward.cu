@@ -835,6 +835,30 @@ int dispatch_wide(const TableBatch &tb, int D, int64_t B, int aggr, float lr, in
 }
 #else
 
+// A side stream + fork/join events per host thread and device (created on first use, never freed:
+// a handful per process).  FFEMB_SMALL_FORK=0 turns the fork off (tuning aid / A-B runs).
+struct SideStream {
+  cudaStream_t s;
+  cudaEvent_t fork, join;
+  bool ok, tried;
+};
+static SideStream *side_stream() {
+  static thread_local SideStream ctx[32];
+  static const bool enabled = [] { const char *e = getenv("FFEMB_SMALL_FORK"); return !e || atoi(e) != 0; }();
+  if (!enabled) return nullptr;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 32) return nullptr;
+  SideStream &c = ctx[dev];
+  if (!c.tried) {
+    c.tried = true;
+    c.ok = cudaStreamCreateWithFlags(&c.s, cudaStreamNonBlocking) == cudaSuccess &&
+           cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming) == cudaSuccess &&
+           cudaEventCreateWithFlags(&c.join, cudaEventDisableTiming) == cudaSuccess;
+    if (!c.ok) cudaGetLastError();
+  }
+  return c.ok ? &c : nullptr;
+}
+
 int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int aggr, float lr,
                            ApplyMode mode, void *ws, size_t ws_bytes, cudaStream_t s, int stage,
                            const OptArgs *opt_host) {
@@ -899,10 +923,32 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
   tb.row_base[tb.num_tables] = rows_l;
   const int64_t rows = (int64_t)rows_l;
   const Carve c = carve((char *)ws, (int64_t)n, rows > 0 ? rows : 1, D);
+  // The bag-major kernels of the small tables are shared-memory-bound and touch neither the sort
+  // buffers nor the sorted tables: when there is sorted work too they are forked onto a side stream
+  // (per host thread and device) and run UNDER the radix sort / the segmented sum instead of in front
+  // of them; the caller's stream joins at the end, so stream semantics are unchanged.
+  SideStream *fork = nullptr;
   if (ts.num_tables && stage != STAGE_SORT) {
-    const int rc = launch_backward_small(ts, n_tiny, D, B, aggr, lr, mode, (float *)((char *)ws + c.total), s);
+    if (n > 0 && mode != APPLY_SGDX) fork = side_stream();
+    cudaStream_t ss = s;
+    if (fork) {
+      if (cudaEventRecord(fork->fork, s) != cudaSuccess || cudaStreamWaitEvent(fork->s, fork->fork, 0) != cudaSuccess)
+        fork = nullptr;
+      else
+        ss = fork->s;
+    }
+    int rc = launch_backward_small(ts, n_tiny, D, B, aggr, lr, mode, (float *)((char *)ws + c.total), ss);
+    if (fork) {
+      if (cudaEventRecord(fork->join, fork->s) != cudaSuccess && !rc) rc = cuda_fail(cudaGetLastError(), "side stream join");
+      if (rc) cudaStreamWaitEvent(s, fork->join, 0);
+    }
     if (rc) return rc;
   }
+  struct Join {  // the caller's stream waits for the forked kernels on every way out
+    SideStream *f;
+    cudaStream_t s;
+    ~Join() { if (f) cudaStreamWaitEvent(s, f->join, 0); }
+  } join{fork, s};
   if (mode == APPLY_SGDX) {
     // optimizer arguments in key order of the tables, copied to the tail of the workspace (pageable
     // source: the copy is staged before cudaMemcpyAsync returns)

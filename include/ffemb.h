@@ -15,7 +15,9 @@
  *     regions); nothing is allocated or freed per call; scratch comes from the caller
  *     (FFHandler::workSpace or an EmbeddingMeta-owned buffer) and is sized by the *_workspace
  *     queries;
- *   - all work is enqueued on `stream`; no host synchronisation, no device selection (the
+ *   - all work is ordered on `stream`: enqueued on it, or (the bag-major small-table kernels of the
+ *     backward) forked from it onto a library-owned side stream and joined back before the call's
+ *     work ends, CUDA-graph-capture style; no host synchronisation, no device selection (the
  *     caller's current device is used), re-entrant across devices and threads;
  *   - returns FFEMB_OK or an error code and never throws / exits; ffemb_last_error() gives the
  *     text for the calling thread.  (The reference asserts / exit(1)s instead,
