@@ -60,6 +60,9 @@ def parse():
     ap.add_argument("--no-overlap", action="store_true",
                     help="run the backward's index sort in stream order instead of on a side stream "
                          "under the forward pass / exchange (it depends on the indices only)")
+    ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
+                    help="N=1: replay the step from a CUDA graph (StepGraph); auto = the launch-bound small "
+                         "configs (<= 2M lookups per step: cfg1, cfg2), where it is worth 1.6-1.9x")
     ap.add_argument("--rows-cap", type=int, default=0, help="cap rows per table (profiling under ncu only)")
     ap.add_argument("--cpu-batch", type=int, default=16384)
     ap.add_argument("--cpu-rows-cap", type=int, default=2_000_000)
@@ -289,6 +292,31 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    use_graph = (args.graph == "on" or (args.graph == "auto" and wl.lookups <= 2_000_000)) and \
+        world == 1 and args.backward == "sorted"
+    per_step_launches, eager_phases = 0, None
+    if use_graph:
+        # phases and the launch count come from an eager profiled pass of the same kernels; the timed
+        # region then replays one captured graph per index batch of the pool
+        for k in range(args.warmup):
+            step(k)
+        barrier()
+        pkg.profile_enable(True)
+        pkg.profile_collect()
+        l0 = pkg.launch_count()
+        for k in range(args.steps):
+            step(k)
+        barrier()
+        per_step_launches = (pkg.launch_count() - l0) / args.steps
+        eager_phases = pkg.profile_collect()
+        pkg.profile_enable(False)
+        graphs = [pkg.StepGraph(dw.coll, wl.batch, wl.lr, idx=[b[p] for b in dw.idx], outs=dw.out,
+                                out_grads=dw.outgrad) for p in range(dw.pool)]
+        overlap = False
+
+        def step(k):  # noqa: F811
+            graphs[k % dw.pool].graph.replay()
+
     for k in range(args.warmup):
         step(k)
     barrier()
@@ -311,6 +339,9 @@ def main():
     launches = pkg.launch_count() - l0
     phase_ms, phase_launch = pkg.profile_collect()
     pkg.profile_enable(False)
+    if use_graph:
+        launches = int(round(per_step_launches * args.steps))  # kernels inside the replayed graphs
+        phase_ms, phase_launch = eager_phases
     clocks = sampler.stop() if sampler else None
     if dist is not None:
         t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
@@ -375,6 +406,7 @@ def main():
                                    f"table-wise x{world} ({args.placement} placement), exchange={args.exchange}"),
                    "table_owner": own if world > 1 else None,
                    "backward": args.backward, "sort_overlapped_on_side_stream": bool(overlap),
+                   "cuda_graph": bool(use_graph),
                    "cache": f"inputs larger than L2: {args.pool} index batches cycled, "
                             f"{sum(wl.rows) * wl.dim * 4 / 1e9:.1f} GB of tables, random rows",
                    "unique_rows_per_step": int(U)},
@@ -514,15 +546,15 @@ def run_e2e(torch, pkg, args, wl, dw, ex, fx, dist, dev, barrier, total_lookups)
         hs.wait(k - 2)
         return hs.submit([x[k % 2] for x in h_idx], h_g[k % 2], h_out[k % 2], wl.lr)
 
-    steps = max(3, min(args.steps, 10))
-    for k in range(2):
+    steps = max(3, min(args.steps, 200 if wl.lookups <= 2_000_000 else 10))
+    for k in range(4):   # warm-up; with hs.use_graph the second use of each buffer set captures its graphs
         submit(k)
     hs.wait()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record(stream)
     for k in range(steps):
-        submit(2 + k)
+        submit(4 + k)
     hs.join(stream)   # the last download and the last row update are inside the timed region
     e1.record(stream)
     barrier()
@@ -534,6 +566,7 @@ def run_e2e(torch, pkg, args, wl, dw, ex, fx, dist, dev, barrier, total_lookups)
         ms, h2d, d2h = t[0].item(), t[1].item(), t[2].item()
     return {"value": total_lookups / (ms / steps * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
             "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+            "cuda_graph": bool(hs.use_graph),
             "api": "HostStep.submit/wait: 3 streams (H2D / compute / D2H), pinned host buffers, device "
                    f"buffers x{hs.depth} so consecutive steps' copies run back to back; host buffers laid out like "
                    "the device slabs: one copy per kind and step",

@@ -15,9 +15,9 @@ from .binding import (AGGR_MODE_AVG, AGGR_MODE_MEAN, AGGR_MODE_NONE, AGGR_MODE_S
                       library_path, profile_collect, profile_enable)
 from . import sharding, synth
 from . import exchange
-from .embedding import Embedding, EmbeddingCollection, EmbeddingMeta, load_sparse_inputs
+from .embedding import Embedding, EmbeddingCollection, EmbeddingMeta, StepGraph, load_sparse_inputs
 from .hoststep import HostStep
 
 __all__ = ["AGGR_MODE_AVG", "AGGR_MODE_NONE", "AGGR_MODE_SUM", "AGGR_MODE_MEAN", "FFEmbError",
            "build_library", "declared_symbols", "exported_symbols", "lib", "library_path",
-           "launch_count", "profile_collect", "profile_enable", "Embedding", "EmbeddingCollection", "EmbeddingMeta", "HostStep", "load_sparse_inputs", "synth", "sharding", "exchange"]
+           "launch_count", "profile_collect", "profile_enable", "Embedding", "EmbeddingCollection", "EmbeddingMeta", "HostStep", "StepGraph", "load_sparse_inputs", "synth", "sharding", "exchange"]

@@ -307,6 +307,45 @@ class EmbeddingCollection:
                                                      ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
 
 
+class StepGraph:
+    """One forward + backward-with-SGD step of a collection captured into a CUDA graph: for
+    launch-bound steps (small batches: a dozen kernels of a few microseconds each) a replay is one
+    launch instead of the dozen.  The entry points qualify because they neither synchronise nor
+    allocate, and the side-stream fork of the small-table kernels is a fork/join on events
+    (include/ffemb.h, conventions) — the captured step is the same kernels in the same order, so
+    its results are bit-identical to the eager calls'.
+
+    Buffers are static: write the step's indices into `self.idx[t]` and the output-grads into
+    `self.out_grads[t]` (or let the caller's kernels write there), then `replay()`; pooled rows
+    are in `self.outs[t]`.  `between` (optional callable) is captured between the two halves —
+    the place of the caller's own work on the capture stream (interaction, dense layers).
+    (The sgdx / adam entry points are not capturable: their scalar arguments change every step.)"""
+
+    def __init__(self, coll, batch, lr, idx=None, outs=None, out_grads=None, between=None):
+        dev = coll.device
+        self.coll, self.batch, self.lr = coll, int(batch), float(lr)
+        new = lambda shape, dt: torch.zeros(shape, dtype=dt, device=dev)
+        self.idx = idx if idx is not None else [new((batch, l), torch.int64) for l in coll.bags]
+        self.outs = outs if outs is not None else [new((batch, coll.dim), torch.float32) for _ in coll.bags]
+        self.out_grads = out_grads if out_grads is not None else \
+            [new((batch, coll.dim), torch.float32) for _ in coll.bags]
+        # one eager step first: workspace allocation, the lazily created side stream and the kernel
+        # attributes all happen outside the capture (lr = 0: no table value changes)
+        coll.forward(self.idx, self.outs)
+        coll.backward_sgd(self.idx, self.out_grads, 0.0)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+            coll.forward(self.idx, self.outs)
+            if between is not None:
+                between(self)
+            coll.backward_sgd(self.idx, self.out_grads, self.lr)
+
+    def replay(self):
+        self.graph.replay()
+        return self.outs
+
+
 def load_sparse_inputs(full, bags, batch, first_sample=0, sample_ids=None, cols=None, outs=None, stream=None):
     """DataLoader::load_sparse_input for ALL tables in one launch
     (/root/reference/examples/cpp/DLRM/dlrm.cu:19-58, dlrm.cc:482-520; ffemb_load_sparse_inputs).

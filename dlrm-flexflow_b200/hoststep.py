@@ -20,12 +20,22 @@ import torch
 
 
 class HostStep:
-    def __init__(self, coll, batch, exchange=None, depth=2):
+    GRAPH_MAX_LOOKUPS = 2_000_000
+
+    def __init__(self, coll, batch, exchange=None, depth=2, graph="auto"):
         """coll: EmbeddingCollection of this GPU's tables (or None on a rank that owns none);
         exchange: FusedTableWiseExchange for N > 1 (then the host-side result is the rank's
         interaction input x and the host-side gradient is its dx; those live in one symmetric
-        buffer each, so steps are not overlapped there: depth 1)."""
+        buffer each, so steps are not overlapped there: depth 1).
+        graph: replay the kernels of a step from two CUDA graphs per buffer set (forward + index sort;
+        segmented sum + SGD) instead of launching them one by one — "auto" = single-GPU steps of at
+        most GRAPH_MAX_LOOKUPS lookups, which are bound by the host's launch rate, not by the GPU or
+        PCIe.  The copies stay eager (three per step), so steps still overlap across buffer sets."""
         self.coll, self.fx, self.B = coll, exchange, int(batch)
+        small = coll is not None and int(batch) * sum(coll.bags) <= self.GRAPH_MAX_LOOKUPS
+        self.use_graph = exchange is None and coll is not None and (graph is True or graph == "on" or
+                                                                    (graph == "auto" and small))
+        self._graphs, self._last_lr, self.graph_replays = {}, {}, 0
         dev = coll.device if coll is not None else exchange.device
         self.dev = dev
         self.depth = 1 if exchange is not None else max(1, int(depth))
@@ -138,9 +148,13 @@ class HostStep:
             else:
                 fx.dx.copy_(h_grad, non_blocking=True)
             self.ev_g[s].record(self.s_in)
+        gr = self._step_graphs(s, float(lr)) if self.use_graph else None
         main.wait_event(self.ev_idx[s])
         main.wait_event(self.ev_out[s])            # the previous download out of d_out[s] has drained
-        if fx is None:
+        if gr is not None:
+            with torch.cuda.stream(main):
+                gr[0].replay()                     # forward + keygen / radix sort
+        elif fx is None:
             coll.forward(d_idx, self.d_out[s])
         else:
             fx.forward(coll, d_idx)
@@ -152,9 +166,16 @@ class HostStep:
             else:
                 h_out.copy_(fx.x, non_blocking=True)
             self.ev_out[s].record(self.s_out)
-        if coll is not None:
+        if coll is not None and gr is None:
             coll.backward_prepare(d_idx)       # sort: indices only, runs while the grads upload
         main.wait_event(self.ev_g[s])
+        if gr is not None:
+            with torch.cuda.stream(main):
+                gr[1].replay()                     # segmented sum + SGD row updates
+            self.graph_replays += 2
+            self.ev_done[s].record(main)
+            self.ticket = k + 1
+            return k
         if fx is not None:
             fx.backward()
             grads = fx.outgrads
@@ -165,6 +186,27 @@ class HostStep:
         self.ev_done[s].record(main)
         self.ticket = k + 1
         return k
+
+    def _step_graphs(self, s, lr):
+        """The two graphs of buffer set s for this learning rate, captured the second time the set is
+        used with it (the first use runs eagerly: it is the warm-up — workspace, side stream, kernel
+        attributes — and the device buffers hold real indices from then on).  A step with another
+        learning rate runs eagerly; the graphs are re-captured when the new rate repeats."""
+        have = self._graphs.get(s)
+        if have is not None and have[0] == lr:
+            return have[1]
+        seen, self._last_lr[s] = self._last_lr.get(s), lr
+        if seen != lr:
+            return None
+        coll, d_idx = self.coll, self.d_idx[s]
+        ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(ga, capture_error_mode="thread_local"):
+            coll.forward(d_idx, self.d_out[s])
+            coll.backward_prepare(d_idx)
+        with torch.cuda.graph(gb, capture_error_mode="thread_local"):
+            coll.backward_sgd(d_idx, self.d_g[s], lr, prepared=True)
+        self._graphs[s] = (lr, (ga, gb))
+        return self._graphs[s][1]
 
     def wait(self, ticket=None):
         """Block until step `ticket` (default: the last submitted) has finished: its pooled outputs

@@ -312,6 +312,37 @@ def test_backward_split_in_prepare_and_apply_is_bit_identical(ffemb, torch_cuda)
         assert torch.equal(x, y)
 
 
+def test_step_captured_in_a_cuda_graph_replays_bit_exact(ffemb, oracle, torch_cuda):
+    """The entry points are capturable (no synchronisation, no allocation, fork/join side stream):
+    a forward + backward-with-SGD step captured once and replayed on new inputs gives the oracle's
+    pooled rows and tables bit-identical to the eager calls', step after step (sorted path, small
+    bag-major path and tiny tables together; the between-hook stands for the caller's own kernels)."""
+    torch = torch_cuda
+    rows, bags, D, B = [5, 100000, 33, 20000, 4, 977], [1, 3, 20, 2, 7, 9], 64, 3000
+    Ws = [make_inputs(R, D, L, B, seed=700 + t)[0] for t, (R, L) in enumerate(zip(rows, bags))]
+    a = [dev(torch, w) for w in Ws]
+    b = [dev(torch, w) for w in Ws]
+    eager = ffemb.EmbeddingCollection(a, bags)
+    sg = ffemb.StepGraph(ffemb.EmbeddingCollection(b, bags), B, 0.01,
+                         between=lambda s: [g.copy_(o).mul_(0.5) for g, o in zip(s.out_grads, s.outs)])
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)  # capturing (and the lr = 0 warm-up step) changed no table
+    for step in range(3):
+        idxs = [make_inputs(R, D, L, B, seed=710 + 10 * step + t)[1] for t, (R, L) in enumerate(zip(rows, bags))]
+        d_idx = [dev(torch, i) for i in idxs]
+        outs = eager.forward(d_idx)
+        eager.backward_sgd(d_idx, [o * 0.5 for o in outs], 0.01)
+        for dst, src in zip(sg.idx, d_idx):
+            dst.copy_(src)
+        got = sg.replay()
+        torch.cuda.synchronize()
+        for t in range(len(rows)):
+            assert torch.equal(got[t], outs[t]), (step, t)
+            assert torch.equal(a[t], b[t]), (step, t)
+            if step == 0:
+                assert np.array_equal(got[t].cpu().numpy(), oracle.forward(idxs[t], Ws[t])), t
+
+
 def test_host_step_matches_device_step(ffemb, oracle, torch_cuda):
     """HostStep (pinned host buffers, three streams) == the device-resident calls, bit for bit, and
     the pooled outputs that land on the host are the oracle's."""
@@ -336,11 +367,14 @@ def test_host_step_matches_device_step(ffemb, oracle, torch_cuda):
 
 
 def test_host_steps_in_flight_together_match_sequential_steps(ffemb, oracle, torch_cuda):
-    """HostStep.submit / wait: four steps with different batches, two in flight at any time (device
-    buffers double buffered) == the same four steps one after the other on the device, bit for bit;
-    every step's pooled outputs are those of the table state it ran on."""
+    """HostStep.submit / wait: six steps with different batches, two in flight at any time (device
+    buffers double buffered) == the same six steps one after the other on the device, bit for bit;
+    every step's pooled outputs are those of the table state it ran on.  Steps 2 and 3 replay the
+    kernels from CUDA graphs (captured on the second use of a buffer set), steps 4 and 5 change the
+    learning rate and run eagerly again."""
     torch = torch_cuda
-    rows, bags, D, B, K = [7, 30000, 977], [2, 3, 9], 64, 5000, 4
+    rows, bags, D, B, K = [7, 30000, 977], [2, 3, 9], 64, 5000, 6
+    lrs = [0.01, 0.01, 0.01, 0.01, 0.02, 0.02]
     Ws, idxs, gs = [], [], []
     for t, (R, L) in enumerate(zip(rows, bags)):
         W = make_inputs(R, D, L, B, seed=500 + t)[0]
@@ -353,16 +387,17 @@ def test_host_steps_in_flight_together_match_sequential_steps(ffemb, oracle, tor
     for k in range(K):
         di = [dev(torch, idxs[t][k]) for t in range(len(rows))]
         seq_out.append([o.cpu().numpy() for o in ca.forward(di)])
-        ca.backward_sgd(di, [dev(torch, gs[t][k]) for t in range(len(rows))], 0.01)
+        ca.backward_sgd(di, [dev(torch, gs[t][k]) for t in range(len(rows))], lrs[k])
     b = [dev(torch, w) for w in Ws]
     hs = ffemb.HostStep(ffemb.EmbeddingCollection(b, bags), B)
-    assert hs.depth == 2
+    assert hs.depth == 2 and hs.use_graph
     h_idx = [[torch.from_numpy(idxs[t][k]).pin_memory() for t in range(len(rows))] for k in range(K)]
     h_g = [[torch.from_numpy(gs[t][k]).pin_memory() for t in range(len(rows))] for k in range(K)]
     h_out = [[torch.empty((B, D)).pin_memory() for _ in rows] for k in range(K)]
-    tickets = [hs.submit(h_idx[k], h_g[k], h_out[k], 0.01) for k in range(K)]
+    tickets = [hs.submit(h_idx[k], h_g[k], h_out[k], lrs[k]) for k in range(K)]
     for k in tickets:
         hs.wait(k)
+    assert hs.graph_replays == 4  # two graphs per step, steps 2 and 3
     for k in range(K):
         for t in range(len(rows)):
             assert np.array_equal(h_out[k][t].numpy(), seq_out[k][t]), (k, t)
