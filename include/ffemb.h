@@ -196,7 +196,10 @@ FFEMB_API int ffemb_backward_dense_batched(const ffemb_table_t *tables, int num_
  *   V[t]       : momentum buffer of table t, [R][D] floats (ignored when momentum == 0; the reference
  *                allocates it zero-initialised, src/runtime/optimizer.cc:50-87)
  *   touched[t] : ffemb_sgd_touched_words(R) 32-bit words, all zero on entry, all zero on return
- * Every table goes through the sorted path; no split (prepare) form.                             */
+ * Every table goes through the sorted path; no split (prepare) form.
+ * Stream capture: unlike the other entry points this one (and the Adam form below) must NOT be
+ * recorded into a CUDA graph — the optimizer arguments are uploaded from a host copy that lives
+ * only for the duration of the call (and Adam's alpha_t changes every step anyway).             */
 typedef struct ffemb_sgd {
   float lr, weight_decay, momentum;
   int32_t nesterov;

@@ -1,14 +1,17 @@
 #!/bin/bash
-# scratch experiment: CUDA-graph replay inside HostStep (e2e of the small configs)
+# scratch experiment: batch slices of the backward (output-grad slab per table kept inside L2)
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "host_step or cuda_graph" > gpurun_out/g_test.log 2>&1
-echo "test rc=$?" >> gpurun_out/g_test.log
-tail -5 gpurun_out/g_test.log
-for w in 1 2; do
-  timeout 300 python bench.py --workload $w --steps 200 --warmup 20 --no-cpu > gpurun_out/h_cfg${w}.json 2> gpurun_out/h_cfg${w}.err
-done
-for f in gpurun_out/h_cfg*.json; do echo $f; python -c "
-import json,sys
-j=json.loads(open('$f').read().strip().splitlines()[-1])
-print(j['ms_per_step'], j['value'], j['gpu_launches'], j['e2e']['ms_per_step'], j['e2e']['value'], j['e2e']['h2d_gbs'], j['e2e']['cuda_graph'])
-" || tail -3 ${f%.json}.err; done
+run() { # tag workload slice_mb
+  FFEMB_BWD_SLICE_MB=$3 timeout 400 python bench.py --workload $2 --steps 20 --warmup 5 --no-cpu --no-e2e --no-overlap --graph off > gpurun_out/s_$1.json 2> gpurun_out/s_$1.err
+  python -c "
+import json
+j=json.loads(open('gpurun_out/s_$1.json').read().strip().splitlines()[-1])
+print('$1', j['ms_per_step'], j['gpu_launches'], j['roofline']['phases_ms_per_step'])
+" || tail -3 gpurun_out/s_$1.err
+}
+run c5_off 5 0
+run c5_64 5 64
+run c5_32 5 32
+run c5_16 5 16
+run c3_off 3 0
+run c3_16 3 16
