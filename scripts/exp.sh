@@ -1,17 +1,21 @@
 #!/bin/bash
-# scratch experiment: batch slices of the backward (output-grad slab per table kept inside L2)
+# scratch: launch lists of the small configs (which kernels make up the graph-replayed step)
 mkdir -p gpurun_out
-run() { # tag workload slice_mb
-  FFEMB_BWD_SLICE_MB=$3 timeout 400 python bench.py --workload $2 --steps 20 --warmup 5 --no-cpu --no-e2e --no-overlap --graph off > gpurun_out/s_$1.json 2> gpurun_out/s_$1.err
-  python -c "
-import json
-j=json.loads(open('gpurun_out/s_$1.json').read().strip().splitlines()[-1])
-print('$1', j['ms_per_step'], j['gpu_launches'], j['roofline']['phases_ms_per_step'])
-" || tail -3 gpurun_out/s_$1.err
-}
-run c5_off 5 0
-run c5_64 5 64
-run c5_32 5 32
-run c5_16 5 16
-run c3_off 3 0
-run c3_16 3 16
+for w in 1 2; do
+  ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 100 --csv --log-file gpurun_out/l_cfg${w}.csv python bench.py --workload $w --steps 2 --warmup 3 --no-e2e --no-cpu --graph off > gpurun_out/l_cfg${w}.log 2>&1
+done
+python - <<'P'
+import csv,re
+for w in (1,2):
+    rows=list(csv.reader(open(f'gpurun_out/l_cfg{w}.csv')))
+    hdr=None;tot=0
+    for r in rows:
+        if 'Kernel Name' in r: hdr=r; continue
+        if hdr and len(r)==len(hdr):
+            d=dict(zip(hdr,r))
+            if d.get('Metric Name')!='gpu__time_duration.sum': continue
+            v=float(d['Metric Value'].replace(',',''))/1e3
+            if int(d['ID'])<14: print(w,d['ID'],re.sub(r'\(.*','',d['Kernel Name'])[:70],d['Grid Size'],d['Block Size'],round(v,1))
+            tot+=v
+    print('total us for 2 steps',round(tot,1))
+P
