@@ -289,6 +289,32 @@ def test_backward_streaming_and_resident_tables_interleaved(ffemb, oracle, torch
         assert np.all(np.abs(alone - got) <= REL_TOL * np.abs(got).max()), t   # repeated rows: tile cuts differ
 
 
+@pytest.mark.parametrize("B,L", [(100, 1), (4096, 1), (4097, 1), (1024, 8), (8193, 1), (16384, 1), (819, 20),
+                                 (16385, 1), (30000, 3)])
+@pytest.mark.parametrize("R", [37, 100000, 3000000])
+def test_backward_sort_is_the_stable_sort_by_row(ffemb, torch_cuda, B, L, R):
+    """White box: after ffemb_backward_prepare the workspace holds the lookups sorted by row with the
+    bags ascending inside a run of equal rows (the summation order of the segmented sum) — checked
+    against numpy's stable sort, from a hundred lookups to beyond one radix-sort tile."""
+    torch = torch_cuda
+    D = 16
+    if ffemb.lib().ffemb_backward_path(R, L, D, B) != 0:
+        pytest.skip("this table takes the bag-major path: nothing is sorted")
+    rng = np.random.default_rng(B * 31 + L + R)
+    idx = rng.integers(0, R, size=(B, L), dtype=np.int64)
+    coll = ffemb.EmbeddingCollection([torch.zeros((R, D), device="cuda")], [L])
+    coll.backward_prepare([dev(torch, idx)])
+    torch.cuda.synchronize()
+    n = B * L
+    seg = (n * 4 + 255) // 256 * 256  # workspace carve: keys_a, keys_b, vals_a, vals_b (256-byte aligned)
+    ws = coll._workspaces(B)[0].cpu().numpy()
+    keys = ws[seg:seg + 4 * n].view(np.uint32)
+    vals = ws[3 * seg:3 * seg + 4 * n].view(np.uint32)
+    order = np.argsort(idx.reshape(-1), kind="stable")
+    assert np.array_equal(keys, idx.reshape(-1)[order].astype(np.uint32))
+    assert np.array_equal(vals, (np.arange(n) // L)[order].astype(np.uint32))  # table 0: value = bag number
+
+
 def test_backward_split_in_prepare_and_apply_is_bit_identical(ffemb, torch_cuda):
     """ffemb_backward_prepare (sort, indices only, here on a side stream) + ffemb_backward_sgd_prepared
     == ffemb_backward_sgd_batched, bit for bit."""
