@@ -1,11 +1,14 @@
 #!/bin/bash
-# scratch: one-CTA sort variants on cfg1 (16384 pairs)
+# scratch: L1 warm-up pass in the upper levels — parity suite, then cfg1 / cfg2 / cfg3
 mkdir -p gpurun_out
-for v in 0 1 2 3 4; do
-  FFEMB_BSORT=$v timeout 300 python bench.py --workload 1 --steps 200 --warmup 20 --no-cpu --no-e2e > gpurun_out/v_$v.json 2> gpurun_out/v_$v.err
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
+tail -2 gpurun_out/pytest_gpu.log
+for w in 1 2 3; do
+  st=200; [ $w = 3 ] && st=50
+  timeout 300 python bench.py --workload $w --steps $st --warmup 10 --no-cpu --no-e2e > gpurun_out/u_cfg${w}.json 2> gpurun_out/u_cfg${w}.err
   python -c "
 import json
-j=json.loads(open('gpurun_out/v_$v.json').read().strip().splitlines()[-1])
-print($v, j['ms_per_step'], j['roofline']['phases_ms_per_step'])
-" || tail -3 gpurun_out/v_$v.err
+j=json.loads(open('gpurun_out/u_cfg${w}.json').read().strip().splitlines()[-1])
+print($w, j['ms_per_step'], j['value'], j['roofline']['phases_ms_per_step'])
+" || tail -3 gpurun_out/u_cfg${w}.err
 done
