@@ -787,11 +787,14 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
   int64_t m = 2 * ntiles1;
   if (ntiles1 > 1) {
     int ups = 1;
-    for (int64_t mm = m; mm > kSmallLevel; mm = 2 * ((mm + CH2 - 1) / CH2)) ups++;
+    // one CTA walks (kThreads / 32) * SLOTS tiles per round: that many tiles of partial slots (256 slots at
+    // D = 128, 2048 at D = 16) finish in the single-CTA tail instead of paying another grid launch
+    const int64_t small_level = (int64_t)kSmallLevel * SLOTS;
+    for (int64_t mm = m; mm > small_level; mm = 2 * ((mm + CH2 - 1) / CH2)) ups++;
     ProfScope prof(FFEMB_PHASE_REDUCE_UP, ups, s);
     int cur = 0;
     K *pk[2] = {pk0, pk1};
-    while (m > kSmallLevel) {  // grid-wide levels while the partial array is large
+    while (m > small_level) {  // grid-wide levels while the partial array is large
       const int64_t tiles = (m + CH2 - 1) / CH2;
       reduce_level_kernel<K, G, C, false, MODE>
           <<<(unsigned)((tiles + slots_per_cta - 1) / slots_per_cta), kThreads, 0, s>>>(

@@ -1,12 +1,14 @@
 #!/bin/bash
-# the other single-GPU BASELINE configs through the full bench line (value, e2e, cpu_baseline)
+# scratch: single-CTA tail threshold scaled with the slots per warp — parity suite, then cfg1 / cfg2 / cfg3
 mkdir -p gpurun_out
-for w in 1 2 5; do
-  timeout 400 python bench.py --workload $w > gpurun_out/final_cfg$w.json 2> gpurun_out/final_cfg$w.err; echo "cfg$w rc=$?"
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
+tail -2 gpurun_out/pytest_gpu.log
+for w in 1 2 3; do
+  st=200; [ $w = 3 ] && st=50
+  timeout 300 python bench.py --workload $w --steps $st --warmup 10 --no-cpu --no-e2e > gpurun_out/t_cfg${w}.json 2> gpurun_out/t_cfg${w}.err
   python -c "
 import json
-d=json.loads(open('gpurun_out/final_cfg$w.json').read().strip().splitlines()[-1])
-r=d['roofline']; e=d.get('e2e',{}); c=d.get('cpu_baseline',{})
-print('cfg$w', round(d['ms_per_step'],4),'ms', '%.4g'%d['value'], 'graph', d['config']['cuda_graph'], 'frac', r['step_frac_of_peak'], 'e2e_ms', round(e.get('ms_per_step',0),4), '%.4g'%e.get('value',0), 'cpu', '%.4g'%c.get('value',0), c.get('cores'), c.get('kind'))
-" || tail -3 gpurun_out/final_cfg$w.err
+j=json.loads(open('gpurun_out/t_cfg${w}.json').read().strip().splitlines()[-1])
+print($w, j['ms_per_step'], j['value'], j['gpu_launches'], j['roofline']['phases_ms_per_step'])
+" || tail -3 gpurun_out/t_cfg${w}.err
 done
