@@ -47,7 +47,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", type=int, default=3, help="BASELINE config number 1..5")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink rows/batch (debug only)")
-    ap.add_argument("--pool", type=int, default=4, help="distinct index batches cycled")
+    ap.add_argument("--pool", type=int, default=16, help="distinct index batches cycled (SURVEY 8d: >= 16)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--placement", default="balanced", choices=["modulo", "balanced"],
@@ -64,7 +64,8 @@ def parse():
                     help="N=1: replay the step from a CUDA graph (StepGraph); auto = the launch-bound small "
                          "configs (<= 2M lookups per step: cfg1, cfg2), where it is worth 1.6-1.9x")
     ap.add_argument("--rows-cap", type=int, default=0, help="cap rows per table (profiling under ncu only)")
-    ap.add_argument("--cpu-batch", type=int, default=16384)
+    ap.add_argument("--cpu-batch", type=int, default=65536,
+                    help="batch of the CPU sample (capped at the workload's batch)")
     ap.add_argument("--cpu-rows-cap", type=int, default=2_000_000)
     return ap.parse_args()
 
@@ -203,6 +204,17 @@ class DeviceWorkload:
         fwd = 8 * n + 4 * D * n + 4 * D * T * B
         bwd = 8 * n + 4 * D * T * B + 8 * D * U
         return fwd, bwd, U
+
+    def compulsory_bytes_per_step(self):
+        """The cache-aware count: §8d credits every lookup with a row read from HBM (4*D*N), which
+        holds only for tables far larger than L2 with no repeats.  Compulsory traffic reads each
+        DISTINCT touched row once per step (4*D*U; a table that fits L2 can at most be credited once
+        per step), and the backward then finds it again only if it is still resident, so its
+        read-modify-write stays at 8*D*U:  fwd = 8N + 4D*U + 4D*T*B ; bwd = 8N + 4D*T*B + 8D*U."""
+        D, B = self.wl.dim, self.wl.batch
+        n, T = self.lookups(), len(self.owned)
+        U = sum(sum(u) / len(u) for u in self.uniq)
+        return 8 * n + 4 * D * U + 4 * D * T * B, 8 * n + 4 * D * T * B + 8 * D * U
 
 
 def main():
@@ -376,19 +388,54 @@ def main():
     # ("small" is excluded too: those kernels are forked onto a side stream and run UNDER the sort / level 1,
     # so their event span is not busy time)
     cand = {k: v for k, v in kernel_phases.items() if alg.get(k, 0) > 0 and k in ("forward", "reduce1", "atomic")}
-    dom = max(cand, key=cand.get) if cand else (max(kernel_phases, key=kernel_phases.get) if kernel_phases else "forward")
+    # cache-aware (compulsory) bytes: the forward reads each DISTINCT row once; level 1 / the atomic
+    # comparison are already counted that way by §8d (one read-modify-write per distinct row)
+    cfwd_b, cbwd_b = dw.compulsory_bytes_per_step()
+    comp = dict(alg)
+    comp["forward"] = cfwd_b
+    # dominant kernel = the longest such phase whose credited bytes DRAM could actually have delivered
+    # (compulsory count within the 1.2 x peak sanity bound); a phase beyond it ran out of cache and says
+    # nothing about HBM
+    order = sorted(cand, key=cand.get, reverse=True)
+    sane = [k for k in order if comp.get(k, 0) / (cand[k] * 1e-3) / 1e9 <= 1.2 * peak]
+    dom = sane[0] if sane else (order[0] if order else (max(kernel_phases, key=kernel_phases.get) if kernel_phases else "forward"))
     dom_ms = kernel_phases.get(dom, ms_step)
     achieved = alg.get(dom, 0) / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    achieved_c = comp.get(dom, 0) / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    # §8d's figure is the headline unless on-chip hits inflate it beyond what DRAM can deliver (the
+    # B200_PROFILING.md sanity bound: a good kernel may read a little above 1.0, far above means the bytes
+    # credited were not moved); then the compulsory count is the figure and the line says so
+    basis = "survey-8d algorithmic bytes"
+    frac = achieved / peak
+    if frac > 1.2:
+        achieved, frac = achieved_c, achieved_c / peak
+        basis = "compulsory bytes (the 8d credit exceeded 1.2 x peak: rows served from L2/L1, not HBM)"
+    traffic = load_traffic(dom) if world == 1 and not args.rows_cap and args.workload == 3 else None
+    step_dram = load_traffic("step_total") if world == 1 and not args.rows_cap and args.workload == 3 else None
+    gbs = lambda b: b / (ms_step * 1e-3) / 1e9
     roof = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-            "frac": round(achieved / peak, 4),
-            "traffic": load_traffic(dom) if world == 1 and not args.rows_cap and args.workload == 3 else None,
+            "frac": round(frac, 4), "frac_basis": basis,
+            "frac_8d": round(alg.get(dom, 0) / (dom_ms * 1e-3) / 1e9 / peak, 4) if dom_ms > 0 else None,
+            "frac_compulsory": round(achieved_c / peak, 4),
+            "traffic": traffic,
             "peak_source": peak_src, "ms_per_launch": round(dom_ms, 4),
             "algorithmic_bytes_per_launch": int(alg.get(dom, 0)),
+            "compulsory_bytes": int(comp.get(dom, 0)),
             "phases_ms_per_step": {k: round(v, 4) for k, v in kernel_phases.items()},
             "step_algorithmic_bytes": int(fwd_b + bwd_b),
-            "step_achieved_gbs": round((fwd_b + bwd_b) / (ms_step * 1e-3) / 1e9, 1),
-            "step_frac_of_peak": round((fwd_b + bwd_b) / (ms_step * 1e-3) / 1e9 / peak, 4),
-            "step_frac_of_8000": round((fwd_b + bwd_b) / (ms_step * 1e-3) / 1e9 / 8000.0, 4)}
+            "step_compulsory_bytes": int(cfwd_b + cbwd_b),
+            "step_achieved_gbs": round(gbs(fwd_b + bwd_b), 1),
+            "step_frac_of_peak": round(gbs(fwd_b + bwd_b) / peak, 4),
+            "step_frac_of_8000": round(gbs(fwd_b + bwd_b) / 8000.0, 4),
+            "step_frac_compulsory": round(gbs(cfwd_b + cbwd_b) / peak, 4),
+            "step_frac_compulsory_of_8000": round(gbs(cfwd_b + cbwd_b) / 8000.0, 4),
+            # DRAM bytes of one whole step as ncu counted them (sum over every kernel of the step, the
+            # radix-sort passes included; profiles/traffic.json, captured at this size)
+            "step_dram_bytes": step_dram,
+            "step_frac_dram": round(gbs(step_dram) / peak, 4) if step_dram else None}
+    if roof["frac"] > 1.2:  # no phase within the bound (everything on chip): the line says so, frac is capped
+        roof["frac_uncapped"], roof["frac"] = roof["frac"], 1.2
+        roof["frac_basis"] += "; CAPPED at the 1.2 sanity bound: this launch ran out of cache, not HBM"
 
     if rank != 0:
         if dist is not None:
@@ -418,6 +465,9 @@ def main():
         line["e2e"] = e2e
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args, wl, steps=3, warmup=1)
+        ref_gpu = reference_gpu_leg(torch, wl, dw, args)
+        if ref_gpu is not None:
+            line["reference_on_b200"] = ref_gpu
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
@@ -501,6 +551,61 @@ def run_rowwise(args, torch, pkg, dist, wl, rank, world, dev):
     return 0
 
 
+def reference_gpu_leg(torch, wl, dw, args):
+    """BASELINE.md 3.2, "reference on B200": the reference's own GPU code for this path, compiled
+    unmodified for sm_100a (oracle/_ref/libffref_gpu.so), timed on the SAME device-resident inputs as
+    the product arm — per table and step: ZeroInitializer::init_task on the dense weight-grad
+    (Op::zero_grad), Embedding::forward_kernel, Embedding::backward_kernel (atomicAdd scatter) and
+    SGDOptimizer::ps_update_task (sgd_update over all R*D elements).  A reported baseline like
+    cpu_baseline (same rule: never the thing shipped); only for workloads whose tables stay below the
+    reference's int cliffs (R*D < 2^31: cfg1, cfg2) and fit a second dense buffer."""
+    try:
+        from oracle import oracle as O
+        if not O.ref_gpu_available() or any(r * wl.dim >= (1 << 31) for r in wl.rows):
+            return None
+        if sum(wl.rows) * wl.dim * 4 > 40e9:
+            return None
+        L = O.ref_gpu()
+        steps, warmup = max(3, min(args.steps, 20)), 3
+        Ws = [w.clone() for w in dw.W]
+        Wg = [torch.empty_like(w) for w in dw.W]
+        stream = torch.cuda.current_stream()
+
+        def step(k):
+            p = k % dw.pool
+            for t in range(len(Ws)):
+                R = int(Ws[t].shape[0])
+                L.ffref_gpu_zero_task(Wg[t].data_ptr(), R, wl.dim)
+                L.ffref_gpu_forward_kernel(dw.idx[t][p].data_ptr(), dw.out[t].data_ptr(), Ws[t].data_ptr(),
+                                           wl.bags[t], wl.dim, wl.batch, wl.aggr, None)
+                L.ffref_gpu_backward_kernel(dw.idx[t][p].data_ptr(), dw.outgrad[t].data_ptr(), Wg[t].data_ptr(),
+                                            wl.bags[t], wl.dim, wl.batch, wl.aggr, None)
+                L.ffref_gpu_sgd_task(Wg[t].data_ptr(), Ws[t].data_ptr(), R, wl.dim, float(wl.lr), 0.0)
+
+        # the reference's tasks run on the legacy default stream (built with DISABLE_LEGION_CUDA_HIJACK)
+        torch.cuda.synchronize()
+        with torch.cuda.stream(torch.cuda.default_stream()):
+            for k in range(warmup):
+                step(k)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(torch.cuda.default_stream())
+            for k in range(steps):
+                step(warmup + k)
+            e1.record(torch.cuda.default_stream())
+            torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        dense = 16 * sum(wl.rows) * wl.dim  # zero-fill 4 + sgd_update 12 bytes per element
+        return {"value": wl.lookups / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": steps,
+                "kind": "reference", "dense_bytes_per_step": int(dense),
+                "what": "oracle/_ref/libffref_gpu.so: the reference's embedding.cu / initializer_kernel.cu / "
+                        "optimizer_kernel.cu compiled unmodified for sm_100a; per table zero-fill + forward_kernel + "
+                        "backward_kernel (atomicAdd) + ps_update_task (sgd_update over every row), same inputs, "
+                        "device-resident (the reference keeps outputs in zero-copy host memory: not charged here)"}
+    except Exception as e:
+        return {"value": None, "unit": UNIT, "what": f"failed: {e!r}"}
+
+
 def load_traffic(phase):
     """dram bytes per launch of the dominant kernel from the committed ncu summary, or None."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
@@ -576,46 +681,74 @@ def run_e2e(torch, pkg, args, wl, dw, ex, fx, dist, dev, barrier, total_lookups)
 # ---------------------------------------------------------------------------------------------
 # CPU arm: the reference's own CPU embedding tasks on the box's host cores
 # ---------------------------------------------------------------------------------------------
-def cpu_arm(args, wl, steps, warmup):
-    """Bounded sample of `wl` on the host: every table (rows capped), batch args.cpu_batch.
+class CpuSample:
+    """Bounded sample of `wl` in host memory: every table (rows capped), batch B, two index batches."""
+
+    def __init__(self, wl, B, cap):
+        import numpy as np
+        self.wl, self.B, self.cap = wl, B, cap
+        rng = np.random.default_rng(1234)
+        self.tabs = []
+        for t in range(wl.num_tables):
+            R = min(wl.rows[t], cap)
+            W = np.empty((R, wl.dim), np.float32)
+            rng.random(out=W, dtype=np.float32)
+            W *= 2 * (1.0 / R) ** 0.5
+            idx = [rng.integers(0, R, (B, wl.bags[t]), dtype=np.int64) for _ in range(2)]
+            g = rng.random((B, wl.dim), dtype=np.float32) * 2 - 1
+            self.tabs.append((R, W, idx, g, np.zeros((R, wl.dim), np.float32)))
+        self.lookups = B * sum(wl.bags)
+
+
+def cpu_arm(wl, sample, steps, warmup, P, full_step=False):
+    """One timing of the CPU path over `sample`.
     Forward = the reference's AVX2 EmbeddingLookup (oracle/_ref, src/ops/embedding.cc:23-319)
     when built, else the oracle port; backward = the reference's backward_task_cpu for bag 1,
     the oracle port of embed_backward (src/ops/embedding.cu:192-217) for multi-hot bags, which
-    the reference's CPU code cannot do.  One task per table, tables spread over P host threads
-    (Legion -ll:cpu P; dlrm_strategy_hetero.cc:28-36)."""
-    import numpy as np
+    the reference's CPU code cannot do (src/ops/embedding.cc:408).  One task per table, tables
+    spread over P host threads (Legion -ll:cpu P; dlrm_strategy_hetero.cc:28-36).
+    full_step: each table's task additionally zero-fills the dense weight-grad before the backward
+    (Op::zero_grad, src/runtime/model.cc:466-490) and runs sgd_update over all R*D elements after it
+    (src/runtime/optimizer_kernel.cu:23-41) — RESTATED on the CPU (oracle port): the reference has no
+    CPU optimizer (SGD_UPD_* are GPU-only, src/runtime/model.cc:2990-3022)."""
     from concurrent.futures import ThreadPoolExecutor
     from oracle import oracle as O
     O.lib()
     have_ref = O.ref_cpu_available(ndebug=True)
-    cores = os.cpu_count() or 1
-    P = min(cores, wl.num_tables)
-    B = min(args.cpu_batch, wl.batch)
-    cap = args.cpu_rows_cap
-    rng = np.random.default_rng(1234)
-    tabs = []
-    for t in range(wl.num_tables):
-        R = min(wl.rows[t], cap)
-        W = np.empty((R, wl.dim), np.float32)
-        rng.random(out=W, dtype=np.float32)
-        W *= 2 * (1.0 / R) ** 0.5
-        idx = [rng.integers(0, R, (B, wl.bags[t]), dtype=np.int64) for _ in range(2)]
-        g = rng.random((B, wl.dim), dtype=np.float32) * 2 - 1
-        tabs.append((R, W, idx, g, np.zeros((R, wl.dim), np.float32)))
     kind = "reference" if have_ref and all(l == 1 for l in wl.bags) else "port"
 
     def run_table(t, p):
-        R, W, idx, g, Wg = tabs[t]
+        R, W, idx, g, Wg = sample.tabs[t]
         L = wl.bags[t]
         if have_ref:
             O.ref_cpu_lookup(idx[p], W, normalize=(wl.aggr != 21), ndebug=True)
         else:
             O.forward(idx[p], W, 122 if wl.aggr != 21 else 21, check_range=False)
+        if full_step:
+            Wg.fill(0.0)
         if have_ref and L == 1:
             O.ref_cpu_backward_task(idx[p], g, Wg, ndebug=True)
         else:
             O.backward_dense(idx[p], g, R, wl.aggr, Wgrad=Wg)
+        if full_step:
+            O.lib().oracle_sgd_update(W.size, wl.lr, 0.0, 0.0, 0, Wg.reshape(-1), None, W.reshape(-1), 1)
 
+    if kind == "reference" and not full_step:
+        # the reference's own task bodies (forward_task_cpu + backward_task_cpu) driven from C++ worker
+        # threads, table t on thread t % P (oracle/ref_glue_cpu.cc): no Python between the tasks.  Built
+        # with the reference's flags; asserts stay on (its Release flags keep them) unless a table has more
+        # rows than the data_size = 1,000,000 the CPU kernel asserts against (src/ops/embedding.cc:71-73,404)
+        import numpy as np
+        nd = max(tb[0] for tb in sample.tabs) > 1_000_000
+        T = wl.num_tables
+        idxb = [np.ascontiguousarray(np.stack(tb[2])) for tb in sample.tabs]
+        outs = [np.empty((sample.B, wl.dim), np.float32) for _ in range(T)]
+        Ws, gs, Wgs = [tb[1] for tb in sample.tabs], [tb[3] for tb in sample.tabs], [tb[4] for tb in sample.tabs]
+        if warmup:
+            O.ref_cpu_run_tables(idxb, outs, Ws, gs, Wgs, P, warmup, ndebug=nd)
+        dt = O.ref_cpu_run_tables(idxb, outs, Ws, gs, Wgs, P, steps, ndebug=nd)
+        return {"value": sample.lookups / (dt / steps), "ms_per_step": dt / steps * 1e3, "kind": kind,
+                "have_ref": True, "driver": "C++ worker threads (ffref_cpu_run_tables)"}
     order = sorted(range(wl.num_tables), key=lambda t: -wl.bags[t])  # longest tasks first
     with ThreadPoolExecutor(P) as pool:
         def one_step(k):
@@ -626,34 +759,61 @@ def cpu_arm(args, wl, steps, warmup):
         for k in range(steps):
             one_step(warmup + k)
         dt = time.perf_counter() - t0
-    lookups = B * sum(wl.bags)
-    return {"value": lookups / (dt / steps), "unit": UNIT, "cores": P, "kind": kind,
-            "ms_per_step": dt / steps * 1e3, "host_cores": cores,
-            "sample": f"{wl.name}: all {wl.num_tables} tables, batch {B} of {wl.batch}, rows capped at {cap}; "
-                      f"fwd={'reference AVX2 EmbeddingLookup (oracle/_ref)' if have_ref else 'oracle port'}, "
+    return {"value": sample.lookups / (dt / steps), "ms_per_step": dt / steps * 1e3, "kind": kind,
+            "have_ref": have_ref}
+
+
+def cpu_report(args, wl, steps, warmup):
+    """cpu_baseline object: task bodies at P = all usable host cores (the headline
+    `value`), the same at P = 1 and P = 4 (the reference scripts' -ll:cpu 4, run_random.sh:9), and the
+    restated full step (dense zero-fill + sgd_update) at P = all."""
+    cores = os.cpu_count() or 1
+    P = min(cores, wl.num_tables)
+    B = min(args.cpu_batch, wl.batch)
+    sample = CpuSample(wl, B, args.cpu_rows_cap)
+    main = cpu_arm(wl, sample, steps, warmup, P)
+    side = max(1, min(steps, 2))
+    by = {str(P): round(main["value"], 1)}
+    for p in (1, 4):
+        if p < P:
+            # bounded: one pass over a quarter of the sample's batch would change the cache behaviour;
+            # instead fewer steps of the same sample
+            by[str(p)] = round(cpu_arm(wl, sample, 1, 0, p)["value"], 1)
+    full = cpu_arm(wl, sample, side, 1 if warmup else 0, P, full_step=True)
+    have_ref, kind = main["have_ref"], main["kind"]
+    return {"value": main["value"], "unit": UNIT, "cores": P, "kind": kind,
+            "ms_per_step": main["ms_per_step"], "host_cores": cores, "steps": steps, "warmup": warmup,
+            "by_threads": by,
+            "full_step": {"value": round(full["value"], 1), "ms_per_step": round(full["ms_per_step"], 3),
+                          "cores": P, "what": "task bodies + RESTATED dense zero-fill and sgd_update over all rows "
+                          "(oracle port; the reference has no CPU optimizer)"},
+            "sample": f"{wl.name}: all {wl.num_tables} tables, batch {B} of {wl.batch}, rows capped at "
+                      f"{args.cpu_rows_cap}; fwd={'reference AVX2 EmbeddingLookup (oracle/_ref)' if have_ref else 'oracle port'}, "
                       f"bwd={'reference backward_task_cpu' if kind == 'reference' else 'oracle port of embed_backward (multi-hot)'}"
-                      f"; task bodies only (no dense zero-fill / sgd_update)"}
+                      f"; `value` = task bodies only (no dense zero-fill / sgd_update), see full_step"}
 
 
 def cpu_baseline(args, wl, steps, warmup):
     try:
-        return cpu_arm(args, wl, steps, warmup)
+        return cpu_report(args, wl, steps, warmup)
     except Exception as e:  # the baseline is a reported figure, never a reason to lose the line
         return {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"failed: {e!r}"}
 
 
 def reference_arm(args, world):
+    """--impl reference: the reference's CPU implementation of the path on the host cores, K timed steps
+    after W warm-up steps as asked; each step is a bounded sample of the workload (stated in `sample`)."""
     pkg = importlib.import_module("dlrm-flexflow_b200")
     wl = pkg.synth.config(args.workload, args.scale)
-    steps, warmup = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
-    r = cpu_arm(args, wl, steps, warmup)
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    r = cpu_report(args, wl, steps, warmup)
     return {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world,
             "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl.name, "tables": wl.num_tables, "dim": wl.dim, "batch": wl.batch,
                        "bags": wl.bags, "aggr": wl.aggr, "index_dist": wl.dist},
-            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
-                             "sample": r["sample"]},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "by_threads",
+                                               "full_step", "host_cores")},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 

@@ -1,6 +1,7 @@
 // ffemb_api.cu — the extern "C" surface of libffemb.so (include/ffemb.h): argument checking,
 // descriptor packing, error text.  No allocation, no synchronisation, no device selection.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -24,6 +25,34 @@ int cuda_fail(cudaError_t e, const char *what) {
   if (e == cudaSuccess) return FFEMB_OK;
   set_error("%s: %s", what, cudaGetErrorString(e));
   return FFEMB_ECUDA;
+}
+
+const Tuning &tuning() {
+  static const Tuning t = [] {
+    auto num = [](const char *name) -> long long {
+      const char *e = getenv(name);
+      return (e && *e) ? atoll(e) : -1;
+    };
+    Tuning x;
+    x.stream_mb = num("FFEMB_STREAM_MB");
+    x.l1_kb = num("FFEMB_L1_KB");
+    x.fwd_perm = (int)num("FFEMB_FWD_PERM");
+    x.fwd_avg_div = (int)num("FFEMB_FWD_AVG_DIV");
+    x.fwd_target = (int)num("FFEMB_FWD_TARGET");
+    x.r1_mix = (int)num("FFEMB_R1_MIX");
+    x.r1_flags = (int)num("FFEMB_R1_FLAGS");
+    x.r1_pipe = (int)num("FFEMB_R1_PIPE");
+    x.r1_ring = (int)num("FFEMB_R1_RING");
+    x.small = (int)num("FFEMB_SMALL");
+    x.small_fork = (int)num("FFEMB_SMALL_FORK");
+    x.up_fused = (int)num("FFEMB_UP_FUSED");
+    x.hot = (int)num("FFEMB_HOT");
+    x.slab_mb = (int)num("FFEMB_SLAB_MB");
+    x.own_sort = (int)num("FFEMB_OWN_SORT");
+    x.xpush = (int)num("FFEMB_XPUSH");
+    return x;
+  }();
+  return t;
 }
 
 // ---- profiling ------------------------------------------------------------------------------

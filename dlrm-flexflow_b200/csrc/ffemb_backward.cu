@@ -9,7 +9,7 @@
 //
 // Pipeline (all tables of a GPU at once):
 //   1. keygen : lookup n=(table t, bag b, slot j) -> key = row_base[t] + idx  (global row id),
-//               val = t*B + b (global bag id).  Lookups are enumerated in (t, b, j) order.
+//               val = (t << 26) | b (table, bag).  Lookups are enumerated in (t, b, j) order.
 //   2. sort   : stable LSD radix sort of (key, val) on the ceil(log2(total_rows)) key bits
 //               (cub::DeviceRadixSort, onesweep) -> equal rows adjacent, bags ascending.
 //   3. level 1: the sorted array is cut into fixed tiles of CH1 entries; a slot of G=D/4 lanes
@@ -58,7 +58,7 @@ __device__ __forceinline__ float4 f4_div(float4 a, float d) {
   return make_float4(a.x / d, a.y / d, a.z / d, a.w / d);
 }
 __device__ __forceinline__ float4 f4_div_rn(float4 a, float d, float r) {
-  return make_float4(div_rn(a.x, d, r), div_rn(a.y, d, r), div_rn(a.z, d, r), div_rn(a.w, d, r));
+  return make_float4(div_exact(a.x, d, r), div_exact(a.y, d, r), div_exact(a.z, d, r), div_exact(a.w, d, r));
 }
 __device__ __forceinline__ float4 ld_f4(const float *p) { return *reinterpret_cast<const float4 *>(p); }
 __device__ __forceinline__ void st_f4(float *p, float4 v) { *reinterpret_cast<float4 *>(p) = v; }
@@ -100,17 +100,15 @@ __device__ __forceinline__ int find_table(const TableBatch &tb, uint64_t key) {
   return lo;
 }
 
-// ---- 3/4. one tile of the segmented sum -----------------------------------------------------
-// LEVEL1: entries are sorted lookups; the row of entry p is outgrad[vals[p]] (scaled by 1/L for
-//         AVG/MEAN, per element, like embedding.cu:210).  No invalid keys inside [0, n).
-// else  : entries are the previous level's partial rows rows_in[p]; keys may be INV
-//         (transparent: skipped, and runs continue across ONE invalid slot — by construction two
-//         partials of the same run are never separated by more than one, see header).
-template <typename K, int G, int C, bool LEVEL1, int MODE>
+// ---- 4. one tile of the upper levels of the segmented sum ------------------------------------
+// Entries are the previous level's partial rows rows_in[p]; keys may be INV (transparent: skipped,
+// and runs continue across ONE invalid slot — by construction two partials of the same run are
+// never separated by more than one, see header).  (Level 1, whose entries are sorted lookups, has
+// its own kernels: reduce1_kernel / reduce1_ring_kernel.)
+template <typename K, int G, int C, int MODE>
 __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
-                                            const uint32_t *vals,
                                             const float *rows_in, int64_t n, int64_t tile, int CH,
-                                            bool active, int D, uint32_t B, int aggr, float lr,
+                                            bool active, int D, float lr,
                                             K *keys_out, float *rows_out, int sub, int sl,
                                             const OptArgs *oa = nullptr) {
   constexpr K INV = KeyTraits<K>::INV;
@@ -131,15 +129,13 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
   for (int64_t p0 = t0; p0 < t0 + CH; p0 += G) {  // trip count uniform across the warp
     const int64_t p = p0 + sl;
     K k = INV, kn = INV, kn2 = INV;
-    uint32_t v = 0;
     if (p < t1) {
       k = keys[p];
       if (p + 1 < n) kn = keys[p + 1];
-      if (!LEVEL1 && p + 2 < n) kn2 = keys[p + 2];
-      if (LEVEL1) v = vals[p];
+      if (p + 2 < n) kn2 = keys[p + 2];
     }
     // does the run of entry p stop at p?  (lookahead crosses the tile edge on purpose)
-    const bool is_end = (k != INV) && !(kn == k || (!LEVEL1 && kn == INV && kn2 == k));
+    const bool is_end = (k != INV) && !(kn == k || (kn == INV && kn2 == k));
 
     for (int jj = 0; jj < G; jj += UNR) {
       if (p0 + jj >= t0 + CH) break;  // uniform
@@ -147,38 +143,25 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
       K ek[UNR];
       bool eend[UNR];
       float *wp[UNR];
-      float scale[UNR];
       int et[UNR];
 #pragma unroll
       for (int u = 0; u < UNR; u++) {
         const int src = sub * G + jj + u;
         ek[u] = shfl_key<K>(k, src);
-        const uint32_t ev = __shfl_sync(0xffffffffu, v, src);
         eend[u] = __shfl_sync(0xffffffffu, (int)is_end, src) != 0;
         wp[u] = nullptr;
-        scale[u] = 1.0f;
         et[u] = 0;
         if (jj + u < G && ek[u] != INV) {
-          const float *gp;
-          if (LEVEL1) {
-            const uint32_t t = ev / B;
-            const uint32_t b = ev - t * B;
-            et[u] = (int)t;
-            gp = tb.t[t].out + (int64_t)b * tb.og_stride;
-            if (aggr != FFEMB_AGGR_SUM) scale[u] = (float)tb.t[t].L;
-            if (eend[u]) wp[u] = tb.t[t].table + (int64_t)(ek[u] - tb.row_base[t]) * D;
-          } else {
-            gp = rows_in + (p0 + jj + u) * (int64_t)D;
-            if (eend[u]) {
-              const int t = find_table(tb, (uint64_t)ek[u]);
-              et[u] = t;
-              wp[u] = tb.t[t].table + (int64_t)((uint64_t)ek[u] - tb.row_base[t]) * D;
-            }
+          const float *gp = rows_in + (p0 + jj + u) * (int64_t)D;
+          if (eend[u]) {
+            const int t = find_table(tb, (uint64_t)ek[u]);
+            et[u] = t;
+            wp[u] = tb.t[t].table + (int64_t)((uint64_t)ek[u] - tb.row_base[t]) * D;
           }
 #pragma unroll
           for (int c = 0; c < C; c++) {
             if (sl + c * G < D4) {
-              g[u][c] = LEVEL1 ? ldg_row(gp + 4 * (sl + c * G)) : ld_f4(gp + 4 * (sl + c * G));
+              g[u][c] = ld_f4(gp + 4 * (sl + c * G));
               if (wp[u]) w[u][c] = ld_f4(wp[u] + 4 * (sl + c * G));
             }
           }
@@ -194,16 +177,12 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
           const int64_t q = p0 + jj + u;
           K km1 = INV, km2 = INV;
           if (q >= 1) km1 = keys[q - 1];
-          if (!LEVEL1 && q >= 2) km2 = keys[q - 2];
-          first_open = (km1 == ek[u]) || (!LEVEL1 && km1 == INV && km2 == ek[u]);
+          if (q >= 2) km2 = keys[q - 2];
+          first_open = (km1 == ek[u]) || (km1 == INV && km2 == ek[u]);
         }
 #pragma unroll
         for (int c = 0; c < C; c++) {
-          if (sl + c * G < D4) {
-            float4 x = g[u][c];
-            if (LEVEL1 && aggr != FFEMB_AGGR_SUM) x = f4_div(x, scale[u]);
-            f4_add(acc[c], x);
-          }
+          if (sl + c * G < D4) f4_add(acc[c], g[u][c]);
         }
         pending = true;
         pend_key = ek[u];
@@ -517,18 +496,18 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
 #include "ffemb_reduce1_ring.cuh"
 namespace ffemb {
 
-template <typename K, int G, int C, bool LEVEL1, int MODE>
+template <typename K, int G, int C, int MODE>
 __global__ void __launch_bounds__(kThreads)
-reduce_level_kernel(const __grid_constant__ TableBatch tb, const K *keys, const uint32_t *vals,
-                    const float *rows_in, int64_t n, int CH, int D, uint32_t B, int aggr, float lr,
+reduce_level_kernel(const __grid_constant__ TableBatch tb, const K *keys,
+                    const float *rows_in, int64_t n, int CH, int D, float lr,
                     K *keys_out, float *rows_out, const OptArgs *oa) {
   constexpr int SLOTS = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int sub = lane / G, sl = lane % G;
   const int64_t tile = ((int64_t)blockIdx.x * (kThreads / 32) + warp) * SLOTS + sub;
   const int64_t ntiles = (n + CH - 1) / CH;
-  reduce_tile<K, G, C, LEVEL1, MODE>(tb, keys, vals, rows_in, n, tile, CH, tile < ntiles, D, B,
-                                     aggr, lr, keys_out, rows_out, sub, sl, oa);
+  reduce_tile<K, G, C, MODE>(tb, keys, rows_in, n, tile, CH, tile < ntiles, D, lr, keys_out, rows_out,
+                             sub, sl, oa);
 }
 
 // All remaining levels in ONE CTA: level i reads buffer (i&1), writes buffer ((i+1)&1).
@@ -547,8 +526,7 @@ reduce_tail_kernel(const __grid_constant__ TableBatch tb, K *keys_a, float *rows
     const int64_t ntiles = (n + CH - 1) / CH;
     for (int64_t base = 0; base < ntiles; base += nslots) {
       const int64_t tile = base + slot;
-      reduce_tile<K, G, C, false, MODE>(tb, kin, nullptr, rin, n, tile, CH, tile < ntiles, D, 1u,
-                                        FFEMB_AGGR_SUM, lr, kout, rout, sub, sl, oa);
+      reduce_tile<K, G, C, MODE>(tb, kin, rin, n, tile, CH, tile < ntiles, D, lr, kout, rout, sub, sl, oa);
     }
     if (ntiles <= 1) break;
     __syncthreads();  // partial rows written by this CTA are visible to it after the barrier
@@ -747,12 +725,12 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     // CTAs [0, split) hold the streaming tables' lookups (they come first in the key order)
     uint32_t split = (uint32_t)((n_stream + EPC - 1) / EPC);
     if (n_stream == 0 || n_stream >= n) split = 0;
-    if (const char *e = getenv("FFEMB_R1_MIX")) { if (!atoi(e)) split = 0; }  // tuning aid
+    if (tuning().r1_mix == 0) split = 0;  // tuning aid
     // output-grad of one table larger than (half of) L2 -> the gathers miss: pipelined variant
     bool pipe = B * (int64_t)D * 4 > (48ll << 20);
     int flags = 0;
-    if (const char *e = getenv("FFEMB_R1_FLAGS")) flags = atoi(e);  // tuning aid
-    if (const char *e = getenv("FFEMB_R1_PIPE")) pipe = atoi(e) != 0;
+    if (tuning().r1_flags >= 0) flags = tuning().r1_flags;  // tuning aid
+    if (tuning().r1_pipe >= 0) pipe = tuning().r1_pipe != 0;
     const size_t sm_sum = EPC * sizeof(EntryDesc), sm_avg = EPC * (sizeof(EntryDesc) + sizeof(float2));
     auto go = [&](auto kern, size_t sm) {
       kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], flags, split, oa);
@@ -764,7 +742,7 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     // otherwise.  FFEMB_R1_RING=0|4|8 / FFEMB_R1_PIPE override (tuning aids).
     bool pipe_done = false;
     int ring = 4;
-    if (const char *e = getenv("FFEMB_R1_RING")) ring = atoi(e);
+    if (tuning().r1_ring >= 0) ring = tuning().r1_ring;
     if (C == 1 && ring > 0) {
       auto gor = [&](auto kern, int S) {
         const size_t sm = EPC * sizeof(EntryDesc) + (size_t)(T1 / 32) * S * 2 * 32 * 16;
@@ -796,10 +774,9 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     K *pk[2] = {pk0, pk1};
     while (m > small_level) {  // grid-wide levels while the partial array is large
       const int64_t tiles = (m + CH2 - 1) / CH2;
-      reduce_level_kernel<K, G, C, false, MODE>
+      reduce_level_kernel<K, G, C, MODE>
           <<<(unsigned)((tiles + slots_per_cta - 1) / slots_per_cta), kThreads, 0, s>>>(
-              tb, pk[cur], nullptr, c.prows[cur], m, CH2, D, 1u, FFEMB_AGGR_SUM, lr, pk[cur ^ 1],
-              c.prows[cur ^ 1], oa);
+              tb, pk[cur], c.prows[cur], m, CH2, D, lr, pk[cur ^ 1], c.prows[cur ^ 1], oa);
       m = 2 * tiles;
       cur ^= 1;
     }
@@ -847,7 +824,7 @@ struct SideStream {
 };
 static SideStream *side_stream() {
   static thread_local SideStream ctx[32];
-  static const bool enabled = [] { const char *e = getenv("FFEMB_SMALL_FORK"); return !e || atoi(e) != 0; }();
+  const bool enabled = tuning().small_fork != 0;
   if (!enabled) return nullptr;
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 32) return nullptr;

@@ -36,12 +36,7 @@ static constexpr int kSmallThreads = 512, kSmallCtas = 148 * 2, kChunkBags = 16;
 
 // 0 = sorted path, 1 = tiny (register accumulators), 2 = small (shared-memory accumulator)
 int backward_path(int64_t R, int64_t L, int64_t D, int64_t B) {
-  static int enabled = -1;
-  if (enabled < 0) {
-    const char *e = getenv("FFEMB_SMALL");  // tuning aid: FFEMB_SMALL=0 forces the sorted path
-    enabled = e ? atoi(e) : 1;
-  }
-  if (!enabled) return 0;
+  if (tuning().small == 0) return 0;  // tuning aid: FFEMB_SMALL=0 forces the sorted path
   if (D % 4 != 0 || D < 32 || D > 128 || L < 1 || L > kSmallMaxBag || R < 1) return 0;
   const int64_t n = B * L;
   if (n < 16384 || n < 16 * R) return 0;  // little duplication / little work: sorting is fine
@@ -64,7 +59,7 @@ __device__ __forceinline__ int find_by_cta(const TableBatch &tb, uint32_t cta) {
 }
 
 __device__ __forceinline__ float4 f4_scale_div(float4 a, float d, float r) {
-  return make_float4(div_rn(a.x, d, r), div_rn(a.y, d, r), div_rn(a.z, d, r), div_rn(a.w, d, r));
+  return make_float4(div_exact(a.x, d, r), div_exact(a.y, d, r), div_exact(a.z, d, r), div_exact(a.w, d, r));
 }
 
 // ---- chunk staging shared by both kernels ---------------------------------------------------------
@@ -277,7 +272,7 @@ bwd_small_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, float 
     const int rank = __popc(m & ((1u << lane) - 1u));
     if (rank == 0 && row >= 0) wcnt[warp * NBIN + bin] = __popc(m);
     if (AVG)  // gradient = output-grad / in_dim per element, once per staged row (embedding.cu:210)
-      for (int i = threadIdx.x; i < nb * D; i += kSmallThreads) gb[i] = div_rn(gb[i], Lf, Linv);
+      for (int i = threadIdx.x; i < nb * D; i += kSmallThreads) gb[i] = div_exact(gb[i], Lf, Linv);
     __syncthreads();  // (b)
     // 2. per bin: exclusive prefix of the per-batch counts (lane = batch)
     for (int o = warp; o < NBIN; o += NW) {

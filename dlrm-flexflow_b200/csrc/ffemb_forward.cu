@@ -47,9 +47,7 @@ __device__ __forceinline__ void f4_mul(float4 &a, float m) {
 //                      the IEEE division (a rare, well-predicted branch).
 __device__ __forceinline__ float avg_div(float a, float d, float r, bool pow2) {
   if (pow2) return a * r;
-  float q = div_rn(a, d, r);
-  if (fabsf(a) < 7.9e-31f) q = a / d;
-  return q;
+  return div_exact(a, d, r);  // tiny / zero / inf / nan accumulators take the IEEE division
 }
 // The general form is NOT inlined: the pipelined walk is unrolled 64 lookups deep, and the residual
 // correction + fallback per element made the AVG kernel 268 KB of code — it then ran out of the
@@ -94,7 +92,7 @@ template <int G, int C, int AG, int UNR, bool FULL, bool TINY, bool EXCH>
 __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const float *__restrict__ W,
                                          float *op, int L, int D, int nl, int nl_max, int sl,
                                          uint64_t pol_rows, uint64_t pol_stream, const OutMap &om,
-                                         int64_t bag0, uint32_t col) {
+                                         int64_t bag0, uint32_t col, bool check_hi) {
   constexpr int K = FwdCfg<G>::K, CH = G * K, NG = CH / UNR;
   static_assert(CH % UNR == 0 && NG % 2 == 0, "group pipeline needs an even number of groups");
   const int D4 = D >> 2;
@@ -106,13 +104,16 @@ __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const f
   for (int c = 0; c < C; c++) own[c] = FULL || (sl + c * G < D4);
 
   uint32_t cur[K], nxt[K];
+  uint32_t hi_or = 0u;  // OR of the upper halves of every index read (row numbers travel as 32 bits)
 #pragma unroll
   for (int k = 0; k < K; k++) nxt[k] = 0u;
   auto load_idx = [&](uint32_t (&r)[K], int base) {
 #pragma unroll
     for (int k = 0; k < K; k++) {
       const int e = base + k * G + sl;
-      r[k] = e < nl ? (uint32_t)ldg_idx_stream(ip + e, pol_stream) : 0u;
+      const int64_t v = e < nl ? ldg_idx_stream(ip + e, pol_stream) : 0ll;
+      r[k] = (uint32_t)v;
+      hi_or |= (uint32_t)((uint64_t)v >> 32);
     }
   };
   float4 v[2][UNR][C];
@@ -201,6 +202,10 @@ __device__ __forceinline__ void fwd_slot(const int64_t *__restrict__ ip, const f
 #pragma unroll
     for (int k = 0; k < K; k++) cur[k] = nxt[k];
   }
+  // The row count is unknown to the single-table entry point (Embedding::forward_kernel has no such
+  // argument), so the host cannot rule out rows beyond 2^32 there: an index that does not fit 32 bits
+  // (or a negative one) stops the kernel instead of gathering a wrong row silently.
+  if (check_hi && hi_or) __trap();
 }
 
 template <int G, int C, int AG, int UNR, bool FULL, bool EXCH>
@@ -250,9 +255,9 @@ fwd_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target, 
   const int64_t bytes = td.R * (int64_t)D * 4;
   const uint64_t pol_rows = bytes > stream_bytes ? pol_stream : policy_evict_normal();
   if (td.R > 0 && bytes <= l1_bytes)
-    fwd_slot<G, C, AG, UNR, FULL, true, EXCH>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream, om, bag0, td.lookup_base);
+    fwd_slot<G, C, AG, UNR, FULL, true, EXCH>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream, om, bag0, td.lookup_base, false);
   else
-    fwd_slot<G, C, AG, UNR, FULL, false, EXCH>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream, om, bag0, td.lookup_base);
+    fwd_slot<G, C, AG, UNR, FULL, false, EXCH>(ip, W, op, L, D, nl, nl_max, sl, pol_rows, pol_stream, om, bag0, td.lookup_base, td.R == 0);
 }
 
 // ---- AGGR_MODE_AVG as the reference computes it (divide inside the bag loop) ----------------
@@ -347,15 +352,15 @@ static void launch_vec2(const TableBatch &tb, int D, int64_t B, int ag, int targ
                         const OutMap &om, cudaStream_t s) {
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
   int64_t stream_bytes = kStreamBytes;
-  if (const char *e = getenv("FFEMB_STREAM_MB")) stream_bytes = atoll(e) << 20;  // tuning aid
+  if (tuning().stream_mb >= 0) stream_bytes = tuning().stream_mb << 20;  // tuning aid
   bool p2 = true;  // AVG: every bag width a power of two -> the in-loop divide is one exact multiply
   for (int t = 0; t < tb.num_tables; t++) p2 = p2 && (tb.t[t].L & (tb.t[t].L - 1)) == 0;
   int64_t l1_bytes = kL1Bytes;
-  if (const char *e = getenv("FFEMB_L1_KB")) l1_bytes = atoll(e) << 10;  // tuning aid
+  if (tuning().l1_kb >= 0) l1_bytes = tuning().l1_kb << 10;  // tuning aid
   // CTA -> work item permutation: odd-ish multiplier near the golden ratio of the grid, coprime with it
   uint32_t pmul = 1;
   bool perm = tb.num_tables > 1;
-  if (const char *e = getenv("FFEMB_FWD_PERM")) perm = atoi(e) != 0;  // tuning aid
+  if (tuning().fwd_perm >= 0) perm = tuning().fwd_perm != 0;  // tuning aid
   if (perm && ctas > 2) {
     auto gcd = [](uint32_t a, uint32_t b) { while (b) { const uint32_t r = a % b; a = b; b = r; } return a; };
     pmul = (uint32_t)((double)ctas * 0.6180339887) | 1u;
@@ -381,7 +386,7 @@ static void launch_vec(const TableBatch &tb_in, int D, int64_t B, int ag, const 
   // AVG-literal: the pipelined kernel with the in-loop divide done by avg_div; the one-bag-per-slot
   // kernel with the IEEE division subroutine is kept as the measured comparison (FFEMB_FWD_AVG_DIV=1)
   bool avg_old = false;
-  if (const char *e = getenv("FFEMB_FWD_AVG_DIV")) avg_old = atoi(e) != 0;
+  if (tuning().fwd_avg_div >= 0) avg_old = tuning().fwd_avg_div != 0;
   if (ag == AG_AVG && avg_old) {
     const int64_t per_cta = (int64_t)(kThreads / 32) * SLOTS;
     dim3 grid((unsigned)((B + per_cta - 1) / per_cta), tb_in.num_tables);
@@ -394,7 +399,7 @@ static void launch_vec(const TableBatch &tb_in, int D, int64_t B, int ag, const 
   for (int t = 0; t < tb.num_tables; t++) n += B * (tb.t[t].L > 0 ? tb.t[t].L : 1);
   int target = 8;
   while (target < kFwdTargetMax && n / (2 * target) >= (int64_t)148 * 64 * SLOTS) target *= 2;
-  if (const char *e = getenv("FFEMB_FWD_TARGET")) target = atoi(e);  // tuning aid
+  if (tuning().fwd_target > 0) target = tuning().fwd_target;  // tuning aid
   uint32_t ctas = 0;
   for (int t = 0; t < tb.num_tables; t++) {
     tb.cta_base[t] = ctas;

@@ -55,6 +55,15 @@ struct OutMap {
 void set_error(const char *fmt, ...);
 int cuda_fail(cudaError_t e, const char *what);
 
+// Tuning aids (FFEMB_* environment variables, A/B runs only).  Read ONCE per process on first use
+// (ffemb_api.cu), never on the launch path; -1 = not set, the built-in default applies.
+struct Tuning {
+  long long stream_mb, l1_kb;
+  int fwd_perm, fwd_avg_div, fwd_target, r1_mix, r1_flags, r1_pipe, r1_ring, small, small_fork,
+      up_fused, hot, slab_mb, own_sort, xpush;
+};
+const Tuning &tuning();
+
 // profiling hooks (ffemb_api.cu): no-ops unless ffemb_profile_enable(1)
 void prof_begin(int phase, cudaStream_t s);
 void prof_end(int phase, int launches, cudaStream_t s);
@@ -270,6 +279,15 @@ __device__ __forceinline__ float div_rn(float a, float d, float r) {
   float q = a * r;
   q = fmaf(fmaf(-d, q, a), r, q);
   q = fmaf(fmaf(-d, q, a), r, q);
+  return q;
+}
+// The same quotient for EVERY input: outside the range where the residual trick is exact (tiny
+// values whose residual a - d*q would underflow, zero, inf, nan) the IEEE division takes over — a
+// rare, well-predicted branch.  Bit-identical to a / d.
+__device__ __forceinline__ float div_exact(float a, float d, float r) {
+  float q = div_rn(a, d, r);
+  const float m = fabsf(a);
+  if (!(m >= 7.9e-31f && m <= 3.0e38f)) q = a / d;
   return q;
 }
 __device__ __forceinline__ int64_t shfl_i64(int64_t v, int src) {

@@ -95,9 +95,17 @@ void Embedding::forward_task(const Task *task, const std::vector<PhysicalRegion>
   TensorAccessorW<float, 2> out(regions[1], task->regions[1], FID_DATA, ctx, runtime, false);
   TensorAccessorR<float, 2> tab(regions[2], task->regions[2], FID_DATA, ctx, runtime);
   const Shape f = shape_of(in, out, tab);
-  die_unless_ok(ffemb_forward(in.ptr, out.ptr, tab.ptr, f.bag, f.dim, f.batch, (int)m->aggr,
-                              task_stream()),
-                "ffemb_forward");
+  // the task knows the row count from the table's rectangle, the raw-pointer wrapper above does not:
+  // with it the library can pick the 64-bit row path for tables of more than 2^32 rows
+  ffemb_table_t one;
+  one.idx = in.ptr;
+  one.out = out.ptr;
+  one.table = const_cast<float *>(tab.ptr);
+  one.R = f.rows;
+  one.L = (int32_t)f.bag;
+  one.reserved = 0;
+  die_unless_ok(ffemb_forward_batched(&one, 1, f.dim, f.batch, (int)m->aggr, task_stream()),
+                "ffemb_forward_batched");
   if (m->profiling) checkCUDA(cudaDeviceSynchronize());
 }
 

@@ -82,7 +82,10 @@ FFEMB_API int ffemb_version(void);
 /* ---- forward: replaces Embedding::forward_kernel ------------------------------------------
  * out[b][d] = pool_j table[idx[b][j]][d]; every element of out is written (region is
  * WRITE_ONLY in the reference).  Accumulation is sequential in j per output element, so SUM
- * and AVG(REF_LITERAL) are bit-identical to embed_forward.                                   */
+ * and AVG(REF_LITERAL) are bit-identical to embed_forward.  ffemb_forward has no row count (neither
+ * has the wrapper it replaces): row numbers are carried as 32 bits there, and an index >= 2^32 (or
+ * negative) TRAPS the kernel rather than gathering a wrong row; tables of more than 2^32 rows go
+ * through ffemb_forward_batched with R set, which then takes the 64-bit path.                 */
 FFEMB_API int ffemb_forward(const int64_t *idx, float *out, const float *table, int64_t L, int64_t D,
                   int64_t B, int aggr, ffemb_stream_t stream);
 
