@@ -52,6 +52,13 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--placement", default="balanced", choices=["modulo", "balanced"],
                     help="N>1: modulo = the reference's t %% G; balanced = greedy by measured per-lookup cost")
+    ap.add_argument("--groups", type=int, default=2,
+                    help="N>1, fused exchange: pipeline groups per rank (1 = forward(all), push(all), backward(all))")
+    ap.add_argument("--trace", action="store_true",
+                    help="N>1: after the timed region, one more step with CUDA events around every piece of the "
+                         "pipelined schedule; per-rank timelines go to stderr (tuning aid)")
+    ap.add_argument("--no-split", action="store_true",
+                    help="N>1: keep every table whole (no column split of heavy tables)")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="N>1: fused = pooled rows stored straight into the peer's Concat input by the "
                          "gather-pool kernel (NVLink peer memory); nccl = all_to_all_single + pack/unpack copies")
@@ -170,15 +177,23 @@ def zipf_indices(torch, gen, rows, shape, alpha, table_id, dev):
 
 
 class DeviceWorkload:
-    def __init__(self, torch, pkg, wl, owned, dev, pool, seed):
-        self.torch, self.wl, self.owned, self.dev = torch, wl, owned, dev
+    """This rank's parts (sharding.Part: whole tables, or column ranges of split ones) with their
+    synthetic inputs.  Index batches are seeded per TABLE, so the ranks that share a split table see the
+    same indices."""
+
+    def __init__(self, torch, pkg, wl, parts, dev, pool, seed):
+        self.torch, self.wl, self.parts, self.dev = torch, wl, parts, dev
+        self.owned = [p.table for p in parts]
+        self.widths = [p.width for p in parts]
         g = torch.Generator(device=dev)
         self.W, self.idx, self.outgrad, self.out, self.uniq = [], [], [], [], []
-        for t in owned:
-            g.manual_seed(seed + t)
+        for p in parts:
+            t = p.table
             R, L = wl.rows[t], wl.bags[t]
             a = (1.0 / R) ** 0.5  # examples/cpp/DLRM/dlrm.cc:44-45
-            self.W.append(torch.empty((R, wl.dim), dtype=torch.float32, device=dev).uniform_(-a, a, generator=g))
+            g.manual_seed(seed + t + 1000 * p.col0)
+            self.W.append(torch.empty((R, p.width), dtype=torch.float32, device=dev).uniform_(-a, a, generator=g))
+            g.manual_seed(seed + t)
             batches = []
             for k in range(pool):
                 if wl.dist == "zipf":
@@ -187,22 +202,34 @@ class DeviceWorkload:
                     batches.append(torch.randint(0, R, (wl.batch, L), dtype=torch.int64, device=dev, generator=g))
             self.idx.append(batches)
             self.uniq.append([int(torch.unique(b).numel()) for b in batches])
-            self.outgrad.append(torch.empty((wl.batch, wl.dim), dtype=torch.float32, device=dev).uniform_(-1, 1, generator=g))
-            self.out.append(torch.empty((wl.batch, wl.dim), dtype=torch.float32, device=dev))
+            self.outgrad.append(torch.empty((wl.batch, p.width), dtype=torch.float32, device=dev).uniform_(-1, 1, generator=g))
+            self.out.append(torch.empty((wl.batch, p.width), dtype=torch.float32, device=dev))
         self.pool = pool
-        self.coll = pkg.EmbeddingCollection(self.W, [wl.bags[t] for t in owned], wl.aggr) if owned else None
+        # one collection per pipeline group (a group's parts share one width)
+        self.K = 1 + max((p.group for p in parts), default=0)
+        self.group_of = [[i for i, p in enumerate(parts) if p.group == k] for k in range(self.K)]
+        self.colls = [pkg.EmbeddingCollection([self.W[i] for i in ids], [wl.bags[parts[i].table] for i in ids], wl.aggr)
+                      if ids else None for ids in self.group_of]
+        self.coll = self.colls[0] if self.K == 1 else None
 
     def lookups(self):
+        """lookups this rank walks (a column-split table's lookups are walked by every rank of the split)"""
         return sum(self.wl.batch * self.wl.bags[t] for t in self.owned)
+
+    def frac(self, i):
+        return self.widths[i] / float(self.wl.dim)
 
     def bytes_per_step(self):
         """SURVEY §8d algorithmic bytes for the owned tables, averaged over the pool:
         fwd = 8N + 4DN + 4D*T*B ; bwd = 8N + 4D*T*B + 8D*U."""
-        D, B = self.wl.dim, self.wl.batch
-        n, T = self.lookups(), len(self.owned)
-        U = sum(sum(u) / len(u) for u in self.uniq)
-        fwd = 8 * n + 4 * D * n + 4 * D * T * B
-        bwd = 8 * n + 4 * D * T * B + 8 * D * U
+        B = self.wl.batch
+        fwd = bwd = U = 0.0
+        for i, t in enumerate(self.owned):
+            w, n = self.widths[i], B * self.wl.bags[t]
+            u = sum(self.uniq[i]) / len(self.uniq[i])
+            fwd += 8 * n + 4 * w * n + 4 * w * B
+            bwd += 8 * n + 4 * w * B + 8 * w * u
+            U += u * self.frac(i)
         return fwd, bwd, U
 
     def compulsory_bytes_per_step(self):
@@ -211,10 +238,14 @@ class DeviceWorkload:
         DISTINCT touched row once per step (4*D*U; a table that fits L2 can at most be credited once
         per step), and the backward then finds it again only if it is still resident, so its
         read-modify-write stays at 8*D*U:  fwd = 8N + 4D*U + 4D*T*B ; bwd = 8N + 4D*T*B + 8D*U."""
-        D, B = self.wl.dim, self.wl.batch
-        n, T = self.lookups(), len(self.owned)
-        U = sum(sum(u) / len(u) for u in self.uniq)
-        return 8 * n + 4 * D * U + 4 * D * T * B, 8 * n + 4 * D * T * B + 8 * D * U
+        B = self.wl.batch
+        fwd = bwd = 0.0
+        for i, t in enumerate(self.owned):
+            w, n = self.widths[i], B * self.wl.bags[t]
+            u = sum(self.uniq[i]) / len(self.uniq[i])
+            fwd += 8 * n + 4 * w * u + 4 * w * B
+            bwd += 8 * n + 4 * w * B + 8 * w * u
+        return fwd, bwd
 
 
 def main():
@@ -243,29 +274,38 @@ def main():
         wl.name += f"-rowscap{args.rows_cap}"
     if args.workload == 4 and world > 1:
         return run_rowwise(args, torch, pkg, dist, wl, rank, world, dev)
-    own = placement(wl, world, args.placement)
-    owned = [t for t in range(wl.num_tables) if own[t] == rank]
-    dw = DeviceWorkload(torch, pkg, wl, owned, dev, args.pool, seed=1234)
-    ex = fx = None
+    # shard plan: whole tables by t % N (the reference's generator) or by cost, heavy tables split by
+    # columns, this rank's parts dealt into pipeline groups (sharding.plan_shards); the NCCL comparison
+    # form moves whole tables only
+    fused = world > 1 and args.exchange == "fused"
+    plan = pkg.sharding.plan_shards(wl.rows, wl.bags, wl.dim, world, args.placement,
+                                    split=fused and not args.no_split, groups=args.groups if fused else 1)
+    own = [next(p.rank for p in plan if p.table == t) for t in range(wl.num_tables)]
+    mine = sorted([p for p in plan if p.rank == rank], key=lambda p: (p.group, p.table, p.col0))
+    owned = [p.table for p in mine]
+    dw = DeviceWorkload(torch, pkg, wl, mine, dev, args.pool, seed=1234)
+    ex = fx = sstep = None
     if world > 1 and args.exchange == "nccl":
         ex = pkg.exchange.TableWiseExchange(wl.num_tables, own, wl.batch, wl.dim, rank, world, dev)
     elif world > 1:
-        fx = pkg.exchange.FusedTableWiseExchange(wl.num_tables, own, wl.batch, wl.dim, rank, world, dev)
-        fx.dx.uniform_(-1, 1)
+        fx = pkg.exchange.FusedTableWiseExchange(wl.num_tables, own, wl.batch, wl.dim, rank, world, dev, parts=plan)
+        g = torch.Generator(device=dev).manual_seed(4321 + rank)
+        fx.dx.uniform_(-1, 1, generator=g)
         dw.outgrad = fx.outgrads  # the owners' output-grad buffers are the peers' push targets
+        sstep = pkg.exchange.ShardedStep(fx, dw.colls, dev)
     stream = torch.cuda.current_stream()
 
     wgrads = None
     if args.backward == "atomic":  # the measured comparison: dense grad + atomics + dense update
         wgrads = [torch.zeros_like(w) for w in dw.W]
 
-    overlap = not args.no_overlap and args.backward == "sorted" and dw.coll is not None
-    side = torch.cuda.Stream(device=dev) if overlap else None
+    overlap = not args.no_overlap and args.backward == "sorted" and (dw.coll is not None or fx is not None)
+    side = torch.cuda.Stream(device=dev) if overlap and fx is None else None
 
     def presort(idx):
         """keygen + radix sort on the side stream: needs the indices only, so it runs under the
         forward pass and the exchange; the main stream joins before the segmented sum."""
-        if overlap:
+        if overlap and fx is None:
             side.wait_stream(stream)  # the previous step's reduction is done with the sort buffers
             dw.coll.backward_prepare(idx, stream=side)
 
@@ -274,12 +314,9 @@ def main():
         idx = [b[p] for b in dw.idx]
         presort(idx)
         if fx is not None:
-            fx.forward(dw.coll, idx)      # gather-pool + exchange in one kernel, then a barrier
-            fx.backward()                 # dx column blocks pushed to the table owners, barrier
-            if dw.coll is not None:
-                if overlap:
-                    stream.wait_stream(side)
-                dw.coll.backward_sgd(idx, dw.outgrad, wl.lr, prepared=overlap)
+            # gather-pool kernels that store into the peers' Concat inputs, output-grad push over NVLink and
+            # the owners' fused backward, pipelined over the plan's groups on three streams (ShardedStep)
+            sstep.run([[idx[i] for i in ids] for ids in dw.group_of], wl.lr, overlap=overlap)
             return
         if dw.coll is not None:
             dw.coll.forward(idx, dw.out)
@@ -329,6 +366,9 @@ def main():
         def step(k):  # noqa: F811
             graphs[k % dw.pool].graph.replay()
 
+    parity = None
+    if fx is not None:
+        parity = sharded_parity_step(torch, pkg, dist, wl, dw, fx, sstep, plan, rank, world, dev)
     for k in range(args.warmup):
         step(k)
     barrier()
@@ -361,6 +401,18 @@ def main():
         ms_total = t.item()
     ms_step = ms_total / args.steps
     total_lookups = wl.lookups
+    if args.trace and sstep is not None:
+        for rep_ in range(2):
+            barrier()
+            sstep.trace = []
+            step(args.warmup + args.steps + rep_)
+            torch.cuda.synchronize()
+            tl = sstep.trace_ms()
+            sstep.trace = None
+        for r in range(world):
+            barrier()
+            if r == rank:
+                print(f"[trace rank {rank}] " + " ".join(f"{l}:{a:.3f}-{b:.3f}" for l, a, b in tl), file=sys.stderr, flush=True)
 
     # ---- e2e: host buffers, copies inside the timed region ----------------------------------
     e2e = None
@@ -375,13 +427,15 @@ def main():
     n_own, T_own = dw.lookups(), len(owned)
     # tables whose gradient fits on chip take the bag-major "small" kernels, the rest the sorted path
     path = pkg.lib().ffemb_backward_path
-    small = [i for i, t in enumerate(owned) if path(wl.rows[t], wl.bags[t], D, B)]
+    small = [i for i, t in enumerate(owned) if path(wl.rows[t], wl.bags[t], dw.widths[i], B)]
     n_s = sum(B * wl.bags[owned[i]] for i in small)
-    U_s = sum(sum(dw.uniq[i]) / len(dw.uniq[i]) for i in small)
+    umean = lambda i: sum(dw.uniq[i]) / len(dw.uniq[i])
+    sorted_ids = [i for i in range(T_own) if i not in small]
     alg = {"forward": fwd_b, "atomic": bwd_b, "sort": 0, "reduce_up": 0,
-           "reduce1": 4 * D * (T_own - len(small)) * B + 8 * D * (U - U_s) + 8 * (n_own - n_s),
+           "reduce1": sum(4 * dw.widths[i] * B + 8 * dw.widths[i] * umean(i) + 8 * B * wl.bags[owned[i]] for i in sorted_ids),
            "exchange": (8 * D * wl.num_tables * fx.local_batch) if fx is not None else 0,
-           "keygen": 8 * (n_own - n_s), "small": 8 * n_s + 4 * D * len(small) * B + 8 * D * U_s}
+           "keygen": 8 * (n_own - n_s),
+           "small": sum(8 * B * wl.bags[owned[i]] + 4 * dw.widths[i] * B + 8 * dw.widths[i] * umean(i) for i in small)}
     # dominant kernel = the longest phase that moves algorithmic bytes (sort / keygen / upper levels are
     # overhead phases: no bytes are credited to them, and at N > 1 the sort's span is stretched by the
     # exchange it runs under)
@@ -450,8 +504,11 @@ def main():
                    "bags": wl.bags, "rows_total": int(sum(wl.rows)), "lookups_per_step": total_lookups,
                    "aggr": wl.aggr, "index_dist": wl.dist, "lr": wl.lr,
                    "parallelism": ("single" if world == 1 else
-                                   f"table-wise x{world} ({args.placement} placement), exchange={args.exchange}"),
+                                   f"table-wise x{world} ({args.placement} placement"
+                                   + (f", heavy tables split by columns, {fx.K} pipeline groups per rank" if fx is not None else "")
+                                   + f"), exchange={args.exchange}"),
                    "table_owner": own if world > 1 else None,
+                   "shard_plan": [[p.table, p.col0, p.width, p.rank, p.group] for p in plan] if world > 1 else None,
                    "backward": args.backward, "sort_overlapped_on_side_stream": bool(overlap),
                    "cuda_graph": bool(use_graph),
                    "cache": f"inputs larger than L2: {args.pool} index batches cycled, "
@@ -461,6 +518,9 @@ def main():
         "clocks": clocks,
         "roofline": roof,
     }
+    if parity is not None:
+        line["parity_ok"] = bool(parity["ok"])
+        line["parity"] = parity
     if e2e is not None:
         line["e2e"] = e2e
     if world == 1 and not args.no_cpu:
@@ -606,6 +666,86 @@ def reference_gpu_leg(torch, wl, dw, args):
         return {"value": None, "unit": UNIT, "what": f"failed: {e!r}"}
 
 
+def sharded_parity_step(torch, pkg, dist, wl, dw, fx, sstep, plan, rank, world, dev):
+    """One UN-TIMED step before warm-up whose results are checked (the flag travels in the bench line, so
+    the driver's scaling runs carry their own parity evidence):
+      * interaction input: every column block of x on every rank BIT-EXACT against the pooled rows the
+        part's owner computes with the plain (non-exchange) forward kernel — broadcast by the owner;
+      * routed output-grads of one sampled part per rank BIT-EXACT against the ranks' dx blocks
+        (all-gathered);
+      * the sampled part's table after the step against a single-rank recomputation (a one-table call on
+        a copy, the routed reference gradient): rows with at most one lookup bit-identical, every row
+        within 1e-6 * (|W0| + lr * count) (|g| <= 1; the summation tree's tiles depend on which tables
+        are batched together, the addends do not).
+    torch.distributed (NCCL) moves the reference data: plumbing for the check only."""
+    try:
+        B, D, lr = wl.batch, wl.dim, wl.lr
+        lo, hi = fx.lo, fx.hi
+        idx0 = [b[0] for b in dw.idx]
+        # plain forward of this rank's parts
+        ref_out = {}
+        for ids, coll in zip(dw.group_of, dw.colls):
+            if coll is not None:
+                outs = coll.forward([idx0[i] for i in ids])
+                for i, o in zip(ids, outs):
+                    ref_out[(dw.parts[i].table, dw.parts[i].col0)] = o
+        # sampled part: most lookups among those whose copies fit comfortably
+        free = torch.cuda.mem_get_info(dev)[0]
+        cands = [i for i in range(len(dw.parts)) if 2.5 * dw.W[i].numel() * 4 < free]
+        samp = max(cands, key=lambda i: (wl.bags[dw.parts[i].table] * min(wl.rows[dw.parts[i].table], 10**7), -i)) if cands else None
+        W0 = dw.W[samp].clone() if samp is not None else None
+        sstep.run([[idx0[i] for i in ids] for ids in dw.group_of], lr, overlap=True)
+        torch.cuda.synchronize()
+        dist.barrier()
+        ok = torch.ones(3, dtype=torch.int32, device=dev)
+        x = fx.x[:hi - lo]
+        for p in sorted(plan, key=lambda p: (p.table, p.col0)):
+            buf = ref_out[(p.table, p.col0)] if p.rank == rank else torch.empty((B, p.width), device=dev)
+            dist.broadcast(buf, src=p.rank)
+            c0 = p.table * D + p.col0
+            if not torch.equal(x[:, c0:c0 + p.width], buf[lo:hi]):
+                ok[0] = 0
+        # routed output-grads + table update of each rank's sampled part
+        for r in range(world):
+            meta = torch.tensor([dw.parts[samp].table, dw.parts[samp].col0, dw.parts[samp].width] if (r == rank and samp is not None)
+                                else [-1, 0, 0], dtype=torch.int64, device=dev)
+            dist.broadcast(meta, src=r)
+            t, c0, w = [int(v) for v in meta.tolist()]
+            if t < 0:
+                continue
+            blk = torch.zeros((fx.ext, w), device=dev)
+            blk[:hi - lo].copy_(fx.dx[:, t * D + c0:t * D + c0 + w])
+            full = torch.empty((world * fx.ext, w), device=dev)
+            dist.all_gather_into_tensor(full, blk)
+            if r != rank:
+                continue
+            og = full[:B].contiguous()
+            k = dw.parts[samp].group
+            j = dw.group_of[k].index(samp)
+            if not torch.equal(fx.outgrads_by_group[k][j], og):
+                ok[1] = 0
+            L = wl.bags[t]
+            pkg.EmbeddingCollection([W0], [L], wl.aggr).backward_sgd([idx0[samp]], [og], lr)
+            torch.cuda.synchronize()
+            cnt = torch.bincount(idx0[samp].reshape(-1), minlength=W0.shape[0])
+            single = cnt <= 1
+            if not torch.equal(dw.W[samp][single], W0[single]):
+                ok[2] = 0
+            # W0 now holds the recomputed table; the bound uses its magnitude (the update is tiny against it)
+            bound = 1e-6 * (W0.abs() + lr * cnt[:, None].float())
+            if not bool(((dw.W[samp] - W0).abs() <= bound).all()):
+                ok[2] = 0
+            del W0, full, og
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        o = [int(v) for v in ok.tolist()]
+        return {"ok": all(o), "interaction_input_bit_exact": bool(o[0]), "routed_outgrads_bit_exact": bool(o[1]),
+                "sampled_tables_match_single_rank_recompute": bool(o[2]),
+                "what": "one un-timed step before warm-up: x vs the owners' plain forward (all parts, all ranks), "
+                        "routed output-grads and updated table of one sampled part per rank vs a single-rank recomputation"}
+    except Exception as e:  # the check must never take the bench line with it
+        return {"ok": False, "what": f"parity step failed: {e!r}"}
+
+
 def load_traffic(phase):
     """dram bytes per launch of the dominant kernel from the committed ncu summary, or None."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
@@ -621,8 +761,8 @@ def run_e2e(torch, pkg, args, wl, dw, ex, fx, dist, dev, barrier, total_lookups)
     interaction input x; its dx is the uploaded gradient); a step ends when every copy has landed."""
     if ex is not None:
         return None  # the NCCL comparison form has no host-buffer API
-    have = dw.coll is not None
-    hs = pkg.HostStep(dw.coll, wl.batch, exchange=fx)
+    have = len(dw.owned) > 0
+    hs = pkg.HostStep(dw.colls if fx is not None else dw.coll, wl.batch, exchange=fx)
     if fx is None:
         # two pinned host buffer sets laid out like HostStep's device slabs (one copy per kind and step);
         # consecutive steps are in flight together (HostStep.submit / wait)

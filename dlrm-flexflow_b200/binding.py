@@ -43,6 +43,10 @@ class ffemb_exchange_t(C.Structure):
                 ("reserved", C.c_int32), ("batch_per_peer", C.c_int64), ("row_stride", C.c_int64)]
 
 
+class ffemb_sync_t(C.Structure):
+    _fields_ = [("peer_pad", C.c_void_p * FFEMB_MAX_PEERS), ("num_peers", C.c_int32), ("rank", C.c_int32)]
+
+
 def library_path():
     return os.path.join(HERE, "libffemb.so")
 
@@ -92,6 +96,10 @@ def lib():
     L.ffemb_forward_batched.argtypes = [tp, i32, i64, i64, i32, vp]
     L.ffemb_forward_exchange.argtypes = [tp, i32, i64, i64, i32, C.POINTER(ffemb_exchange_t), vp]
     L.ffemb_exchange_backward.argtypes = [tp, i32, i64, vp, i64, i64, i64, vp]
+    L.ffemb_exchange_backward_parts.argtypes = [tp, i32, vp, i64, i64, i64, vp]
+    L.ffemb_sync_pad_bytes.restype = sz
+    L.ffemb_sync_signal.argtypes = [C.POINTER(ffemb_sync_t), i32, vp]
+    L.ffemb_sync_wait.argtypes = [C.POINTER(ffemb_sync_t), i32, vp]
     L.ffemb_forward_rowwise.argtypes = [vp, vp, C.POINTER(vp), i32, i64, i64, i64, i64, i32, vp]
     L.ffemb_rowwise_localize.argtypes = [vp, vp, i64, i64, i32, vp, i64, vp]
     L.ffemb_backward_dense_atomic.argtypes = [vp, vp, vp, i64, i64, i64, i32, vp]
@@ -124,7 +132,8 @@ def lib():
     return L
 
 
-PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small", "exchange", "input", "dense"]
+PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small", "exchange", "input", "dense",
+          "sync"]
 
 
 def profile_enable(on=True):

@@ -58,7 +58,7 @@ __device__ __forceinline__ float4 f4_div(float4 a, float d) {
   return make_float4(a.x / d, a.y / d, a.z / d, a.w / d);
 }
 __device__ __forceinline__ float4 f4_div_rn(float4 a, float d, float r) {
-  return make_float4(div_exact(a.x, d, r), div_exact(a.y, d, r), div_exact(a.z, d, r), div_exact(a.w, d, r));
+  return f4_div_exact(a, d, r);
 }
 __device__ __forceinline__ float4 ld_f4(const float *p) { return *reinterpret_cast<const float4 *>(p); }
 __device__ __forceinline__ void st_f4(float *p, float4 v) { *reinterpret_cast<float4 *>(p) = v; }

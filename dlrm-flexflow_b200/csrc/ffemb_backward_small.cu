@@ -59,7 +59,7 @@ __device__ __forceinline__ int find_by_cta(const TableBatch &tb, uint32_t cta) {
 }
 
 __device__ __forceinline__ float4 f4_scale_div(float4 a, float d, float r) {
-  return make_float4(div_exact(a.x, d, r), div_exact(a.y, d, r), div_exact(a.z, d, r), div_exact(a.w, d, r));
+  return f4_div_exact(a, d, r);
 }
 
 // ---- chunk staging shared by both kernels ---------------------------------------------------------
@@ -272,7 +272,8 @@ bwd_small_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, float 
     const int rank = __popc(m & ((1u << lane) - 1u));
     if (rank == 0 && row >= 0) wcnt[warp * NBIN + bin] = __popc(m);
     if (AVG)  // gradient = output-grad / in_dim per element, once per staged row (embedding.cu:210)
-      for (int i = threadIdx.x; i < nb * D; i += kSmallThreads) gb[i] = div_exact(gb[i], Lf, Linv);
+      for (int i = threadIdx.x; i < nb * (D >> 2); i += kSmallThreads)
+        reinterpret_cast<float4 *>(gb)[i] = f4_div_exact(reinterpret_cast<const float4 *>(gb)[i], Lf, Linv);
     __syncthreads();  // (b)
     // 2. per bin: exclusive prefix of the per-batch counts (lane = batch)
     for (int o = warp; o < NBIN; o += NW) {

@@ -82,6 +82,9 @@ static inline bool aggr_valid(int aggr) {
 int launch_forward(const TableBatch &tb, int64_t D, int64_t B, int aggr, const OutMap &om, cudaStream_t s);
 int launch_exchange_backward(const TableBatch &tb, int64_t D, const float *dx, int64_t n, int64_t first,
                              int64_t stride, cudaStream_t s);
+// push of parts of mixed width with bulk copies (ffemb_exchange.cu); tb.t[p].lookup_base = column offset
+int launch_push_bulk(const TableBatch &tb, const int32_t *widths, const float *dx, int64_t n, int64_t first,
+                     int64_t stride, cudaStream_t s);
 int launch_backward_atomic(const TableBatch &tb, int64_t D, int64_t B, int aggr, cudaStream_t s);
 enum ApplyMode { APPLY_SGD = 0, APPLY_GRAD = 1, APPLY_SGDX = 2 };
 // APPLY_SGDX: the reference's full sgd_update (/root/reference/src/runtime/optimizer_kernel.cu:23-41:
@@ -288,6 +291,23 @@ __device__ __forceinline__ float div_exact(float a, float d, float r) {
   float q = div_rn(a, d, r);
   const float m = fabsf(a);
   if (!(m >= 7.9e-31f && m <= 3.0e38f)) q = a / d;
+  return q;
+}
+// The 16-byte fragment form for the backward's gradient scaling (g / in_dim per element,
+// /root/reference/src/ops/embedding.cu:210): four Markstein quotients, one combined range test, and
+// the IEEE divisions behind a NON-inlined call — inlined per element they bloat the serial walk of the
+// segmented sum (measured on cfg5: level 1 12.5 -> 19.2 ms).  A zero addend counts as safe: its
+// quotient is a zero whose sign cannot be observed in a sum that starts from +0.
+static __device__ __noinline__ float4 f4_div_ieee(float4 a, float d) {
+  return make_float4(a.x / d, a.y / d, a.z / d, a.w / d);
+}
+__device__ __forceinline__ bool div_rn_safe(float a) {
+  const float m = fabsf(a);
+  return (m >= 7.9e-31f && m <= 3.0e38f) || m == 0.0f;
+}
+__device__ __forceinline__ float4 f4_div_exact(float4 a, float d, float r) {
+  float4 q = make_float4(div_rn(a.x, d, r), div_rn(a.y, d, r), div_rn(a.z, d, r), div_rn(a.w, d, r));
+  if (!(div_rn_safe(a.x) && div_rn_safe(a.y) && div_rn_safe(a.z) && div_rn_safe(a.w))) q = f4_div_ieee(a, d);
   return q;
 }
 __device__ __forceinline__ int64_t shfl_i64(int64_t v, int src) {

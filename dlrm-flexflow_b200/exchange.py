@@ -89,88 +89,257 @@ class TableWiseExchange:
 
 
 class FusedTableWiseExchange:
-    """The exchange fused into the kernels, over NVLink peer memory (no NCCL on the data path).
+    """The exchange fused into the kernels, over NVLink peer memory (no NCCL on the data path), cut into
+    pipeline groups so that it overlaps the compute around it.
 
-    forward : ffemb_forward_exchange — the gather-pool kernel of the table owner stores every pooled
-              row straight into the interaction input x_h [B_h][T*D] of the rank h that owns the
-              sample (the Concat layout, /root/reference/src/ops/concat.cu:211-251), tile by tile
-              while it computes; one cross-rank barrier on the stream orders the consumers.
-    backward: ffemb_exchange_backward — every rank pushes column block t of its dx_h into rows
-              [lo_h, hi_h) of the owner's output-grad buffer for table t; barrier; then the owner's
-              fused backward + SGD runs locally.
-    Buffers are torch symmetric memory (peer-mapped allocations + signal pads: plumbing only).
-    Same placement / batch split as TableWiseExchange (the collective form, kept as the comparison).
+    Units are PARTS (sharding.Part): a whole table on its owner, or a column range of a heavy table.
+    Every rank deals its parts into K groups (sharding.plan_shards); group k of the step is
+
+      forward_group(k): ffemb_forward_exchange — the gather-pool kernel of the part owner stores every
+              pooled row straight into the interaction input x_h [B_h][T*D] of the rank h that owns the
+              sample (the Concat layout, /root/reference/src/ops/concat.cu:211-251), tile by tile while
+              it computes; then ffemb_sync_signal(X_k).
+      push_group(k)   : ffemb_sync_wait(X_k) — group k's pooled rows of EVERY rank have landed here — then
+              ffemb_exchange_backward_parts pushes column block (t, cols) of this rank's dx into rows
+              [lo_h, hi_h) of the owner's output-grad buffer for every part of group k (bulk copies over
+              NVLink), then ffemb_sync_signal(G_k).  Runs on its own stream: under forward_group(k + 1)
+              and under the backward of group k - 1.
+      wait_grads(k)   : ffemb_sync_wait(G_k) — every rank's block of group k's output-grads has landed;
+              the owner's fused backward + SGD of group k follows on the same stream.
+
+    The flags are epoch counters in a peer-mapped pad (include/ffemb.h, ffemb_sync_*): no host
+    synchronisation, no collective call, capturable in a CUDA graph.  x is double-buffered by step parity:
+    a rank may run ahead into the next step's forward while a peer still reads the previous x (the
+    write-after-read hazard of a single buffer); a consumer of x(step) only has to be ordered before the
+    same rank's forward of step + 1.  Buffers are torch symmetric memory (peer-mapped allocations:
+    plumbing only).  K = 1 with whole tables is the un-pipelined form of round 1.
     """
 
-    def __init__(self, num_tables, owner, batch, dim, rank, world, device, group=None):
+    X_SLOT, G_SLOT = 0, 8   # flag slots: X_k = k, G_k = 8 + k  (FFEMB_SYNC_SLOTS = 16)
+
+    def __init__(self, num_tables, owner, batch, dim, rank, world, device, group=None, parts=None, groups=None):
         import torch.distributed._symmetric_memory as symm
-        self.T, self.owner, self.B, self.D = int(num_tables), list(owner), int(batch), int(dim)
+        from .binding import ffemb_sync_t, lib
+        from .sharding import Part, num_groups
+        self.T, self.B, self.D = int(num_tables), int(batch), int(dim)
         self.rank, self.world, self.device = rank, world, device
         self.group = group if group is not None else dist.group.WORLD
-        self.owned_by = [[t for t in range(self.T) if self.owner[t] == g] for g in range(world)]
-        self.owned = self.owned_by[rank]
-        self.slot = {t: i for g in range(world) for i, t in enumerate(self.owned_by[g])}
+        if parts is None:
+            parts = [Part(t, 0, self.D, int(owner[t]), 0) for t in range(self.T)]
+        self.parts = sorted(parts, key=lambda p: (p.table, p.col0))
+        self.K = int(groups) if groups is not None else num_groups(self.parts)
+        if not 1 <= self.K <= 8:
+            raise ValueError("1..8 pipeline groups")
+        self.owner = list(owner) if owner is not None else None
+        self.mine = [[p for p in self.parts if p.rank == rank and p.group == k] for k in range(self.K)]
+        self.owned_parts = [p for k in range(self.K) for p in self.mine[k]]
+        self.owned = [p.table for p in self.owned_parts]
         self.ext = (self.B + world - 1) // world
         self.lo, self.hi = batch_block(self.B, world, rank)
         self.local_batch = self.hi - self.lo
         self.stride = self.T * self.D
-        max_owned = max(1, max(len(o) for o in self.owned_by))
+        # output-grad buffers of a rank: its parts back to back ([B][w] each), group by group
+        self.g_off = {}
+        sizes = [0] * world
+        for g in range(world):
+            for k in range(self.K):
+                for p in self.parts:
+                    if p.rank == g and p.group == k:
+                        self.g_off[(p.table, p.col0)] = sizes[g]
+                        sizes[g] += self.B * p.width
         f32 = dict(dtype=torch.float32, device=device)
-        self.x = symm.empty((self.ext, self.stride), **f32)            # interaction input (embedding part)
-        self.gbuf = symm.empty((max_owned, self.B, self.D), **f32)     # output-grads of the owned tables
-        self.hx = symm.rendezvous(self.x, self.group)
+        self.xbuf = symm.empty((2, self.ext, self.stride), **f32)        # interaction input, by step parity
+        self.gbuf = symm.empty((max(4, max(sizes)),), **f32)              # output-grads of the owned parts
+        self.pad = symm.empty((lib().ffemb_sync_pad_bytes() // 8,), dtype=torch.int64, device=device)
+        self.hx = symm.rendezvous(self.xbuf, self.group)
         self.hg = symm.rendezvous(self.gbuf, self.group)
-        self.x.zero_()
+        self.hp = symm.rendezvous(self.pad, self.group)
+        self.xbuf.zero_()
         self.gbuf.zero_()
-        self.dx = torch.zeros((self.local_batch, self.stride), **f32)  # gradient of x, produced locally
-        self.outgrads = [self.gbuf[i] for i in range(len(self.owned))]
-        self._ex = None
-        self._push = None
+        self.pad.zero_()
+        self.dx = torch.zeros((self.local_batch, self.stride), **f32)    # gradient of x, produced locally
+        self.outgrads_by_group = [
+            [self.gbuf[self.g_off[(p.table, p.col0)]:self.g_off[(p.table, p.col0)] + self.B * p.width].view(self.B, p.width)
+             for p in self.mine[k]] for k in range(self.K)]
+        self.outgrads = [g for k in range(self.K) for g in self.outgrads_by_group[k]]
+        self.parity = 1          # begin_step() flips it: the first step writes x[0]
+        self._ex = [None, None]
+        self._push = [None] * self.K
+        sy = ffemb_sync_t()
+        for h in range(world):
+            sy.peer_pad[h] = int(self.hp.buffer_ptrs[h])
+        sy.num_peers, sy.rank = world, rank
+        self._sync = sy
         torch.cuda.synchronize(device)
         dist.barrier(group=self.group)
 
+    # ---- the interaction input of the current step ----------------------------------------------
+    @property
+    def x(self):
+        return self.xbuf[self.parity]
+
+    def begin_step(self):
+        self.parity ^= 1
+
     def _exchange_desc(self):
-        if self._ex is None:
+        if self._ex[self.parity] is None:
             from .binding import ffemb_exchange_t
             ex = ffemb_exchange_t()
+            off = self.parity * self.ext * self.stride * 4
             for h in range(self.world):
-                ex.peer_x[h] = int(self.hx.buffer_ptrs[h])
+                ex.peer_x[h] = int(self.hx.buffer_ptrs[h]) + off
             ex.num_peers, ex.batch_per_peer, ex.row_stride = self.world, self.ext, self.stride
-            self._ex = ex
-        return self._ex
+            self._ex[self.parity] = ex
+        return self._ex[self.parity]
 
-    def forward(self, coll, indices, stream=None):
-        """coll: EmbeddingCollection of the owned tables (in self.owned order). Fills x on all ranks."""
+    def signal(self, slot, stream=None):
+        import ctypes as C
+        from .binding import check, lib
+        from .embedding import _stream_ptr
+        check(lib().ffemb_sync_signal(C.byref(self._sync), slot, _stream_ptr(stream)))
+
+    def wait(self, slot, stream=None):
+        import ctypes as C
+        from .binding import check, lib
+        from .embedding import _stream_ptr
+        check(lib().ffemb_sync_wait(C.byref(self._sync), slot, _stream_ptr(stream)))
+
+    # ---- group-wise pieces of a step ---------------------------------------------------------------
+    def forward_group(self, k, coll, indices, stream=None):
+        """coll: EmbeddingCollection of this rank's parts of group k (in self.mine[k] order; None when
+        the rank has none); fills columns of x on ALL ranks, then signals X_k."""
         import ctypes as C
         from .binding import check, ffemb_table_t, lib
         from .embedding import _stream_ptr
-        n = len(self.owned)
-        if n:
+        mine = self.mine[k]
+        if mine:
+            n, w = len(mine), mine[0].width
             arr = (ffemb_table_t * n)()
-            for i, t in enumerate(self.owned):
+            for i, p in enumerate(mine):
                 arr[i].idx, arr[i].out, arr[i].table = indices[i].data_ptr(), None, coll.weights[i].data_ptr()
-                arr[i].R, arr[i].L, arr[i].reserved = int(coll.weights[i].shape[0]), coll.bags[i], t * self.D
-            check(lib().ffemb_forward_exchange(arr, n, self.D, self.B, coll.aggr,
-                                               C.byref(self._exchange_desc()), _stream_ptr(stream)))
-        self.hx.barrier(channel=0)
+                arr[i].R, arr[i].L, arr[i].reserved = int(coll.weights[i].shape[0]), coll.bags[i], p.table * self.D + p.col0
+            check(lib().ffemb_forward_exchange(arr, n, w, self.B, coll.aggr, C.byref(self._exchange_desc()),
+                                               _stream_ptr(stream)))
+        self.signal(self.X_SLOT + k, stream)
+
+    def wait_x(self, k, stream=None):
+        self.wait(self.X_SLOT + k, stream)
+
+    def push_group(self, k, stream=None):
+        """Column blocks of dx of every part of group k (of all ranks) -> their owners; signals G_k."""
+        from .binding import check, ffemb_table_t, lib
+        from .embedding import _stream_ptr
+        if self._push[k] is None:
+            ps = [p for p in self.parts if p.group == k]
+            arr = (ffemb_table_t * max(1, len(ps)))()
+            for i, p in enumerate(ps):
+                arr[i].out = int(self.hg.buffer_ptrs[p.rank]) + self.g_off[(p.table, p.col0)] * 4
+                arr[i].reserved, arr[i].L = p.table * self.D + p.col0, p.width
+            self._push[k] = (arr, len(ps))
+        arr, n = self._push[k]
+        if self.local_batch and n:
+            check(lib().ffemb_exchange_backward_parts(arr, n, self.dx.data_ptr(), self.local_batch, self.lo,
+                                                      self.stride, _stream_ptr(stream)))
+        self.signal(self.G_SLOT + k, stream)
+
+    def wait_grads(self, k, stream=None):
+        self.wait(self.G_SLOT + k, stream)
+
+    # ---- the un-pipelined calls (K == 1, or every group back to back on one stream) -----------------
+    def forward(self, coll, indices, stream=None):
+        """coll / indices: one EmbeddingCollection (all owned parts, K == 1) or per-group lists.
+        Fills x on all ranks and returns it once every rank's rows have landed."""
+        self.begin_step()
+        colls = coll if isinstance(coll, (list, tuple)) else [coll]
+        idxs = indices if isinstance(coll, (list, tuple)) else [indices]
+        for k in range(self.K):
+            self.forward_group(k, colls[k], idxs[k], stream)
+        for k in range(self.K):
+            self.wait_x(k, stream)
         return self.x
 
     def backward(self, stream=None):
-        """dx on every rank -> self.outgrads ([B][D] per owned table) on the owners."""
-        from .binding import check, ffemb_table_t, lib
-        from .embedding import _stream_ptr
-        if self._push is None:
-            arr = (ffemb_table_t * self.T)()
-            for t in range(self.T):
-                base = int(self.hg.buffer_ptrs[self.owner[t]])
-                arr[t].out = base + self.slot[t] * self.B * self.D * 4
-                arr[t].reserved = t * self.D
-            self._push = arr
-        if self.local_batch:
-            check(lib().ffemb_exchange_backward(self._push, self.T, self.D, self.dx.data_ptr(),
-                                                self.local_batch, self.lo, self.stride, _stream_ptr(stream)))
-        self.hg.barrier(channel=1)
+        """dx on every rank -> self.outgrads ([B][w] per owned part) on the owners."""
+        for k in range(self.K):
+            self.push_group(k, stream)
+        for k in range(self.K):
+            self.wait_grads(k, stream)
         return self.outgrads
+
+
+class ShardedStep:
+    """One training step of this rank's share of the embedding tables, pipelined over the exchange's
+    groups on three streams (the schedule a per-GPU Legion leaf task would enqueue;
+    csrc/flexflow/embedding_ffemb.cu has the C++ form):
+
+        main : forward(0) sig  forward(1) sig ...            wait G_0  backward(0)  wait G_1  backward(1) ...
+        push :          wait X_0  push(0) sig   wait X_1  push(1) sig ...
+        side : keygen + radix sort of group 0, 1, ...   (needs the indices only)
+
+    `dx_ready`: optional event after which this rank's dx holds the step's gradient (with a model in
+    between it is recorded after the dense layers' backward; the host-buffer step records it after the
+    upload).  The data dependence kept per group: the gradient block of a part is pushed only once that
+    part's pooled rows have landed on every rank."""
+
+    def __init__(self, fx, colls, device):
+        self.fx, self.colls, self.dev = fx, colls, device
+        # the push and the index sort are short, latency-critical pieces that must get SM slots while a
+        # long gather-pool / segmented-sum grid is draining: high-priority streams
+        self.s_push = torch.cuda.Stream(device=device, priority=-1)
+        self.s_side = torch.cuda.Stream(device=device, priority=-1)
+        self.ev_sorted = [torch.cuda.Event() for _ in range(fx.K)]
+        self.ev_x = torch.cuda.Event()
+        self.trace = None   # set to [] to collect (label, start event, end event) of every piece of a step
+
+    def _span(self, label, stream, fn):
+        if self.trace is None:
+            return fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        r = fn()
+        b.record(stream)
+        self.trace.append((label, a, b))
+        return r
+
+    def trace_ms(self):
+        """[(label, start ms, end ms)] relative to the first recorded event (call after a synchronize)."""
+        if not self.trace:
+            return []
+        t0 = self.trace[0][1]
+        return [(l, round(t0.elapsed_time(a), 4), round(t0.elapsed_time(b), 4)) for l, a, b in self.trace]
+
+    def run(self, idx_groups, lr, dx_ready=None, overlap=True, stream=None):
+        fx, K = self.fx, self.fx.K
+        main = stream if stream is not None else torch.cuda.current_stream(self.dev)
+        push, side = self.s_push, self.s_side
+        fx.begin_step()
+        self._span("step_start", main, lambda: None)
+        push.wait_stream(main)
+        if overlap:
+            side.wait_stream(main)   # the previous step's reductions are done with the sort buffers
+            for k in range(K):
+                if self.colls[k] is not None:
+                    self._span(f"sort{k}", side, lambda: self.colls[k].backward_prepare(idx_groups[k], stream=side))
+                self.ev_sorted[k].record(side)
+        for k in range(K):
+            self._span(f"fwd{k}", main, lambda: fx.forward_group(k, self.colls[k], idx_groups[k], main))
+        with torch.cuda.stream(push):
+            for k in range(K):
+                self._span(f"waitx{k}", push, lambda: fx.wait_x(k, push))
+                if k == K - 1:
+                    self.ev_x.record(push)   # x is complete on this rank
+                if dx_ready is not None and k == 0:
+                    push.wait_event(dx_ready)
+                self._span(f"push{k}", push, lambda: fx.push_group(k, push))
+        for k in range(K):
+            self._span(f"waitg{k}", main, lambda: fx.wait_grads(k, main))
+            if self.colls[k] is not None:
+                if overlap:
+                    main.wait_event(self.ev_sorted[k])
+                self._span(f"bwd{k}", main, lambda: self.colls[k].backward_sgd(
+                    idx_groups[k], fx.outgrads_by_group[k], lr, stream=main, prepared=overlap))
+        main.wait_stream(push)
+        return fx.x
 
 
 class RowWiseTable:

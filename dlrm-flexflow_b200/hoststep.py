@@ -23,16 +23,27 @@ class HostStep:
     GRAPH_MAX_LOOKUPS = 2_000_000
 
     def __init__(self, coll, batch, exchange=None, depth=2, graph="auto"):
-        """coll: EmbeddingCollection of this GPU's tables (or None on a rank that owns none);
+        """coll: EmbeddingCollection of this GPU's tables (or None on a rank that owns none); with an
+        exchange: the list of per-group collections of this rank's parts (exchange.ShardedStep order,
+        None for an empty group).
         exchange: FusedTableWiseExchange for N > 1 (then the host-side result is the rank's
-        interaction input x and the host-side gradient is its dx; those live in one symmetric
-        buffer each, so steps are not overlapped there: depth 1).
+        interaction input x and the host-side gradient is its dx; dx lives in one buffer, so
+        steps are not overlapped there: depth 1).
         graph: replay the kernels of a step from two CUDA graphs per buffer set (forward + index sort;
         segmented sum + SGD) instead of launching them one by one — "auto" = single-GPU steps of at
         most GRAPH_MAX_LOOKUPS lookups, which are bound by the host's launch rate, not by the GPU or
         PCIe.  The copies stay eager (three per step), so steps still overlap across buffer sets."""
-        self.coll, self.fx, self.B = coll, exchange, int(batch)
-        small = coll is not None and int(batch) * sum(coll.bags) <= self.GRAPH_MAX_LOOKUPS
+        self.fx, self.B = exchange, int(batch)
+        self.colls = None
+        if exchange is not None:
+            from .exchange import ShardedStep
+            self.colls = list(coll) if isinstance(coll, (list, tuple)) else [coll]
+            live = [c for c in self.colls if c is not None]
+            coll = live[0] if live else None
+            self.sharded = ShardedStep(exchange, self.colls, exchange.device)
+            self.group_bags = [list(c.bags) if c is not None else [] for c in self.colls]
+        self.coll = coll
+        small = coll is not None and exchange is None and int(batch) * sum(coll.bags) <= self.GRAPH_MAX_LOOKUPS
         self.use_graph = exchange is None and coll is not None and (graph is True or graph == "on" or
                                                                     (graph == "auto" and small))
         self._graphs, self._last_lr, self.graph_replays = {}, {}, 0
@@ -51,8 +62,9 @@ class HostStep:
         self.slab_idx, self.slab_g, self.slab_out = [], [], []
         f32 = dict(dtype=torch.float32, device=dev)
         for _ in range(self.depth):
-            if coll is not None:
-                slab, views = self._slab([(self.B, l) for l in coll.bags], torch.int64, dev)
+            bags = [l for g in self.group_bags for l in g] if exchange is not None else (coll.bags if coll is not None else [])
+            if bags:
+                slab, views = self._slab([(self.B, l) for l in bags], torch.int64, dev)
             else:
                 slab, views = None, []
             self.slab_idx.append(slab)
@@ -151,22 +163,32 @@ class HostStep:
         gr = self._step_graphs(s, float(lr)) if self.use_graph else None
         main.wait_event(self.ev_idx[s])
         main.wait_event(self.ev_out[s])            # the previous download out of d_out[s] has drained
+        if fx is not None:
+            # sharded step: forward + exchange, push (once this step's dx has landed), backward, pipelined
+            # over the exchange's groups; the download of x starts the moment x is complete on this rank
+            groups, o = [], 0
+            for g in self.group_bags:
+                groups.append(d_idx[o:o + len(g)])
+                o += len(g)
+            x = self.sharded.run(groups, lr, dx_ready=self.ev_g[s], stream=main)
+            with torch.cuda.stream(self.s_out):
+                self.s_out.wait_event(self.sharded.ev_x)
+                h_out.copy_(x, non_blocking=True)
+                self.ev_out[s].record(self.s_out)
+            self.ev_done[s].record(main)
+            self.ticket = k + 1
+            return k
         if gr is not None:
             with torch.cuda.stream(main):
                 gr[0].replay()                     # forward + keygen / radix sort
-        elif fx is None:
-            coll.forward(d_idx, self.d_out[s])
         else:
-            fx.forward(coll, d_idx)
+            coll.forward(d_idx, self.d_out[s])
         self.ev_fwd[s].record(main)
         with torch.cuda.stream(self.s_out):
             self.s_out.wait_event(self.ev_fwd[s])
-            if fx is None:
-                self._copy(h_out, None, self.d_out[s], self.slab_out[s], to_host=True)
-            else:
-                h_out.copy_(fx.x, non_blocking=True)
+            self._copy(h_out, None, self.d_out[s], self.slab_out[s], to_host=True)
             self.ev_out[s].record(self.s_out)
-        if coll is not None and gr is None:
+        if gr is None:
             coll.backward_prepare(d_idx)       # sort: indices only, runs while the grads upload
         main.wait_event(self.ev_g[s])
         if gr is not None:
@@ -176,13 +198,7 @@ class HostStep:
             self.ev_done[s].record(main)
             self.ticket = k + 1
             return k
-        if fx is not None:
-            fx.backward()
-            grads = fx.outgrads
-        else:
-            grads = self.d_g[s]
-        if coll is not None:
-            coll.backward_sgd(d_idx, grads, lr, prepared=True)
+        coll.backward_sgd(d_idx, self.d_g[s], lr, prepared=True)
         self.ev_done[s].record(main)
         self.ticket = k + 1
         return k

@@ -191,3 +191,131 @@ def place_tables(rows, bags, dim, world, kind="balanced", hbm_bytes=150e9):
         g = next((g for g in cands if mem[g] + rows[t] * dim * 4 < hbm_bytes), cands[0])
         own[t], load[g], mem[g] = g, load[g] + cost(t), mem[g] + rows[t] * dim * 4
     return own
+
+
+# ---------------------------------------------------------------------------------------------
+# Shard plan with column splits and pipeline groups (table-wise sharding)
+# ---------------------------------------------------------------------------------------------
+@dataclass
+class Part:
+    """A placement unit: columns [col0, col0 + width) of table `table`, whole on GPU `rank`, processed
+    in pipeline group `group` of that rank.  width == dim: the reference's unit, the whole table
+    (/root/reference/examples/cpp/DLRM/strategies/dlrm_strategy.cc:252-256).  width < dim: a heavy table
+    split by COLUMNS over several ranks — every rank of the split sees the same indices and pools /
+    updates its own columns, so pooled rows and updated tables are bit-identical to the unsplit table
+    and the exchange moves exactly the same bytes (each rank sends its columns of every sample)."""
+    table: int
+    col0: int
+    width: int
+    rank: int
+    group: int = 0
+
+
+def part_cost(rows, bag, dim, width):
+    """Estimated time (ms at batch 65536) of one part on one B200: forward + index sort + segmented sum,
+    in the three regimes measured per table in isolation (scripts/per_table_cost.py,
+    profiles/r2_per_table_cost.md): rows streamed from HBM (table far larger than L2), L2-resident
+    tables through the sorted path, tables whose gradient stays on chip.  A half-width part keeps the
+    whole index sort and the per-lookup walk, so it costs more than half."""
+    f = width / float(dim)
+    half = 0.55 if f < 1.0 else 1.0          # measured: forward / level 1 of a D/2 part vs the full table
+    scale = dim / 128.0
+    table_bytes = rows * dim * 4
+    if table_bytes > (64 << 20):
+        per = 0.0065 * half + 0.0024 + 0.0145 * half
+    elif rows <= 16 or (rows * dim * 4 <= (80 << 10) and bag >= 8):
+        per = 0.0025 * half + 0.0023
+    else:
+        per = (0.0029 + 0.0037) * (0.65 if f < 1.0 else 1.0) + 0.0024
+    return bag * per * max(scale, 0.25) + 0.01 * f * scale
+
+
+def plan_shards(rows, bags, dim, world, kind="balanced", split=True, groups=1, hbm_bytes=150e9):
+    """-> list of Part, one or more per table, in a deterministic order (every rank computes the same).
+
+    kind "modulo"  : the reference generator's placement, table i whole on GPU i % world.
+    kind "balanced": greedy longest-processing-time over part_cost; with split=True a table whose cost
+                     exceeds 3/4 of the mean load per rank is first cut into two column halves (and a
+                     half that still does into quarters), so that no single table sets the step.
+    groups         : pipeline groups per rank (forward(g+1) overlaps the exchange of g, the push of g+1
+                     overlaps the backward of g).  Parts of one group share one width (the kernels take
+                     one row width per launch): a rank holding parts of two widths gets one group per
+                     width; otherwise its parts are dealt into `groups` bins of equal cost."""
+    T = len(rows)
+    parts = [Part(t, 0, dim, t % world) for t in range(T)]
+    if kind != "modulo" and world > 1:
+        cost = lambda p: part_cost(rows[p.table], bags[p.table], dim, p.width)
+        mean = sum(cost(p) for p in parts) / world
+        if split:
+            for _ in range(2):  # halves, then quarters
+                nxt = []
+                for p in parts:
+                    if cost(p) > 0.75 * mean and p.width % 8 == 0 and p.width >= 32:
+                        h = p.width // 2
+                        nxt += [Part(p.table, p.col0, h, 0), Part(p.table, p.col0 + h, h, 0)]
+                    else:
+                        nxt.append(p)
+                parts = nxt
+        load, mem = [0.0] * world, [0.0] * world
+        for p in sorted(parts, key=lambda p: (-cost(p), p.table, p.col0)):
+            b = rows[p.table] * p.width * 4
+            cands = sorted(range(world), key=lambda g: (load[g], mem[g], g))
+            # two parts of one table never share a rank (they would be the unsplit table again)
+            cands = [g for g in cands if not any(q.table == p.table and q.rank == g and q is not p and q.group == -1
+                                                 for q in parts)] or cands
+            g = next((g for g in cands if mem[g] + b < hbm_bytes), cands[0])
+            p.rank, p.group = g, -1   # -1: placed, group not yet assigned
+            load[g] += cost(p)
+            mem[g] += b
+        parts.sort(key=lambda p: (p.table, p.col0))
+    # pipeline groups per rank
+    for g in range(world):
+        mine = [p for p in parts if p.rank == g]
+        widths = sorted({p.width for p in mine}, reverse=True)
+        if groups <= 1 and len(widths) <= 1:
+            for p in mine:
+                p.group = 0
+        elif len(widths) > 1:
+            for p in mine:
+                p.group = widths.index(p.width)
+        else:
+            bins = [0.0] * groups
+            for p in sorted(mine, key=lambda p: (-part_cost(rows[p.table], bags[p.table], dim, p.width), p.table)):
+                k = min(range(groups), key=lambda k: (bins[k], k))
+                p.group = k
+                bins[k] += part_cost(rows[p.table], bags[p.table], dim, p.width)
+    return parts
+
+
+def num_groups(parts):
+    return 1 + max((p.group for p in parts), default=0)
+
+
+def plan_strategy(parts, world):
+    """The plan in the reference's strategy-file vocabulary (write_strategy): a whole table is
+    "embedding<i>" with a [1,1] grid on its GPU; a table split into c column parts is a [c,1] grid —
+    dim[0] is the feature dimension (/root/reference/src/runtime/model.cc:726-736) — whose device ids
+    are the parts' ranks in column order.  (The reference's Embedding refuses such a grid,
+    src/ops/embedding.cu:84-85: the file is then only readable by this library's planner.)"""
+    s = {}
+    by_table = {}
+    for p in parts:
+        by_table.setdefault(p.table, []).append(p)
+    for t, ps in by_table.items():
+        ps = sorted(ps, key=lambda p: p.col0)
+        s[f"embedding{t}"] = ParallelConfig(DEVICE_GPU, [len(ps), 1], [int(p.rank) for p in ps])
+    s["concat"] = ParallelConfig(DEVICE_GPU, [1, world], list(range(world)))
+    return s
+
+
+def parts_from_strategy(strategies, num_tables, dim):
+    """Inverse of plan_strategy (groups are not part of the file: all 0)."""
+    parts = []
+    for t in range(num_tables):
+        c = strategies[f"embedding{t}"]
+        n = c.dims[0]
+        if c.device_type != DEVICE_GPU or len(c.dims) != 2 or c.dims[1] != 1 or dim % n != 0:
+            raise ValueError(f"embedding{t}: expected a [c,1] grid on GPUs with c dividing the row width")
+        w = dim // n
+        parts += [Part(t, i * w, w, int(c.device_ids[i])) for i in range(n)]
+    return parts

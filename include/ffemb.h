@@ -125,6 +125,48 @@ FFEMB_API int ffemb_exchange_backward(const ffemb_table_t *tables, int num_table
                             const float *dx, int64_t n_samples, int64_t first_sample,
                             int64_t row_stride, ffemb_stream_t stream);
 
+/* The same push for PARTS of mixed width in one launch.  A part is a whole table or a column range
+ * of one (a heavy table split by columns over two ranks: same indices on both, each pools / updates
+ * its own columns — bit-identical results, no extra exchange bytes; sharding.plan_shards):
+ *   parts[p].out      = the owner's output-grad buffer of the part, [B][w_p] floats (peer-mapped)
+ *   parts[p].reserved = first column of the part inside a row of dx
+ *   parts[p].L        = w_p, the part's width in floats (a multiple of 4)
+ * idx / table / R are ignored.  Rows travel as tiles of up to 8 KB: cp.async.bulk global -> shared,
+ * then ONE contiguous cp.async.bulk shared -> peer global per tile (large posted NVLink writes issued
+ * by a few dozen resident warps, so the push runs under the compute kernels of the neighbouring table
+ * group); unaligned shapes fall back to 16-byte load/store per lane.                            */
+FFEMB_API int ffemb_exchange_backward_parts(const ffemb_table_t *parts, int num_parts, const float *dx,
+                                  int64_t n_samples, int64_t first_sample, int64_t row_stride,
+                                  ffemb_stream_t stream);
+
+/* ---- cross-rank ordering of the fused exchange ------------------------------
+ * The stores of ffemb_forward_exchange / ffemb_exchange_backward* land in ANOTHER GPU's memory; the
+ * consumer there must be ordered after them, and the producer's next step after the consumer.  In the
+ * reference that ordering is Legion's (region dependences between the embedding tasks and Concat's,
+ * src/ops/concat.cu:88-97); here it is a set of epoch flags in a small pad per rank that every rank
+ * can address — raw device pointers valid on the calling device: cudaDeviceEnablePeerAccess inside one
+ * Legion process (one process drives all GPUs of a node, src/runtime/model.cc:679-706 builds its
+ * ncclComm_t the same way), cudaIpcOpenMemHandle across processes, or symmetric memory.  No NCCL call
+ * and no host synchronisation is involved.
+ *   pad: ffemb_sync_pad_bytes() bytes per rank, 8-byte aligned, ZERO-FILLED once before first use.
+ *   ffemb_sync_signal(sync, slot): everything enqueued on `stream` before this call is visible to every
+ *       peer that later passes ffemb_sync_wait on the same slot (fence.sys + st.release.sys of this
+ *       rank's next epoch for the slot into every peer's pad, its own included).
+ *   ffemb_sync_wait(sync, slot)  : work enqueued on `stream` after this call runs only once EVERY rank
+ *       has signalled the slot as many times as this rank has now waited on it (a one-warp kernel that
+ *       spins with ld.acquire.sys; it traps after 20 s rather than hanging the device).
+ * Epochs are kept in the pad, so the calls carry no step number and can be captured in a CUDA graph.
+ * Every rank must call signal and wait on a slot equally often.                                  */
+#define FFEMB_SYNC_SLOTS 16
+typedef struct ffemb_sync {
+  uint64_t *peer_pad[FFEMB_MAX_PEERS]; /* pad of rank h as mapped on THIS device */
+  int32_t num_peers;
+  int32_t rank;
+} ffemb_sync_t;
+FFEMB_API size_t ffemb_sync_pad_bytes(void);
+FFEMB_API int ffemb_sync_signal(const ffemb_sync_t *sync, int slot, ffemb_stream_t stream);
+FFEMB_API int ffemb_sync_wait(const ffemb_sync_t *sync, int slot, ffemb_stream_t stream);
+
 /* ---- row-wise sharded tables (a table too large for one GPU) --------------------------------
  * Not in the reference (Embedding asserts sample-dim-only partitioning, src/ops/embedding.cu:84-85).
  * Shard map = Legion's blocked restriction on the row dimension (src/runtime/model.cc:880-892):
@@ -300,7 +342,8 @@ FFEMB_API int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int6
 #define FFEMB_PHASE_EXCHANGE 7  /* output-grad push over peer memory */
 #define FFEMB_PHASE_INPUT 8     /* sparse-input delivery (ffemb_load_sparse_inputs) */
 #define FFEMB_PHASE_DENSE 9     /* general SGD: the pass over the rows a step did not touch */
-#define FFEMB_NUM_PHASES 10
+#define FFEMB_PHASE_SYNC 10     /* cross-rank flag kernels (ffemb_sync_signal / ffemb_sync_wait) */
+#define FFEMB_NUM_PHASES 11
 FFEMB_API int ffemb_profile_enable(int on);
 FFEMB_API int ffemb_profile_collect(float *ms_per_phase, int64_t *launches_per_phase);
 FFEMB_API int64_t ffemb_launch_count(void);

@@ -75,6 +75,71 @@ def main():
                     assert torch.allclose(myW[i], ref_W[t], rtol=0, atol=1e-6 * 0.01 * dup ** 0.5 * 8 + 1e-7), \
                         (kind, aggr, t, "updated table far from the all-tables call")
             dist.barrier()
+        # ---- the pipelined, column-split form (ShardedStep): heavy tables cut into column parts, parts
+        # dealt into 2 groups per rank, push under the neighbouring group's compute, flags instead of
+        # barriers.  Three steps in a row with fresh gradients: the next step's forward may overtake a
+        # peer still reading the previous x (x is double-buffered by step parity). ----
+        S = pkg.sharding
+        for split_tables in ((), (1, 7)):
+            parts = []
+            for t in range(T):
+                if t in split_tables:
+                    parts += [S.Part(t, 0, D // 2, t % world), S.Part(t, D // 2, D // 2, (t + 1) % world)]
+                else:
+                    parts.append(S.Part(t, 0, D, t % world))
+            for g in range(world):   # groups: by width where a rank holds two widths, else alternate
+                mine_g = [p for p in parts if p.rank == g]
+                widths = sorted({p.width for p in mine_g}, reverse=True)
+                for i, p in enumerate(mine_g):
+                    p.group = widths.index(p.width) if len(widths) > 1 else i % 2
+            fx = pkg.exchange.FusedTableWiseExchange(T, None, B, D, rank, world, dev, parts=parts)
+            K = fx.K
+            mine = fx.mine
+            Wp = [[Ws[p.table][:, p.col0:p.col0 + p.width].clone() for p in mine[k]] for k in range(K)]  # (a full-width slice is a view)
+            colls = [pkg.EmbeddingCollection(Wp[k], [bags[p.table] for p in mine[k]], aggr) if mine[k] else None
+                     for k in range(K)]
+            sstep = pkg.exchange.ShardedStep(fx, colls, dev)
+            truth = [w.clone() for w in Ws]
+            tcoll = pkg.EmbeddingCollection(truth, bags, aggr)
+            for it in range(3):
+                # fresh indices and gradients every step; the tables move only in the last one (lr = 0 leaves
+                # them bit-identical), so that every step's x can be held against the unsharded tables bit for bit
+                lr = 0.01 if it == 2 else 0.0
+                idx_it = [(i + it) % r for i, r in zip(idx, rows)]
+                idxg = [[idx_it[p.table] for p in mine[k]] for k in range(K)]
+                dxs = torch.rand((B, T * D), device=dev, generator=torch.Generator(device=dev).manual_seed(100 + it)) - 0.5
+                fx.dx.copy_(dxs[lo:hi])
+                want_x = torch.cat(tcoll.forward(idx_it), dim=1)
+                x = sstep.run(idxg, lr)[:hi - lo]
+                # no synchronisation with the peers here on purpose: compare, then go straight into the next step
+                assert torch.equal(x, want_x[lo:hi]), ("pipelined", aggr, split_tables, it, "interaction input differs")
+                for k in range(K):
+                    for j, p in enumerate(mine[k]):
+                        c0 = p.table * D + p.col0
+                        assert torch.equal(fx.outgrads_by_group[k][j], dxs[:, c0:c0 + p.width]), \
+                            ("pipelined", aggr, split_tables, it, p, "routed output-grad differs")
+                tcoll.backward_sgd(idx_it, [dxs[:, t * D:(t + 1) * D].contiguous() for t in range(T)], lr)
+                torch.cuda.synchronize()
+                for k in range(K):
+                    for j, p in enumerate(mine[k]):
+                        want = truth[p.table][:, p.col0:p.col0 + p.width]
+                        cnt = torch.bincount(idx_it[p.table].reshape(-1), minlength=rows[p.table])
+                        assert torch.equal(Wp[k][j][cnt <= 1], want[cnt <= 1]), ("pipelined", it, p, "single-lookup rows differ")
+                        dup = B * bags[p.table] / rows[p.table] + 1
+                        assert torch.allclose(Wp[k][j], want, rtol=0, atol=1e-6 * 0.01 * dup ** 0.5 * 8 + 1e-7), \
+                            ("pipelined", aggr, split_tables, it, p, "updated part far from the unsharded table")
+            dist.barrier()
+        # ---- forward-only loop across ranks (no backward between the steps): x of step k must survive
+        # until this rank has compared it although the peers are already storing step k + 1 ----
+        fx = pkg.exchange.FusedTableWiseExchange(T, owner, B, D, rank, world, dev)
+        myW = [Ws[t].clone() for t in owned]
+        coll = pkg.EmbeddingCollection(myW, [bags[t] for t in owned], aggr) if owned else None
+        shifted = [[(i + s) % r for i, r in zip(idx, rows)] for s in range(4)]
+        wants = [torch.cat(pkg.EmbeddingCollection(Ws, bags, aggr).forward(sh), dim=1)[lo:hi].clone() for sh in shifted]
+        for s4 in range(4):
+            x = fx.forward(coll, [shifted[s4][t] for t in owned])[:hi - lo]
+            assert torch.equal(x, wants[s4]), ("forward-only", aggr, s4)
+        dist.barrier()
     # ---- row-wise sharded table: remote gathers in the forward, all-gather + local backward ----
     for (R, L, aggr) in ((100003, 1, 21), (5001, 5, 21), (70001, 3, 22)):
         g = torch.Generator(device=dev).manual_seed(11 + L)

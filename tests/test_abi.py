@@ -36,6 +36,28 @@ def test_argument_validation_returns_codes_without_a_device(ffemb):
     assert L.ffemb_forward(None, None, None, 1, 16, 0, ffemb.AGGR_MODE_SUM, None) == 0
 
 
+def test_exchange_entry_points_validate_before_touching_a_device(ffemb):
+    import ctypes as C
+    L = ffemb.lib()
+    from importlib import import_module
+    b = import_module("dlrm-flexflow_b200.binding")
+    assert L.ffemb_sync_pad_bytes() >= 16 * 8 * 8 and L.ffemb_sync_pad_bytes() % 8 == 0
+    sy = b.ffemb_sync_t()
+    sy.num_peers, sy.rank = 2, 0
+    assert L.ffemb_sync_signal(C.byref(sy), 0, None) == 1 and b"peer_pad" in L.ffemb_last_error()  # NULL pads
+    sy.peer_pad[0], sy.peer_pad[1] = 64, 128
+    assert L.ffemb_sync_wait(C.byref(sy), 16, None) == 1      # slot out of range
+    sy.rank = 2
+    assert L.ffemb_sync_signal(C.byref(sy), 0, None) == 1     # rank outside the peer set
+    assert L.ffemb_sync_signal(None, 0, None) == 1
+    parts = (b.ffemb_table_t * 1)()
+    parts[0].out, parts[0].L, parts[0].reserved = 256, 64, 100
+    assert L.ffemb_exchange_backward_parts(parts, 1, 256, 8, 0, 128, None) == 1   # columns 100..163 of 128
+    parts[0].L = 0
+    assert L.ffemb_exchange_backward_parts(parts, 1, 256, 8, 0, 128, None) == 1   # zero width
+    assert L.ffemb_exchange_backward_parts(parts, 0, None, 0, 0, 128, None) == 0  # nothing to do
+
+
 def test_workspace_query(ffemb):
     L = ffemb.lib()
     assert L.ffemb_backward_workspace(0, 10, 16) == 0

@@ -137,3 +137,63 @@ def test_strategy_errors(ffemb, tmp_path):
         S.owners_from_strategy(S.read_strategy(str(p)), 1)
     with pytest.raises(KeyError):
         S.owners_from_strategy({}, 1)
+
+
+# ---- shard plans with column splits and pipeline groups (sharding.plan_shards) -------------------
+def _check_plan(S, parts, rows, dim, world):
+    # every column of every table exactly once; parts of a split table on distinct ranks
+    for t in range(len(rows)):
+        ps = sorted([p for p in parts if p.table == t], key=lambda p: p.col0)
+        assert ps and ps[0].col0 == 0 and sum(p.width for p in ps) == dim
+        for a, b in zip(ps, ps[1:]):
+            assert a.col0 + a.width == b.col0
+        assert len({p.rank for p in ps}) == len(ps)
+        assert all(p.width % 4 == 0 and 0 <= p.rank < world for p in ps)
+    # the kernels take one row width per launch: a (rank, group) never mixes widths
+    for g in range(world):
+        for k in range(S.num_groups(parts)):
+            assert len({p.width for p in parts if p.rank == g and p.group == k}) <= 1
+
+
+def test_plan_modulo_is_the_reference_placement(ffemb):
+    S, wl = ffemb.sharding, ffemb.synth.config(3)
+    for world in (1, 2, 8):
+        parts = S.plan_shards(wl.rows, wl.bags, wl.dim, world, "modulo", split=True, groups=1)
+        assert [(p.table, p.col0, p.width, p.rank, p.group) for p in parts] == \
+            [(t, 0, wl.dim, t % world, 0) for t in range(wl.num_tables)]
+
+
+def test_plan_balanced_splits_the_heaviest_table_and_levels_the_ranks(ffemb):
+    S, wl = ffemb.sharding, ffemb.synth.config(3)
+    cost = lambda ps: sum(S.part_cost(wl.rows[p.table], wl.bags[p.table], wl.dim, p.width) for p in ps)
+    for world in (2, 4, 8):
+        for groups in (1, 2):
+            parts = S.plan_shards(wl.rows, wl.bags, wl.dim, world, "balanced", split=True, groups=groups)
+            again = S.plan_shards(wl.rows, wl.bags, wl.dim, world, "balanced", split=True, groups=groups)
+            assert parts == again  # deterministic: every rank derives the same plan
+            _check_plan(S, parts, wl.rows, wl.dim, world)
+            loads = [cost([p for p in parts if p.rank == g]) for g in range(world)]
+            assert max(loads) <= 1.15 * (sum(loads) / world)
+            modulo = S.plan_shards(wl.rows, wl.bags, wl.dim, world, "modulo")
+            assert max(loads) <= max(cost([p for p in modulo if p.rank == g]) for g in range(world))
+    parts8 = S.plan_shards(wl.rows, wl.bags, wl.dim, 8, "balanced", split=True, groups=2)
+    assert sorted((p.col0, p.width) for p in parts8 if p.table == 0) == [(0, 64), (64, 64)]  # 40M rows x bag 20
+    whole = S.plan_shards(wl.rows, wl.bags, wl.dim, 8, "balanced", split=False, groups=2)
+    assert all(p.width == wl.dim for p in whole)
+    for world in (2, 4):  # per-rank share above the heaviest table: nothing to split
+        assert all(p.width == wl.dim for p in S.plan_shards(wl.rows, wl.bags, wl.dim, world, "balanced", True, 2))
+
+
+def test_plan_round_trips_through_the_strategy_file_format(ffemb, tmp_path):
+    S, wl = ffemb.sharding, ffemb.synth.config(3)
+    parts = S.plan_shards(wl.rows, wl.bags, wl.dim, 8, "balanced", split=True, groups=1)
+    path = str(tmp_path / "plan.strategy")
+    S.write_strategy(path, S.plan_strategy(parts, 8))
+    back = S.parts_from_strategy(S.read_strategy(path), wl.num_tables, wl.dim)
+    key = lambda p: (p.table, p.col0, p.width, p.rank)
+    assert sorted(map(key, back)) == sorted(map(key, parts))
+    # a plan without splits is a plain table-wise strategy of the reference's kind: [1,1] grids
+    whole = S.plan_shards(wl.rows, wl.bags, wl.dim, 8, "balanced", split=False)
+    st = S.plan_strategy(whole, 8)
+    assert S.owners_from_strategy(st, wl.num_tables) == [next(p.rank for p in whole if p.table == t)
+                                                         for t in range(wl.num_tables)]
