@@ -70,6 +70,9 @@ def parse():
     ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
                     help="N=1: replay the step from a CUDA graph (StepGraph); auto = the launch-bound small "
                          "configs (<= 2M lookups per step: cfg1, cfg2), where it is worth 1.6-1.9x")
+    ap.add_argument("--rowwise", default="routed", choices=["routed", "legacy"],
+                    help="cfg4: routed = bucketise by owner + remote stores + owners reduce their own lookups (SURVEY 8e); "
+                         "legacy = round 1's two all-gathers + whole-batch backward on every owner")
     ap.add_argument("--rows-cap", type=int, default=0, help="cap rows per table (profiling under ncu only)")
     ap.add_argument("--cpu-batch", type=int, default=65536,
                     help="batch of the CPU sample (capped at the workload's batch)")
@@ -181,7 +184,7 @@ class DeviceWorkload:
     synthetic inputs.  Index batches are seeded per TABLE, so the ranks that share a split table see the
     same indices."""
 
-    def __init__(self, torch, pkg, wl, parts, dev, pool, seed):
+    def __init__(self, torch, pkg, wl, parts, dev, pool, seed, num_groups=None):
         self.torch, self.wl, self.parts, self.dev = torch, wl, parts, dev
         self.owned = [p.table for p in parts]
         self.widths = [p.width for p in parts]
@@ -206,7 +209,8 @@ class DeviceWorkload:
             self.out.append(torch.empty((wl.batch, p.width), dtype=torch.float32, device=dev))
         self.pool = pool
         # one collection per pipeline group (a group's parts share one width)
-        self.K = 1 + max((p.group for p in parts), default=0)
+        # (the number of groups is the PLAN's: a rank may hold parts of fewer groups than its peers)
+        self.K = num_groups if num_groups is not None else 1 + max((p.group for p in parts), default=0)
         self.group_of = [[i for i, p in enumerate(parts) if p.group == k] for k in range(self.K)]
         self.colls = [pkg.EmbeddingCollection([self.W[i] for i in ids], [wl.bags[parts[i].table] for i in ids], wl.aggr)
                       if ids else None for ids in self.group_of]
@@ -283,7 +287,7 @@ def main():
     own = [next(p.rank for p in plan if p.table == t) for t in range(wl.num_tables)]
     mine = sorted([p for p in plan if p.rank == rank], key=lambda p: (p.group, p.table, p.col0))
     owned = [p.table for p in mine]
-    dw = DeviceWorkload(torch, pkg, wl, mine, dev, args.pool, seed=1234)
+    dw = DeviceWorkload(torch, pkg, wl, mine, dev, args.pool, seed=1234, num_groups=pkg.sharding.num_groups(plan))
     ex = fx = sstep = None
     if world > 1 and args.exchange == "nccl":
         ex = pkg.exchange.TableWiseExchange(wl.num_tables, own, wl.batch, wl.dim, rank, world, dev)
@@ -343,8 +347,34 @@ def main():
 
     use_graph = (args.graph == "on" or (args.graph == "auto" and wl.lookups <= 2_000_000)) and \
         world == 1 and args.backward == "sorted"
+    # N > 1, fused exchange: a rank's share of a step is ~50 launches of 5-100 us on three streams; the
+    # whole pipelined step (flag kernels included) is replayed from one CUDA graph per index batch
+    use_sgraph = fx is not None and overlap and args.graph != "off" and dw.pool % 2 == 0
     per_step_launches, eager_phases = 0, None
-    if use_graph:
+    parity = None
+    if fx is not None:
+        parity = sharded_parity_step(torch, pkg, dist, wl, dw, fx, sstep, plan, rank, world, dev)
+    if use_sgraph:
+        for k in range(args.warmup):
+            step(k)
+        barrier()
+        pkg.profile_enable(True)
+        pkg.profile_collect()
+        l0 = pkg.launch_count()
+        for k in range(args.steps):
+            step(k)
+        barrier()
+        per_step_launches = (pkg.launch_count() - l0) / args.steps
+        eager_phases = pkg.profile_collect()
+        pkg.profile_enable(False)
+        sgraphs = [sstep.capture([[dw.idx[i][p] for i in ids] for ids in dw.group_of], wl.lr, parity=p % 2)
+                   for p in range(dw.pool)]
+        barrier()
+
+        def step(k):  # noqa: F811
+            sgraphs[k % dw.pool].replay()
+        use_graph = True
+    elif use_graph:
         # phases and the launch count come from an eager profiled pass of the same kernels; the timed
         # region then replays one captured graph per index batch of the pool
         for k in range(args.warmup):
@@ -366,9 +396,6 @@ def main():
         def step(k):  # noqa: F811
             graphs[k % dw.pool].graph.replay()
 
-    parity = None
-    if fx is not None:
-        parity = sharded_parity_step(torch, pkg, dist, wl, dw, fx, sstep, plan, rank, world, dev)
     for k in range(args.warmup):
         step(k)
     barrier()
@@ -405,7 +432,8 @@ def main():
         for rep_ in range(2):
             barrier()
             sstep.trace = []
-            step(args.warmup + args.steps + rep_)
+            kk = args.warmup + args.steps + rep_
+            sstep.run([[dw.idx[i][kk % dw.pool] for i in ids] for ids in dw.group_of], wl.lr, overlap=overlap)
             torch.cuda.synchronize()
             tl = sstep.trace_ms()
             sstep.trace = None
@@ -534,14 +562,109 @@ def main():
     return 0
 
 
+def rowwise_parity_step(torch, dist, wl, rc, idx0, dx, out, rank, world, dev):
+    """One un-timed step of the row-wise path held against a recomputation (the check may use
+    collectives and torch reads of peer memory; the product path uses neither):
+      forward : pooled rows bit-exact against the owners' shard rows added in j order;
+      route   : the owner's slot arrays == (global index - first row of the shard, -1 elsewhere) and the
+                routed output-grad rows == the senders' dx rows, bit for bit;
+      update  : touched rows of this shard == old - lr * (sum of their gradients) within 2e-6 relative
+                (fp32 summation order / FMA contraction), a sample of untouched rows bit-identical."""
+    T, D, ext, lr = wl.num_tables, wl.dim, rc.ext, wl.lr
+    n = rc.hi - rc.lo
+    res = {"forward_bit_exact": True, "routed_slots_bit_exact": True, "routed_rows_bit_exact": True,
+           "updated_rows_ok": True, "untouched_rows_bit_identical": True, "worst_rel_err": 0.0}
+    full_idx = []
+    for t in range(T):
+        pad = torch.full((ext, wl.bags[t]), -1, dtype=torch.int64, device=dev)
+        pad[:n] = idx0[t]
+        full = torch.empty((world * ext, wl.bags[t]), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(full, pad)
+        full_idx.append(full)
+    padg = torch.zeros((ext, T * D), device=dev)
+    padg[:n] = dx
+    dx_full = torch.empty((world * ext, T * D), device=dev)
+    dist.all_gather_into_tensor(dx_full, padg)
+    outs = rc.forward(idx0, out)
+    torch.cuda.synchronize()
+    for t in range(T):
+        L, rps = wl.bags[t], rc.rps[t]
+        bufs = [rc.handles[t].get_buffer(g, (rps + 1, D), torch.float32) for g in range(world)]
+        want = torch.zeros((n, D), device=dev)
+        for j in range(L):
+            own = idx0[t][:, j] // rps
+            loc = idx0[t][:, j] - own * rps
+            row = torch.empty((n, D), device=dev)
+            for g in range(world):
+                m = own == g
+                row[m] = bufs[g][loc[m]]
+            want = want + row
+            if wl.aggr == 22:
+                want = want / float(L)
+        if wl.aggr == 122:
+            want = want * (1.0 / L)
+        res["forward_bit_exact"] &= bool(torch.equal(outs[t], want))
+    # rows of this shard the step will touch, and their values before it
+    olds, keys, rnd_rows, rnd_old = [], [], [], []
+    gen = torch.Generator(device=dev).manual_seed(99 + rank)
+    for t in range(T):
+        rps, full = rc.rps[t], full_idx[t]
+        mine = (full >= rank * rps) & (full < (rank + 1) * rps)
+        u, inv = torch.unique(full[mine] - rank * rps, return_inverse=True)
+        keys.append((mine, u, inv))
+        olds.append(rc.shards[t][u].clone())
+        r = torch.randint(0, max(1, rc.local_rows[t]), (4096,), device=dev, generator=gen)
+        r = r[~torch.isin(r, u)]
+        rnd_rows.append(r)
+        rnd_old.append(rc.shards[t][r].clone())
+    dist.barrier()
+    rc.backward_sgd(idx0, dx, lr)
+    torch.cuda.synchronize()
+    dist.barrier()
+    for t in range(T):
+        L, rps, full = wl.bags[t], rc.rps[t], full_idx[t]
+        mine, u, inv = keys[t]
+        if not rc.legacy:
+            want_slots = torch.where(mine, full - rank * rps, torch.full_like(full, -1))
+            res["routed_slots_bit_exact"] &= bool(torch.equal(rc.slot_views[t], want_slots))
+            bags_here = mine.any(dim=1)
+            res["routed_rows_bit_exact"] &= bool(torch.equal(rc.grow_views[t][bags_here],
+                                                             dx_full[bags_here, t * D:(t + 1) * D]))
+        g = dx_full[:, t * D:(t + 1) * D]
+        if wl.aggr != 21:
+            g = g / float(L)
+        bag_of = torch.arange(full.shape[0], device=dev).unsqueeze(1).expand_as(full)[mine]
+        acc = torch.zeros((u.numel(), D), device=dev).index_add_(0, inv, g[bag_of])
+        want = olds[t] - lr * acc
+        got = rc.shards[t][u]
+        err = ((got - want).abs() / want.abs().clamp_min(1e-3)).max().item() if u.numel() else 0.0
+        res["worst_rel_err"] = max(res["worst_rel_err"], err)
+        res["updated_rows_ok"] &= err <= 2e-6
+        res["untouched_rows_bit_identical"] &= bool(torch.equal(rc.shards[t][rnd_rows[t]], rnd_old[t]))
+    flags = [res[k] for k in res if k != "worst_rel_err"]
+    okt = torch.tensor([1 if all(flags) else 0], device=dev)
+    errt = torch.tensor([res["worst_rel_err"]], device=dev, dtype=torch.float64)
+    dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+    dist.all_reduce(errt, op=dist.ReduceOp.MAX)
+    res["ok"] = bool(okt.item())
+    res["worst_rel_err"] = errt.item()
+    res["what"] = ("one un-timed step: forward vs the owners' shard rows (bit-exact), routed slots / output-grad rows "
+                   "(bit-exact), touched rows vs old - lr*sum(g) (<= 2e-6 relative), untouched rows bit-identical; "
+                   "flags of rank 0, `ok` = all ranks")
+    return res
+
+
 def run_rowwise(args, torch, pkg, dist, wl, rank, world, dev):
     """BASELINE config 4: tables too large for one GPU, sharded ROW-WISE over the ranks
-    (exchange.RowWiseTable).  Every rank pools its own samples (rows read from the owners' shards over
-    NVLink inside the kernel); backward = all-gather of indices + output-grads, local sort/reduce/SGD."""
+    (exchange.RowWiseCollection).  Every rank pools its own samples (rows read from the owners' shards
+    over NVLink inside the kernel); backward = route (bucketise by owner, remote stores of local row
+    numbers + output-grad rows), flag, the owners' sorted backward over their own lookups, flag.
+    --rowwise legacy: the round-1 form (two all-gathers, every owner walks the whole batch)."""
     lo, hi = pkg.sharding.batch_block(wl.batch, world, rank)
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
     T, D = wl.num_tables, wl.dim
-    rc = pkg.exchange.RowWiseCollection(wl.rows, D, wl.bags, wl.batch, rank, world, dev, wl.aggr)
+    legacy = args.rowwise == "legacy"
+    rc = pkg.exchange.RowWiseCollection(wl.rows, D, wl.bags, wl.batch, rank, world, dev, wl.aggr, legacy=legacy)
     for t in range(T):
         a = (1.0 / wl.rows[t]) ** 0.5
         rc.shards[t][:rc.local_rows[t]].uniform_(-a, a, generator=g)
@@ -556,14 +679,16 @@ def run_rowwise(args, torch, pkg, dist, wl, rank, world, dev):
         idx.append(pkg.load_sparse_inputs(sm, wl.bags, hi - lo))
     dx = torch.empty((hi - lo, T * D), device=dev).uniform_(-1, 1, generator=g)
     out = [torch.empty((hi - lo, D), device=dev) for _ in range(T)]
-    tabs = [rc]
     stream = torch.cuda.current_stream()
     torch.cuda.synchronize()
     dist.barrier()
+    parity = None
+    if not legacy:
+        parity = rowwise_parity_step(torch, dist, wl, rc, idx[0], dx, out, rank, world, dev)
 
     def step(k):
         rc.forward(idx[k % args.pool], out)
-        rc.backward_sgd(idx_sm[k % args.pool], dx, wl.lr)
+        rc.backward_sgd(idx_sm[k % args.pool] if legacy else idx[k % args.pool], dx, wl.lr)
 
     def barrier():
         dist.barrier()
@@ -572,12 +697,34 @@ def run_rowwise(args, torch, pkg, dist, wl, rank, world, dev):
     for k in range(args.warmup):
         step(k)
     barrier()
+    use_graph = not legacy and args.graph != "off"
+    if use_graph:   # the step is ~25 launches of a few microseconds: replay it from a CUDA graph per index batch
+        graphs = []
+        for p in range(args.pool):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, capture_error_mode="thread_local"):
+                step(p)
+            graphs.append(gr)
+        barrier()
+        eager_step = step
+
+        def step(k):  # noqa: F811
+            graphs[k % args.pool].replay()
+        for k in range(args.warmup):
+            step(k)
+        barrier()
     sampler = ClockSampler(dev.index) if rank == 0 else None
     if sampler:
         sampler.start()
+    pkg.profile_collect()
     l0 = pkg.launch_count()
+    if use_graph:   # launches per step from one eager step
+        eager_step(0)
+        barrier()
+        per_step = pkg.launch_count() - l0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    l0 = pkg.launch_count()
     e0.record(stream)
     for k in range(args.steps):
         step(args.warmup + k)
@@ -586,27 +733,46 @@ def run_rowwise(args, torch, pkg, dist, wl, rank, world, dev):
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = t.item() / args.steps
-    launches = pkg.launch_count() - l0
+    launches = per_step * args.steps if use_graph else pkg.launch_count() - l0
     clocks = sampler.stop() if sampler else None
     peak, peak_src = peaks()
     n, D = wl.lookups, wl.dim
     alg = 16 * n + 4 * D * n + 8 * D * wl.num_tables * wl.batch + 8 * D * n  # U ~ N (uniform over 100M rows)
+    # NVLink bytes this rank sends per step: forward = the rows it READS from foreign shards arrive inbound
+    # (counted at the reader); backward route = one gradient row per (bag, foreign owner) + 8 B per lookup and peer
+    lookups_rank = (hi - lo) * sum(wl.bags)
+    far = (world - 1) / world
+    nvl = {"forward_rows_read_remote": int(lookups_rank * far * D * 4),
+           "route_rows_sent": int(lookups_rank * far * D * 4) if not legacy else None,
+           "route_slots_sent": int(lookups_rank * (world - 1) * 8) if not legacy else None,
+           "allgather_received": int((wl.batch - (hi - lo)) * (T * D * 4 + sum(wl.bags) * 8)) if legacy else None}
     if rank == 0:
-        print(json.dumps({
+        line = {
             "metric": METRIC, "value": n / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl.name, "tables": wl.num_tables, "dim": D, "batch": wl.batch, "bags": wl.bags,
                        "rows_total": int(sum(wl.rows)), "table_bytes_per_gpu": int(sum(sh.numel() * 4 for sh in rc.shards)),
                        "lookups_per_step": n, "parallelism": f"row-wise x{world}: remote gathers over NVLink in the "
-                       "forward kernels; per step ONE all-gather (NCCL) of the sample-major indices and ONE of "
-                       "the interaction-input gradients, then one local deterministic backward for all tables",
+                       "forward kernels; backward = " + (
+                           "ONE all-gather (NCCL) of the sample-major indices and ONE of the interaction-input "
+                           "gradients, then one local deterministic backward over the whole batch (round-1 form)"
+                           if legacy else
+                           "route kernel (bucketise by owner; local row numbers + output-grad rows stored into the "
+                           "owners' buffers over NVLink), epoch flag, the owners' sorted backward + SGD over their own "
+                           "lookups only, epoch flag; no collective"),
+                       "cuda_graph": bool(use_graph),
+                       "nvlink_bytes_per_rank_per_step": nvl,
                        "cache": "tables far larger than L2, random rows"},
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "step (launch/latency-bound at 64K lookups per table)",
                          "achieved": round(alg / (ms_step * 1e-3) / 1e9, 1), "peak": peak * world, "unit": "GB/s",
                          "frac": round(alg / (ms_step * 1e-3) / 1e9 / (peak * world), 4), "traffic": None,
-                         "peak_source": peak_src}}), flush=True)
+                         "peak_source": peak_src}}
+        if parity is not None:
+            line["parity_ok"] = bool(parity["ok"])
+            line["parity"] = parity
+        print(json.dumps(line), flush=True)
     dist.destroy_process_group()
     return 0
 

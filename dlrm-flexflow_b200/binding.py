@@ -47,6 +47,11 @@ class ffemb_sync_t(C.Structure):
     _fields_ = [("peer_pad", C.c_void_p * FFEMB_MAX_PEERS), ("num_peers", C.c_int32), ("rank", C.c_int32)]
 
 
+class ffemb_route_t(C.Structure):
+    _fields_ = [("peer_slots", C.c_void_p * FFEMB_MAX_PEERS), ("peer_rows", C.c_void_p * FFEMB_MAX_PEERS),
+                ("num_peers", C.c_int32), ("rank", C.c_int32), ("samples_per_peer", C.c_int64)]
+
+
 def library_path():
     return os.path.join(HERE, "libffemb.so")
 
@@ -102,6 +107,8 @@ def lib():
     L.ffemb_sync_wait.argtypes = [C.POINTER(ffemb_sync_t), i32, vp]
     L.ffemb_forward_rowwise.argtypes = [vp, vp, C.POINTER(vp), i32, i64, i64, i64, i64, i32, vp]
     L.ffemb_rowwise_localize.argtypes = [vp, vp, i64, i64, i32, vp, i64, vp]
+    L.ffemb_rowwise_route.argtypes = [tp, i32, i64, i64, vp, i64, C.POINTER(ffemb_route_t), vp]
+    L.ffemb_backward_sgd_padded.argtypes = [tp, i32, i64, i64, i32, f32, vp, sz, vp]
     L.ffemb_backward_dense_atomic.argtypes = [vp, vp, vp, i64, i64, i64, i32, vp]
     L.ffemb_backward_dense.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_sgd.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, f32, vp, sz, vp]

@@ -290,6 +290,17 @@ int ffemb_backward_sgd_batched(const ffemb_table_t *tables, int num_tables, int6
                                 (cudaStream_t)stream);
 }
 
+int ffemb_backward_sgd_padded(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                              int aggr, float lr, void *workspace, size_t workspace_bytes,
+                              ffemb_stream_t stream) {
+  TableBatch tb;
+  int rc = pack(tables, num_tables, D, B, aggr, tb);
+  if (rc) return rc;
+  tb.padded = 1;
+  return launch_backward_sorted(tb, D, B, aggr, lr, APPLY_SGD, workspace, workspace_bytes,
+                                (cudaStream_t)stream);
+}
+
 int ffemb_backward_prepare(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B, int aggr,
                            void *workspace, size_t workspace_bytes, ffemb_stream_t stream) {
   TableBatch tb;

@@ -86,7 +86,9 @@ keygen_kernel(const __grid_constant__ TableBatch tb, int64_t B, K *keys, uint32_
   if (i >= n) return;
   const int64_t b = i / L;
   const int64_t row = __ldg(td.idx + i);
-  keys[td.lookup_base + i] = (K)(tb.row_base[blockIdx.y] + (uint64_t)row);
+  K key = (K)(tb.row_base[blockIdx.y] + (uint64_t)row);
+  if (tb.padded && row < 0) key = (K)tb.row_base[tb.num_tables];  // empty slot: past every row
+  keys[td.lookup_base + i] = key;
   vals[td.lookup_base + i] = ((uint32_t)blockIdx.y << BAG_BITS) | (uint32_t)b;
 }
 
@@ -291,7 +293,7 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
     EntryDesc d;
     d.gp = nullptr;
     d.wp = nullptr;
-    if (p < n) {
+    if (p < n && (uint64_t)keys[p] < tb.row_base[tb.num_tables]) {  // (an empty slot's key is past every row)
       const K k = keys[p];
       const uint32_t v = vals[p];
       const bool is_end = (p + 1 == n) || (keys[p + 1] != k);
@@ -701,7 +703,8 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     keygen_kernel<K><<<grid, kThreads, 0, s>>>(tb, B, keys_a, c.vals_a);
   }
   int end_bit = 1;
-  while (end_bit < (int)sizeof(K) * 8 && ((uint64_t)(total_rows - 1) >> end_bit) != 0) end_bit++;
+  const uint64_t max_key = (uint64_t)total_rows - (tb.padded ? 0 : 1);  // (empty slots carry key = total_rows)
+  while (end_bit < (int)sizeof(K) * 8 && (max_key >> end_bit) != 0) end_bit++;
   if (stage != STAGE_APPLY) {
     // onesweep: histogram + scan + one pass per 8 key bits
     ProfScope prof(FFEMB_PHASE_SORT, 2 + (end_bit + 7) / 8, s);
@@ -873,10 +876,12 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
   memset(&tb, 0, sizeof(tb));
   memset(&ts, 0, sizeof(ts));
   tb.og_stride = ts.og_stride = tb_all.og_stride;
+  tb.padded = tb_all.padded;
+  const bool no_chip = mode == APPLY_SGDX || tb_all.padded;  // (the bag-major kernels know no empty slots)
   int n_tiny = 0;
   for (int pass = 1; pass <= 2; pass++) {  // tiny tables first, then small ones
     for (int t = 0; t < tb_all.num_tables; t++) {
-      if (mode != APPLY_SGDX && tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) == pass) {
+      if (!no_chip && tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) == pass) {
         ts.t[ts.num_tables++] = tb_all.t[t];
         n_tiny += pass == 1;
       }
@@ -887,7 +892,7 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
   int src_table[FFEMB_MAX_TABLES];  // position in the caller's list of the k-th table in key order
   for (int pass = 0; pass < 2; pass++) {
     for (int t = 0; t < tb_all.num_tables; t++) {
-      if (mode != APPLY_SGDX && tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) != 0) continue;
+      if (!no_chip && tb_all.t[t].L > 0 && backward_path(tb_all.t[t].R, tb_all.t[t].L, D, B) != 0) continue;
       const bool streams = tb_all.t[t].R * D * 4 > kStreamTableBytes;
       if (streams != (pass == 0)) continue;
       TableDesc &d = tb.t[tb.num_tables];

@@ -38,6 +38,10 @@ struct TableBatch {
   uint64_t row_base[FFEMB_MAX_TABLES + 1];  // first global row id of each table (bwd keys)
   uint32_t cta_base[FFEMB_MAX_TABLES + 1];  // first CTA of each table in the flat forward grid
   int32_t num_tables;
+  // bwd: indices < 0 are EMPTY SLOTS (the routed lookups of a row-wise shard, ffemb_backward_sgd_padded):
+  // keygen gives them the key `row_base[num_tables]` (one past the last row), they sort to the end
+  // and level 1 never loads anything for them
+  int32_t padded;
   // floats between consecutive rows of the output-grad buffers (bwd).  D: plain [B][D] buffers;
   // larger: td.out points at the table's column block inside a wider row-major matrix — the
   // gradient of the Concat output (ffemb_backward_sgd_concat)

@@ -54,7 +54,7 @@ reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__
     EntryDesc d;
     d.gp = nullptr;
     d.wp = nullptr;
-    if (p < n) {
+    if (p < n && (uint64_t)keys[p] < tb.row_base[tb.num_tables]) {  // (an empty slot's key is past every row)
       const K k = keys[p];
       const uint32_t v = vals[p];
       const bool is_end = (p + 1 == n) || (keys[p + 1] != k);
@@ -73,7 +73,19 @@ reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__
   if (t0 >= n) return;
   const bool own = sl < D4;
   const EntryDesc *dq = wd + sub * CH1;
-  const int cnt = (int)min((int64_t)CH1, n - t0);
+  int cnt = (int)min((int64_t)CH1, n - t0);
+  if (tb.padded) {  // the empty slots are the END of the sorted array: cut the tile at its first one
+    int lo = 0, hi = cnt;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (dq[mid].gp) lo = mid + 1; else hi = mid;
+    }
+    cnt = lo;
+    if (cnt == 0) {  // nothing but empty slots: no partial rows
+      if (sl == 0) keys_out[2 * tile] = keys_out[2 * tile + 1] = INV;
+      return;
+    }
+  }
   bool first_open = (t0 > 0) && (keys[t0 - 1] == keys[t0]);
   bool pending = false, wrote_head = false;
   const uint64_t pol_keep = policy_evict_last(), pol_stream = policy_evict_first();

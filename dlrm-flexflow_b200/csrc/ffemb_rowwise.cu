@@ -12,6 +12,8 @@
 // Backward: the owner of a shard runs the ordinary deterministic backward over the whole batch
 // with indices made local by rowwise_localize_kernel: a lookup of a foreign row is pointed at a
 // scratch row appended to the shard (row rows_per_shard), which nobody reads.
+#include <string.h>
+
 #include "ffemb_internal.cuh"
 
 namespace ffemb {
@@ -110,6 +112,75 @@ rowwise_localize_kernel(const int64_t *__restrict__ idx, int64_t *__restrict__ l
   }
 }
 
+
+// ---- backward: route every lookup of THIS rank's samples to the owner of its row ------
+// Owner g keeps, per table, a slot array laid out like the GLOBAL index tensor [G*ext][L] and an
+// output-grad buffer [G*ext][D]; rank h = `rank` fills the slots and rows of ITS samples
+// (global bags [h*ext, h*ext + n)) on every owner, over NVLink peer memory:
+//     slots_g[t][(h*ext + b)*L + j] = idx[b][j] - g*rps   if g owns the row, else -1 (empty slot)
+//     rows_g [t][(h*ext + b)][:]    = dx[b][col_t : col_t + D]   on the owners of >= 1 lookup of the bag
+// Positions are a function of (rank, b, j) only — no counting, no count exchange — and the owner's
+// sorted backward meets equal rows in global (b, j) order, the single-GPU order.  One CTA = a run of
+// whole bags (about 256 lookups): phase A, one thread per lookup, writes the slot on every owner
+// (coalesced 8-byte stores) and ORs the owner into the bag's mask in shared memory; phase B, one warp
+// per bag, loads the bag's output-grad row once and stores it to every owner in the mask.
+struct RouteTable {
+  const int64_t *idx;   // [n][L]
+  int64_t rps;
+  int64_t slot_base;    // first slot of the table in the owners' slot arrays (entries)
+  int64_t row_base;     // first row of the table in the owners' routed output-grad buffers
+  int32_t L, col;
+  uint32_t cta_base;    // first CTA of the table in the flat grid
+  int32_t bags_per_cta;
+};
+struct RouteArgs {
+  RouteTable t[FFEMB_MAX_TABLES];
+  int64_t *slots[FFEMB_MAX_PEERS];
+  float *rows[FFEMB_MAX_PEERS];
+  const float *dx;
+  int64_t dx_stride, n, first;  // samples of this rank, global number of its first sample
+  int32_t num_tables, npeers, D;
+};
+
+__global__ void __launch_bounds__(256) rowwise_route_kernel(const __grid_constant__ RouteArgs a) {
+  __shared__ uint32_t mask[256];
+  int t = 0;
+  while (t + 1 < a.num_tables && blockIdx.x >= a.t[t + 1].cta_base) t++;  // <= 64 tables
+  const RouteTable &rt = a.t[t];
+  const int L = rt.L;
+  const int64_t b0 = (int64_t)(blockIdx.x - rt.cta_base) * rt.bags_per_cta;
+  const int nb = (int)min((int64_t)rt.bags_per_cta, a.n - b0);
+  if (nb <= 0) return;
+  for (int i = threadIdx.x; i < nb; i += 256) mask[i] = 0u;
+  __syncthreads();
+  // phase A
+  const int64_t nl = (int64_t)nb * L;
+  for (int64_t i = threadIdx.x; i < nl; i += 256) {
+    const int64_t r = __ldg(rt.idx + b0 * L + i);
+    const int64_t g = r / rt.rps;
+    const int64_t slot = rt.slot_base + (a.first + b0) * L + i;
+#pragma unroll
+    for (int h = 0; h < FFEMB_MAX_PEERS; h++)
+      if (h < a.npeers) a.slots[h][slot] = h == g ? r - g * rt.rps : -1;
+    atomicOr(&mask[(int)(i / L)], 1u << (int)g);
+  }
+  __syncthreads();
+  // phase B
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int D4 = a.D >> 2;
+  for (int bb = warp; bb < nb; bb += 8) {
+    const uint32_t m = mask[bb];
+    const float *src = a.dx + (b0 + bb) * a.dx_stride + rt.col;
+    const int64_t drow = rt.row_base + a.first + b0 + bb;
+    for (int c = lane; c < D4; c += 32) {
+      const float4 v = ldg_row(src + 4 * c);
+#pragma unroll
+      for (int h = 0; h < FFEMB_MAX_PEERS; h++)
+        if ((m >> h) & 1u) st_stream(a.rows[h] + drow * a.D + 4 * c, v);
+    }
+  }
+}
+
 }  // namespace ffemb
 
 using namespace ffemb;
@@ -167,6 +238,66 @@ int ffemb_rowwise_localize(const int64_t *idx, int64_t *local_idx, int64_t n, in
   rowwise_localize_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(idx, local_idx, n, rows_per_shard,
                                                                                shard, scratch_row, (int)D);
   return cuda_fail(cudaGetLastError(), "rowwise_localize launch");
+}
+
+
+int ffemb_rowwise_route(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t n_samples,
+                        const float *dx, int64_t row_stride, const ffemb_route_t *rt, ffemb_stream_t stream) {
+  if (!tables || num_tables < 0 || num_tables > FFEMB_MAX_TABLES || D <= 0 || D % 4 != 0 || n_samples < 0 ||
+      !rt || rt->num_peers < 1 || rt->num_peers > FFEMB_MAX_PEERS || rt->rank < 0 || rt->rank >= rt->num_peers ||
+      rt->samples_per_peer < n_samples || (n_samples > 0 && !dx) || row_stride < D || row_stride % 4 != 0 ||
+      (uintptr_t)dx % 16 != 0) {
+    set_error("rowwise_route: invalid arguments (D a multiple of 4, dx 16-byte aligned, n_samples <= samples_per_peer)");
+    return FFEMB_EINVAL;
+  }
+  RouteArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int h = 0; h < rt->num_peers; h++) {
+    if (!rt->peer_slots[h] || !rt->peer_rows[h] || (uintptr_t)rt->peer_rows[h] % 16 != 0) {
+      set_error("rowwise_route: peer_slots[%d] / peer_rows[%d] NULL or misaligned", h, h);
+      return FFEMB_EINVAL;
+    }
+    a.slots[h] = rt->peer_slots[h];
+    a.rows[h] = rt->peer_rows[h];
+  }
+  const int64_t ext = rt->samples_per_peer, G = rt->num_peers;
+  int64_t slot_base = 0, row_base = 0, ctas = 0;
+  for (int t = 0; t < num_tables; t++) {
+    const ffemb_table_t &x = tables[t];
+    if (x.L < 0 || x.R < 1 || x.reserved < 0 || x.reserved % 4 != 0 || (int64_t)x.reserved + D > row_stride ||
+        (n_samples > 0 && x.L > 0 && !x.idx)) {
+      set_error("rowwise_route: table %d: invalid descriptor (R = rows of the WHOLE table, reserved = column of "
+                "its block in dx)", t);
+      return FFEMB_EINVAL;
+    }
+    RouteTable &r = a.t[t];
+    r.idx = x.idx;
+    r.rps = (x.R + G - 1) / G;
+    r.slot_base = slot_base;
+    r.row_base = row_base;
+    r.L = x.L;
+    r.col = x.reserved;
+    r.cta_base = (uint32_t)ctas;
+    r.bags_per_cta = x.L <= 0 ? 256 : (x.L >= 256 ? 1 : 256 / x.L);
+    slot_base += G * ext * x.L;
+    row_base += G * ext;
+    ctas += x.L > 0 ? (n_samples + r.bags_per_cta - 1) / r.bags_per_cta : 0;
+    if (ctas >= (1ll << 31)) {
+      set_error("rowwise_route: too many lookups for one call");
+      return FFEMB_EINVAL;
+    }
+  }
+  a.dx = dx;
+  a.dx_stride = row_stride;
+  a.n = n_samples;
+  a.first = (int64_t)rt->rank * ext;
+  a.num_tables = num_tables;
+  a.npeers = rt->num_peers;
+  a.D = (int)D;
+  if (ctas == 0) return FFEMB_OK;
+  ProfScope prof(FFEMB_PHASE_EXCHANGE, 1, (cudaStream_t)stream);
+  rowwise_route_kernel<<<(unsigned)ctas, 256, 0, (cudaStream_t)stream>>>(a);
+  return cuda_fail(cudaGetLastError(), "rowwise_route launch");
 }
 
 }  // extern "C"

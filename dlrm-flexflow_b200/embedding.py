@@ -209,6 +209,17 @@ class EmbeddingCollection:
             check(fn(sub, e - s, self.dim, batch, self.aggr, float(lr), ws.data_ptr(), ws.numel(),
                      _stream_ptr(stream)))
 
+    def backward_sgd_padded(self, indices, out_grads, lr, stream=None):
+        """backward_sgd where an index < 0 is an EMPTY SLOT (the owner's side of the row-wise backward,
+        ffemb_backward_sgd_padded): skipped without loading anything."""
+        batch = int(indices[0].shape[0])
+        if len(self.weights) > B.FFEMB_MAX_TABLES:
+            raise ValueError("at most 64 tables per call")
+        arr = self._descs(indices, out_grads, self.weights, batch)
+        ws = self._workspaces(batch)[0]
+        check(lib().ffemb_backward_sgd_padded(arr, len(self.weights), self.dim, batch, self.aggr, float(lr),
+                                              ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
+
     def backward_sgdx(self, indices, out_grads, lr, weight_decay=0.0, momentum=0.0, nesterov=False,
                       V=None, stream=None):
         """Backward fused with the reference's full sgd_update (weight decay / momentum / nesterov,

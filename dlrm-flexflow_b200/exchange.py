@@ -285,8 +285,9 @@ class ShardedStep:
         self.fx, self.colls, self.dev = fx, colls, device
         # the push and the index sort are short, latency-critical pieces that must get SM slots while a
         # long gather-pool / segmented-sum grid is draining: high-priority streams
-        self.s_push = torch.cuda.Stream(device=device, priority=-1)
-        self.s_side = torch.cuda.Stream(device=device, priority=-1)
+        import os
+        self.s_push = torch.cuda.Stream(device=device, priority=int(os.environ.get("FFEMB_PUSH_PRIO", "-1")))
+        self.s_side = torch.cuda.Stream(device=device, priority=int(os.environ.get("FFEMB_SIDE_PRIO", "-1")))
         self.ev_sorted = [torch.cuda.Event() for _ in range(fx.K)]
         self.ev_x = torch.cuda.Event()
         self.trace = None   # set to [] to collect (label, start event, end event) of every piece of a step
@@ -339,7 +340,40 @@ class ShardedStep:
                 self._span(f"bwd{k}", main, lambda: self.colls[k].backward_sgd(
                     idx_groups[k], fx.outgrads_by_group[k], lr, stream=main, prepared=overlap))
         main.wait_stream(push)
+        if overlap:
+            main.wait_stream(side)   # (a group without parts of this rank leaves its sort event unwaited)
         return fx.x
+
+    def capture(self, idx_groups, lr, parity):
+        """The whole pipelined step — three streams, the cross-rank flag kernels included — as ONE CUDA
+        graph (ShardedStepGraph).  At 8 GPUs a rank's share of a step is ~50 launches of 5-100 us: enqueued
+        one by one from the host they take longer than they run."""
+        return ShardedStepGraph(self, idx_groups, lr, parity)
+
+
+class ShardedStepGraph:
+    """ShardedStep.run captured once for one set of index buffers and one parity of the double-buffered
+    interaction input; replay() = one graph launch.  Capturable because no entry point synchronises or
+    allocates, the flags keep their epochs in the pad (include/ffemb.h, ffemb_sync_*), and the streams
+    fork from / join the capture stream through events.  Every rank must replay the same sequence of
+    steps; consecutive steps must alternate parity (x(step) may still be read while step + 1 is written).
+    Same kernels in the same order as the eager step: bit-identical results."""
+
+    def __init__(self, sstep, idx_groups, lr, parity):
+        fx = sstep.fx
+        self.sstep, self.parity = sstep, int(parity)
+        self.graph = torch.cuda.CUDAGraph()
+        keep = fx.parity
+        fx.parity = self.parity ^ 1      # begin_step() flips it
+        trace, sstep.trace = sstep.trace, None
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+            sstep.run(idx_groups, lr, overlap=True)
+        fx.parity, sstep.trace = keep, trace
+
+    def replay(self):
+        self.sstep.fx.parity = self.parity
+        self.graph.replay()
+        return self.sstep.fx.x
 
 
 class RowWiseTable:
@@ -414,46 +448,89 @@ class RowWiseTable:
 
 
 class RowWiseCollection:
-    """Several row-wise sharded tables driven together (BASELINE config 4: 8 x 100M x 128).
+    """Several row-wise sharded tables driven together (BASELINE config 4: 8 x 100M x 128), SURVEY 8e.
 
-    RowWiseTable costs two collectives and a full launch sequence per table; at 64K lookups per table
-    that is pure latency.  Here one step of ALL tables is
-      forward     : one remote-gather launch per table (rows read from the owners' shards over NVLink);
-      backward_sgd: ONE all-gather of the ranks' sample-major index batches [B_h][sum L] and ONE of
-                    their interaction-input gradients [B_h][T*D] (the layouts the data loader and the
-                    Concat gradient have anyway), then ffemb_load_sparse_inputs cuts every table's
-                    [B][L] out of the gathered batch, rowwise_localize points foreign rows at the
-                    scratch row, and ONE ffemb_backward_sgd_concat reads every table's output-grads in
-                    place from the gathered gradient: one keygen / sort / segmented sum for all tables.
-    Shard map, forward arithmetic and results are RowWiseTable's (bit-identical forward)."""
+      forward     : one remote-gather launch per table — rows are read from the owners' shards over NVLink
+                    inside the gather-pool kernel; adds in j order on the sample's rank (bit-identical to
+                    the unsharded table).
+      backward_sgd: ROUTE (ffemb_rowwise_route, one launch for all tables): every lookup of this rank's
+                    samples is bucketised by owner = row / ceil(R/G) and its local row number stored into
+                    the owner's slot array, the bag's output-grad row into the owner's routed-gradient
+                    buffer — remote stores over NVLink, the all-to-all-v of indices + gradient rows done
+                    by the kernel itself; slot = position of the lookup in the GLOBAL batch, so nothing
+                    is counted and no counts are exchanged (foreign slots hold -1);
+                    flag (ffemb_sync_signal / _wait): all ranks' routes have landed;
+                    REDUCE (ffemb_backward_sgd_padded, one call for all tables): the ordinary sorted
+                    backward + SGD over the owner's slot arrays; empty slots sort to the end and are
+                    never loaded — an owner gathers and updates its own lookups only;
+                    flag: every shard is updated before anyone's next forward reads it.
+    No collective call, no host synchronisation; per rank and step the NVLink carries one output-grad
+    row per (bag, owner) pair + 8 bytes per lookup and owner instead of the whole batch's gradient.
+    `legacy=True` keeps the round-1 form (two all-gathers, every owner walks the whole batch) as the
+    measured comparison."""
 
-    def __init__(self, rows, dim, bags, batch, rank, world, device, aggr=21, group=None):
+    R_SLOT, D_SLOT = 0, 1   # flags: routes landed / shards updated
+
+    def __init__(self, rows, dim, bags, batch, rank, world, device, aggr=21, group=None, legacy=False):
         import torch.distributed._symmetric_memory as symm
+        from .binding import ffemb_route_t, ffemb_sync_t, lib
         from .embedding import EmbeddingCollection
         from .sharding import rows_per_shard, shard_rows
         self.rows, self.D, self.bags, self.B = [int(r) for r in rows], int(dim), [int(l) for l in bags], int(batch)
         self.T = len(self.rows)
         self.rank, self.world, self.device, self.aggr = rank, world, device, int(aggr)
         self.group = group if group is not None else dist.group.WORLD
+        self.legacy = bool(legacy)
         self.rps = [rows_per_shard(r, world) for r in self.rows]
         self.local_rows = [shard_rows(r, world, rank) for r in self.rows]
         self.ext = (self.B + world - 1) // world
         self.lo, self.hi = batch_block(self.B, world, rank)
         self.shards, self.handles = [], []
         for t in range(self.T):
-            s = symm.empty((self.rps[t] + 1, self.D), dtype=torch.float32, device=device)  # + scratch row
+            s = symm.empty((self.rps[t] + 1, self.D), dtype=torch.float32, device=device)  # (+ legacy scratch row)
             self.handles.append(symm.rendezvous(s, self.group))
             s.zero_()
             self.shards.append(s)
         self.sumL = sum(self.bags)
         i64, f32 = dict(dtype=torch.int64, device=device), dict(dtype=torch.float32, device=device)
-        self._pad_i = torch.zeros((self.ext, self.sumL), **i64)
-        self._pad_g = torch.zeros((self.ext, self.T * self.D), **f32)
-        self.idx_full = torch.zeros((world * self.ext, self.sumL), **i64)
-        self.g_full = torch.zeros((world * self.ext, self.T * self.D), **f32)
-        self.idx_glob = [torch.empty((self.B, l), **i64) for l in self.bags]
-        self.idx_local = [torch.empty((self.B, l), **i64) for l in self.bags]
-        self.coll = EmbeddingCollection(self.shards, self.bags, self.aggr)
+        Bp = world * self.ext   # the batch padded to whole blocks: the owners' slot arrays cover it
+        self.Bp = Bp
+        if self.legacy:
+            self._pad_i = torch.zeros((self.ext, self.sumL), **i64)
+            self._pad_g = torch.zeros((self.ext, self.T * self.D), **f32)
+            self.idx_full = torch.zeros((Bp, self.sumL), **i64)
+            self.g_full = torch.zeros((Bp, self.T * self.D), **f32)
+            self.idx_glob = [torch.empty((self.B, l), **i64) for l in self.bags]
+            self.idx_local = [torch.empty((self.B, l), **i64) for l in self.bags]
+            self.coll = EmbeddingCollection(self.shards, self.bags, self.aggr)
+        else:
+            # slot arrays [T][Bp][L_t] (int64, -1 = empty) and routed gradient rows [T][Bp][D], peer-mapped
+            self.slots = symm.empty((max(1, Bp * self.sumL),), **i64)
+            self.grows = symm.empty((max(1, self.T * Bp), self.D), **f32)
+            self.pad = symm.empty((lib().ffemb_sync_pad_bytes() // 8,), **i64)
+            self.hs = symm.rendezvous(self.slots, self.group)
+            self.hr = symm.rendezvous(self.grows, self.group)
+            self.hp = symm.rendezvous(self.pad, self.group)
+            self.slots.fill_(-1)   # (a ragged last block leaves its tail slots untouched: empty)
+            self.grows.zero_()
+            self.pad.zero_()
+            rt = ffemb_route_t()
+            sy = ffemb_sync_t()
+            for h in range(world):
+                rt.peer_slots[h] = int(self.hs.buffer_ptrs[h])
+                rt.peer_rows[h] = int(self.hr.buffer_ptrs[h])
+                sy.peer_pad[h] = int(self.hp.buffer_ptrs[h])
+            rt.num_peers, rt.rank, rt.samples_per_peer = world, rank, self.ext
+            sy.num_peers, sy.rank = world, rank
+            self._route, self._sync = rt, sy
+            off, self.slot_views = 0, []
+            for l in self.bags:
+                self.slot_views.append(self.slots[off:off + Bp * l].view(Bp, l))
+                off += Bp * l
+            self.grow_views = [self.grows[t * Bp:(t + 1) * Bp] for t in range(self.T)]
+            # the owner's reduce: shards as tables of rps rows (the scratch row stays out), batch = Bp
+            self.coll = EmbeddingCollection([s[:self.rps[t]] for t, s in enumerate(self.shards)], self.bags, self.aggr)
+            self._dirty = False   # a backward has signalled D_SLOT and nobody has waited on it yet
         torch.cuda.synchronize(device)
         dist.barrier(group=self.group)
 
@@ -464,6 +541,12 @@ class RowWiseCollection:
         torch.cuda.synchronize(self.device)
         dist.barrier(group=self.group)
 
+    def _flag(self, fn, slot, stream):
+        import ctypes as C
+        from .binding import check
+        from .embedding import _stream_ptr
+        check(fn(C.byref(self._sync), slot, _stream_ptr(stream)))
+
     def forward(self, idx_list, outs=None, stream=None):
         """idx_list[t]: int64 [B_h][L_t] global row ids of this rank's samples -> pooled [B_h][D] per table."""
         import ctypes as C
@@ -472,27 +555,45 @@ class RowWiseCollection:
         n = int(idx_list[0].shape[0])
         if outs is None:
             outs = [torch.empty((n, self.D), dtype=torch.float32, device=self.device) for _ in range(self.T)]
+        if not self.legacy and self._dirty:   # every rank's shards carry the previous step's update
+            self._flag(lib().ffemb_sync_wait, self.D_SLOT, stream)
+            self._dirty = False
         for t in range(self.T):
             ptrs = (C.c_void_p * self.world)(*[int(p) for p in self.handles[t].buffer_ptrs])
             check(lib().ffemb_forward_rowwise(idx_list[t].data_ptr(), outs[t].data_ptr(), ptrs, self.world,
                                               self.rps[t], self.bags[t], self.D, n, self.aggr, _stream_ptr(stream)))
         return outs
 
-    def backward_sgd(self, idx_sm, dx, lr, stream=None):
-        """idx_sm: int64 [B_h][sum L] — this rank's samples, sample-major (table t's bag at columns
-        [sum_{s<t} L_s, +L_t)); dx: [B_h][T*D] — the gradient of its interaction input (table t's
-        block at columns [t*D, +D)).  Updates this rank's shards of every table."""
-        from .binding import check, lib
+    def backward_sgd(self, idx, dx, lr, stream=None):
+        """dx: [B_h][T*D] — the gradient of this rank's interaction input (table t's block at columns
+        [t*D, +D)); idx: the per-table index tensors [B_h][L_t] of its samples (legacy form: ONE
+        sample-major int64 [B_h][sum L] tensor).  Updates this rank's shards of every table."""
+        from .binding import check, ffemb_table_t, lib
         from .embedding import _stream_ptr, load_sparse_inputs
         n = self.hi - self.lo
-        self._pad_i[:n].copy_(idx_sm)
-        self._pad_g[:n].copy_(dx)
-        dist.all_gather_into_tensor(self.idx_full, self._pad_i, group=self.group)  # also orders every
-        dist.all_gather_into_tensor(self.g_full, self._pad_g, group=self.group)    # rank's forward first
-        load_sparse_inputs(self.idx_full, self.bags, self.B, outs=self.idx_glob, stream=stream)
+        if self.legacy:
+            self._pad_i[:n].copy_(idx)
+            self._pad_g[:n].copy_(dx)
+            dist.all_gather_into_tensor(self.idx_full, self._pad_i, group=self.group)  # also orders every
+            dist.all_gather_into_tensor(self.g_full, self._pad_g, group=self.group)    # rank's forward first
+            load_sparse_inputs(self.idx_full, self.bags, self.B, outs=self.idx_glob, stream=stream)
+            for t in range(self.T):
+                check(lib().ffemb_rowwise_localize(self.idx_glob[t].data_ptr(), self.idx_local[t].data_ptr(),
+                                                   self.B * self.bags[t], self.rps[t], self.rank,
+                                                   self.shards[t][self.rps[t]].data_ptr(), self.D, _stream_ptr(stream)))
+            self.coll.backward_sgd_concat(self.idx_local, self.g_full, lr, stream=stream)
+            self.handles[0].barrier(channel=0)  # shards are consistent before anyone's next forward reads them
+            return
+        import ctypes as C
+        arr = (ffemb_table_t * self.T)()
         for t in range(self.T):
-            check(lib().ffemb_rowwise_localize(self.idx_glob[t].data_ptr(), self.idx_local[t].data_ptr(),
-                                               self.B * self.bags[t], self.rps[t], self.rank,
-                                               self.shards[t][self.rps[t]].data_ptr(), self.D, _stream_ptr(stream)))
-        self.coll.backward_sgd_concat(self.idx_local, self.g_full, lr, stream=stream)
-        self.handles[0].barrier(channel=0)  # shards are consistent before anyone's next forward reads them
+            arr[t].idx, arr[t].R, arr[t].L, arr[t].reserved = idx[t].data_ptr(), self.rows[t], self.bags[t], t * self.D
+        if self._dirty:   # (two backwards in a row without a forward: the owners are done with the last routes)
+            self._flag(lib().ffemb_sync_wait, self.D_SLOT, stream)
+        check(lib().ffemb_rowwise_route(arr, self.T, self.D, n, dx.data_ptr(), int(dx.shape[1]),
+                                        C.byref(self._route), _stream_ptr(stream)))
+        self._flag(lib().ffemb_sync_signal, self.R_SLOT, stream)
+        self._flag(lib().ffemb_sync_wait, self.R_SLOT, stream)
+        self.coll.backward_sgd_padded(self.slot_views, self.grow_views, lr, stream=stream)
+        self._flag(lib().ffemb_sync_signal, self.D_SLOT, stream)
+        self._dirty = True

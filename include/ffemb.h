@@ -174,16 +174,53 @@ FFEMB_API int ffemb_sync_wait(const ffemb_sync_t *sync, int slot, ffemb_stream_t
  * forward_rowwise pools THIS rank's samples (idx [B][L] holds global row ids) and reads every row
  * from the owner's shard over NVLink peer memory (peer_shards[g] = device pointer to shard g,
  * valid on this device); adds are sequential in j, so results are bit-identical to the unsharded
- * table.  For the backward the shard owner runs ffemb_backward_sgd over the WHOLE batch on local
- * indices made by rowwise_localize: rows of other shards map to the scratch row `rows_per_shard`
- * that the owner appends to its shard (the shard buffer holds rows_per_shard + 1 rows; the scratch
- * row is cleared here and never read by anyone).                                               */
+ * table.  Backward, SURVEY 8e (bucketise by owner, route indices + the needed output-grad rows to the
+ * owners as remote stores, owners reduce their own lookups only): see ffemb_rowwise_route below.
+ * ffemb_rowwise_localize is the round-1 form kept as the measured comparison (every owner walks the
+ * WHOLE all-gathered batch; rows of other shards map to a scratch row `rows_per_shard` appended to the
+ * shard, cleared here and never read by anyone).                                                  */
 FFEMB_API int ffemb_forward_rowwise(const int64_t *idx, float *out, const float *const *peer_shards,
                           int num_peers, int64_t rows_per_shard, int64_t L, int64_t D, int64_t B,
                           int aggr, ffemb_stream_t stream);
 FFEMB_API int ffemb_rowwise_localize(const int64_t *idx, int64_t *local_idx, int64_t n,
                            int64_t rows_per_shard, int shard, float *scratch_row, int64_t D,
                            ffemb_stream_t stream);
+
+/* Row-wise backward, step 1: ROUTE.  Rank `rank` holds the indices of ITS samples (tables[t].idx =
+ * [n_samples][L_t] global row ids) and dx [n_samples][row_stride], the gradient of its interaction
+ * input (table t's block at column tables[t].reserved).  Every owner g keeps, for all tables back to
+ * back, a slot array shaped like the GLOBAL index tensors and a routed output-grad buffer:
+ *     peer_slots[g] : int64, table t at entry  S_t = sum_{s<t} G*ext*L_s,  shaped [G*ext][L_t]
+ *     peer_rows[g]  : float, table t at row    G*ext*t,                    shaped [G*ext][D]
+ * (ext = samples_per_peer = ceil(B / G), Legion's blocked batch split, src/runtime/model.cc:876-895;
+ * pointers as mapped on THIS device).  The kernel fills the slots of its samples — global bags
+ * [rank*ext, rank*ext + n_samples) — on EVERY owner:  row - g*rows_per_shard  where g owns the row,
+ * -1 (empty slot) elsewhere; and stores the bag's output-grad row to every owner of at least one of
+ * its lookups.  rows_per_shard = ceil(tables[t].R / G) with tables[t].R the rows of the WHOLE table;
+ * tables[t].out / table are ignored.  Slot positions depend on (rank, sample, j) only: nothing is
+ * counted or compacted, no counts are exchanged, and an owner meets equal rows in global (sample, j)
+ * order — the order of the unsharded backward.  NVLink bytes per rank: 8*G per lookup (slots) + one
+ * output-grad row per (bag, owner) pair, against the whole batch's gradient per rank for an
+ * all-gather.  Order the owners' backward after all ranks' routes with ffemb_sync_signal / _wait.  */
+typedef struct ffemb_route {
+  int64_t *peer_slots[FFEMB_MAX_PEERS];
+  float *peer_rows[FFEMB_MAX_PEERS];
+  int32_t num_peers;
+  int32_t rank;
+  int64_t samples_per_peer;
+} ffemb_route_t;
+FFEMB_API int ffemb_rowwise_route(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t n_samples,
+                        const float *dx, int64_t row_stride, const ffemb_route_t *route,
+                        ffemb_stream_t stream);
+/* Row-wise backward, step 2: the owner's fused backward + SGD over its slot arrays.  Exactly
+ * ffemb_backward_sgd_batched (tables[t].idx = the table's slot array [B][L_t] with B = G*ext,
+ * tables[t].out = its routed output-grad rows [B][D], tables[t].table = the shard, R = its rows)
+ * except that an index < 0 is an EMPTY SLOT: it gets the key one past the last row, sorts to the
+ * end, and the segmented sum neither loads an output-grad row nor touches a table row for it.  Every
+ * table takes the sorted path.  ffemb_backward_workspace sizes the scratch as for any batched call. */
+FFEMB_API int ffemb_backward_sgd_padded(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
+                              int aggr, float lr, void *workspace, size_t workspace_bytes,
+                              ffemb_stream_t stream);
 
 /* ---- backward, API-exact (unfused): replaces Embedding::backward_kernel -------------------
  * Accumulates into the dense, caller-zeroed weight-grad like embed_backward

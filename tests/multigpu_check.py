@@ -128,6 +128,30 @@ def main():
                         dup = B * bags[p.table] / rows[p.table] + 1
                         assert torch.allclose(Wp[k][j], want, rtol=0, atol=1e-6 * 0.01 * dup ** 0.5 * 8 + 1e-7), \
                             ("pipelined", aggr, split_tables, it, p, "updated part far from the unsharded table")
+            # the same step replayed from CUDA graphs (ShardedStepGraph): two more steps, alternating parity
+            caps = []
+            for it in (3, 4):
+                idx_it = [(i + it) % r for i, r in zip(idx, rows)]
+                idxg = [[idx_it[p.table] for p in mine[k]] for k in range(K)]
+                caps.append((sstep.capture(idxg, 0.01, parity=it % 2), idx_it, idxg))
+            for (gr, idx_it, idxg), it in zip(caps, (3, 4)):
+                dxs = torch.rand((B, T * D), device=dev, generator=torch.Generator(device=dev).manual_seed(100 + it)) - 0.5
+                fx.dx.copy_(dxs[lo:hi])
+                want_x = torch.cat(tcoll.forward(idx_it), dim=1)
+                x = gr.replay()[:hi - lo]
+                assert torch.allclose(x, want_x[lo:hi], rtol=0, atol=1e-5), ("graph replay", aggr, split_tables, it, "x differs")
+                tcoll.backward_sgd(idx_it, [dxs[:, t * D:(t + 1) * D].contiguous() for t in range(T)], 0.01)
+                torch.cuda.synchronize()
+                for k in range(K):
+                    for j, p in enumerate(mine[k]):
+                        c0 = p.table * D + p.col0
+                        assert torch.equal(fx.outgrads_by_group[k][j], dxs[:, c0:c0 + p.width]), \
+                            ("graph replay", aggr, split_tables, it, p, "routed output-grad differs")
+                        want = truth[p.table][:, p.col0:p.col0 + p.width]
+                        dup = B * bags[p.table] / rows[p.table] + 1
+                        assert torch.allclose(Wp[k][j], want, rtol=0, atol=(it + 1) * (1e-6 * 0.01 * dup ** 0.5 * 8 + 1e-7)), \
+                            ("graph replay", aggr, split_tables, it, p, "updated part far from the unsharded table")
+            del caps
             dist.barrier()
         # ---- forward-only loop across ranks (no backward between the steps): x of step k must survive
         # until this rank has compared it although the peers are already storing step k + 1 ----
@@ -167,32 +191,56 @@ def main():
         torch.cuda.synchronize()
         assert torch.allclose(out2, one.forward([idx])[0][lo:hi], rtol=0, atol=1e-5)
         dist.barrier()
-    # ---- several row-wise tables in one step (RowWiseCollection: two collectives per step in all) ----
-    rows3, bags3, aggr = [100003, 5001, 70001], [1, 5, 3], 21
-    g = torch.Generator(device=dev).manual_seed(23)
-    Ws = [torch.rand((r, D), device=dev, generator=g) - 0.5 for r in rows3]
-    idx = [torch.randint(0, r, (B, l), device=dev, generator=g) for r, l in zip(rows3, bags3)]
-    dx = torch.rand((B, len(rows3) * D), device=dev, generator=g) - 0.5
-    refW = [w.clone() for w in Ws]
-    one = pkg.EmbeddingCollection(refW, bags3, aggr)
-    ref_out = one.forward(idx)
-    one.backward_sgd(idx, [dx[:, t * D:(t + 1) * D].contiguous() for t in range(len(rows3))], 0.01)
-    lo, hi = pkg.sharding.batch_block(B, world, rank)
-    rc = pkg.exchange.RowWiseCollection(rows3, D, bags3, B, rank, world, dev, aggr)
-    rc.load_rows(Ws)
-    outs = rc.forward([i[lo:hi].contiguous() for i in idx])
-    torch.cuda.synchronize()
-    for t in range(len(rows3)):
-        assert torch.equal(outs[t], ref_out[t][lo:hi]), ("row-wise collection forward differs", t)
-    rc.backward_sgd(torch.cat([i[lo:hi] for i in idx], dim=1).contiguous(), dx[lo:hi].contiguous(), 0.01)
-    torch.cuda.synchronize()
-    for t in range(len(rows3)):
-        r0 = rank * rc.rps[t]
-        mine, want = rc.shards[t][:rc.local_rows[t]], refW[t][r0:r0 + rc.local_rows[t]]
-        cnt = torch.bincount(idx[t].reshape(-1), minlength=rows3[t])[r0:r0 + rc.local_rows[t]]
-        assert torch.equal(mine[cnt <= 1], want[cnt <= 1]), ("row-wise collection: single-lookup rows differ", t)
-        assert torch.allclose(mine, want, rtol=0, atol=1e-6), ("row-wise collection update differs", t)
-    dist.barrier()
+    # ---- several row-wise tables in one step (RowWiseCollection).  routed: route kernel + flags + the owners'
+    # padded backward, two steps in a row (the second forward reads every rank's updated shards);
+    # legacy: round 1's two all-gathers + whole-batch backward ----
+    for aggr in (21, 22):
+        rows3, bags3 = [100003, 5001, 70001], [1, 5, 3]
+        g = torch.Generator(device=dev).manual_seed(23)
+        Ws = [torch.rand((r, D), device=dev, generator=g) - 0.5 for r in rows3]
+        lo, hi = pkg.sharding.batch_block(B, world, rank)
+        for legacy in (False, True):
+            refW = [w.clone() for w in Ws]
+            one = pkg.EmbeddingCollection(refW, bags3, aggr)
+            rc = pkg.exchange.RowWiseCollection(rows3, D, bags3, B, rank, world, dev, aggr, legacy=legacy)
+            rc.load_rows(Ws)
+            for it in range(2):
+                gi = torch.Generator(device=dev).manual_seed(31 + it)
+                idx = [torch.randint(0, r, (B, l), device=dev, generator=gi) for r, l in zip(rows3, bags3)]
+                dx = torch.rand((B, len(rows3) * D), device=dev, generator=gi) - 0.5
+                ref_out = one.forward(idx)
+                mine_idx = [i[lo:hi].contiguous() for i in idx]
+                outs = rc.forward(mine_idx)
+                torch.cuda.synchronize()
+                for t in range(len(rows3)):
+                    if it == 0:
+                        assert torch.equal(outs[t], ref_out[t][lo:hi]), ("row-wise collection forward differs", t, legacy)
+                    else:   # the tables of step 2 carry step 1's update: equal up to its summation order
+                        assert torch.allclose(outs[t], ref_out[t][lo:hi], rtol=0, atol=1e-5), ("row-wise forward, step 2", t)
+                one.backward_sgd(idx, [dx[:, t * D:(t + 1) * D].contiguous() for t in range(len(rows3))], 0.01)
+                if legacy:
+                    rc.backward_sgd(torch.cat(mine_idx, dim=1).contiguous(), dx[lo:hi].contiguous(), 0.01)
+                else:
+                    rc.backward_sgd(mine_idx, dx[lo:hi].contiguous(), 0.01)
+                torch.cuda.synchronize()
+                dist.barrier()
+                for t in range(len(rows3)):
+                    r0 = rank * rc.rps[t]
+                    mine, want = rc.shards[t][:rc.local_rows[t]], refW[t][r0:r0 + rc.local_rows[t]]
+                    if not legacy:   # routed slots / rows: bit-exact
+                        full = idx[t]
+                        own = (full >= r0) & (full < r0 + rc.rps[t])
+                        assert torch.equal(rc.slot_views[t][:B], torch.where(own, full - r0, torch.full_like(full, -1))), \
+                            ("routed slots differ", t, it)
+                        assert bool((rc.slot_views[t][B:] == -1).all()), ("slots past the batch must stay empty", t)
+                        bags_here = own.any(dim=1)
+                        assert torch.equal(rc.grow_views[t][:B][bags_here], dx[bags_here, t * D:(t + 1) * D]), \
+                            ("routed output-grad rows differ", t, it)
+                    if it == 0:
+                        cnt = torch.bincount(idx[t].reshape(-1), minlength=rows3[t])[r0:r0 + rc.local_rows[t]]
+                        assert torch.equal(mine[cnt <= 1], want[cnt <= 1]), ("row-wise collection: single-lookup rows differ", t, legacy)
+                    assert torch.allclose(mine, want, rtol=0, atol=2e-6), ("row-wise collection update differs", t, legacy, it)
+            dist.barrier()
     if rank == 0:
         print(f"multigpu_check ok: world={world}, fused and nccl exchanges bit-exact vs single GPU")
     dist.destroy_process_group()

@@ -816,3 +816,89 @@ def test_general_optimizers_on_an_empty_batch_still_update_every_row(ffemb, orac
     wW, wM, wV = oracle.adam_update(W, np.zeros_like(W), np.full_like(W, 0.5), np.full_like(W, 0.125), 1e-3, 0.9, 0.999, 1e-2, 1e-8)
     assert np.array_equal(dW[0].cpu().numpy(), wW)
     assert np.array_equal(dM[0].cpu().numpy(), wM) and np.array_equal(dV[0].cpu().numpy(), wV)
+
+
+# ---------------------------------------------------------------------------------------------
+# row-wise backward: route + the owners' padded backward, G ranks emulated on ONE GPU
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("G", [2, 8])
+@pytest.mark.parametrize("aggr", [21, 22])
+def test_rowwise_route_and_padded_backward_emulated_ranks(ffemb, oracle, torch_cuda, G, aggr):
+    """Every "rank" h runs ffemb_rowwise_route for ITS batch block into G local owner buffers (all peer
+    pointers are plain local memory here), then every "owner" runs ffemb_backward_sgd_padded on its shard:
+      * slot arrays == the oracle's stable bucketing by owner (oracle_route_rows: owner = row / ceil(R/G),
+        local row = row % ceil(R/G)), bit-exact, -1 everywhere else;
+      * routed output-grad rows == the senders' rows on every owner of >= 1 lookup of the bag;
+      * shards put back together == the unsharded step: rows with one lookup bit-identical to the
+        single-GPU call, all rows within the summation-order bound of the oracle's reference step."""
+    import ctypes as C
+    torch = torch_cuda
+    B_, D = 1001, 64   # ragged last block
+    rows, bags = [10007, 300, 50001], [1, 4, 3]
+    T, sumL = len(rows), sum(bags)
+    ext = (B_ + G - 1) // G
+    Bp = G * ext
+    rng = np.random.default_rng(5 + G + aggr)
+    Ws = [rng.uniform(-0.5, 0.5, (r, D)).astype(np.float32) for r in rows]
+    idx = [rng.integers(0, r, (B_, l), dtype=np.int64) for r, l in zip(rows, bags)]
+    idx[1][:, 0] = 7                      # one hot row, met by every sample of every rank
+    dx = rng.uniform(-1, 1, (B_, T * D)).astype(np.float32)
+    d_idx, d_dx = [dev(torch, i) for i in idx], dev(torch, dx)
+    slots = [torch.full((Bp * sumL,), -1, dtype=torch.int64, device="cuda") for _ in range(G)]
+    grows = [torch.zeros((T * Bp, D), dtype=torch.float32, device="cuda") for _ in range(G)]
+    L_ = ffemb.lib()
+    for h in range(G):
+        lo, hi = oracle.batch_block(B_, G, h)
+        rt = ffemb.binding.ffemb_route_t()
+        for g in range(G):
+            rt.peer_slots[g], rt.peer_rows[g] = slots[g].data_ptr(), grows[g].data_ptr()
+        rt.num_peers, rt.rank, rt.samples_per_peer = G, h, ext
+        arr = (ffemb.binding.ffemb_table_t * T)()
+        keep = [d_idx[t][lo:hi].contiguous() for t in range(T)]
+        for t in range(T):
+            arr[t].idx, arr[t].R, arr[t].L, arr[t].reserved = keep[t].data_ptr(), rows[t], bags[t], t * D
+        mine = d_dx[lo:hi].contiguous()
+        ffemb.binding.check(L_.ffemb_rowwise_route(arr, T, D, hi - lo, mine.data_ptr(), T * D, C.byref(rt), None))
+        torch.cuda.synchronize()
+    # slots and routed rows against the oracle's bucketing
+    views, off = [], 0
+    for t in range(T):
+        views.append([s[off:off + Bp * bags[t]].view(Bp, bags[t]) for s in slots])
+        off += Bp * bags[t]
+    for t in range(T):
+        offsets, perm, local = oracle.route_rows(idx[t].reshape(-1), rows[t], G)
+        for g in range(G):
+            want = np.full(Bp * bags[t], -1, np.int64)
+            want[perm[offsets[g]:offsets[g + 1]]] = local[offsets[g]:offsets[g + 1]]
+            assert np.array_equal(views[t][g].cpu().numpy().reshape(-1), want), (t, g, "routed slots")
+            bags_here = (want.reshape(Bp, bags[t])[:B_] >= 0).any(axis=1)
+            got = grows[g][t * Bp:t * Bp + B_].cpu().numpy()
+            assert np.array_equal(got[bags_here], dx[bags_here, t * D:(t + 1) * D]), (t, g, "routed rows")
+    # the owners' backward, then put the shards back together
+    lr = 0.01
+    new = [np.empty_like(w) for w in Ws]
+    for g in range(G):
+        shards = []
+        for t in range(T):
+            rps = oracle.rows_per_shard(rows[t], G)
+            sh = np.zeros((rps, D), np.float32)
+            part = Ws[t][g * rps:(g + 1) * rps]
+            sh[:len(part)] = part
+            shards.append(dev(torch, sh))
+        coll = ffemb.EmbeddingCollection(shards, bags, aggr)
+        coll.backward_sgd_padded([views[t][g] for t in range(T)], [grows[g][t * Bp:(t + 1) * Bp] for t in range(T)], lr)
+        torch.cuda.synchronize()
+        for t in range(T):
+            rps = oracle.rows_per_shard(rows[t], G)
+            n = len(Ws[t][g * rps:(g + 1) * rps])
+            new[t][g * rps:g * rps + n] = shards[t].cpu().numpy()[:n]
+    one = [dev(torch, w) for w in Ws]
+    ffemb.EmbeddingCollection(one, bags, aggr).backward_sgd(d_idx, [d_dx[:, t * D:(t + 1) * D].contiguous() for t in range(T)], lr)
+    torch.cuda.synchronize()
+    for t in range(T):
+        cnt = np.bincount(idx[t].reshape(-1), minlength=rows[t])
+        single = one[t].cpu().numpy()
+        assert np.array_equal(new[t][cnt <= 1], single[cnt <= 1]), (t, "single-lookup / untouched rows")
+        want = oracle.reference_step(idx[t], dx[:, t * D:(t + 1) * D].copy(), Ws[t].copy(), aggr, lr)
+        tol = table_tol(Ws[t]) * np.sqrt(np.maximum(cnt, 1))[:, None] * 2
+        assert np.all(np.abs(new[t].astype(np.float64) - want) <= tol), (t, "updated table")
