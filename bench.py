@@ -70,6 +70,7 @@ def parse():
     ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
                     help="N=1: replay the step from a CUDA graph (StepGraph); auto = the launch-bound small "
                          "configs (<= 2M lookups per step: cfg1, cfg2), where it is worth 1.6-1.9x")
+    ap.add_argument("--aggr", type=int, default=0, help="override the workload's aggregation (21 SUM, 22 AVG literal, 122 MEAN): experiments")
     ap.add_argument("--rowwise", default="routed", choices=["routed", "legacy"],
                     help="cfg4: routed = bucketise by owner + remote stores + owners reduce their own lookups (SURVEY 8e); "
                          "legacy = round 1's two all-gathers + whole-batch backward on every owner")
@@ -273,6 +274,9 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     wl = pkg.synth.config(args.workload, args.scale)
+    if args.aggr:
+        wl.aggr = args.aggr
+        wl.name += f"-aggr{args.aggr}"
     if args.rows_cap:
         wl.rows = [min(r, args.rows_cap) for r in wl.rows]
         wl.name += f"-rowscap{args.rows_cap}"

@@ -126,6 +126,8 @@ def lib():
     L.ffemb_backward_dense_batched.argtypes = [tp, i32, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_workspace.argtypes = [i64, i64, i64]
     L.ffemb_backward_workspace.restype = sz
+    L.ffemb_backward_workspace_avg.argtypes = [i64, i64, i64, i64, i32]
+    L.ffemb_backward_workspace_avg.restype = sz
     L.ffemb_backward_path.argtypes = [i64, i64, i64, i64]
     L.ffemb_load_sparse_inputs.argtypes = [tp, i32, vp, i64, vp, i64, i64, vp]
     L.ffemb_check_indices.argtypes = [vp, i64, i64, vp, vp]
@@ -140,7 +142,7 @@ def lib():
 
 
 PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small", "exchange", "input", "dense",
-          "sync"]
+          "sync", "prescale"]
 
 
 def profile_enable(on=True):

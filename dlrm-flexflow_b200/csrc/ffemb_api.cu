@@ -50,6 +50,7 @@ const Tuning &tuning() {
     x.slab_mb = (int)num("FFEMB_SLAB_MB");
     x.own_sort = (int)num("FFEMB_OWN_SORT");
     x.xpush = (int)num("FFEMB_XPUSH");
+    x.prescale = (int)num("FFEMB_PRESCALE");
     return x;
   }();
   return t;
@@ -471,6 +472,12 @@ int ffemb_backward_path(int64_t R, int64_t L, int64_t D, int64_t B) { return bac
 
 size_t ffemb_backward_workspace(int64_t num_lookups, int64_t total_rows, int64_t D) {
   return backward_workspace_bytes(num_lookups, total_rows, D);
+}
+
+size_t ffemb_backward_workspace_avg(int64_t num_lookups, int64_t total_rows, int64_t D, int64_t B, int num_tables) {
+  const size_t base = backward_workspace_bytes(num_lookups, total_rows, D);
+  if (base == 0 || B < 0 || num_tables < 0 || num_tables > FFEMB_MAX_TABLES) return 0;
+  return base + (size_t)num_tables * prescale_bytes(B, D);
 }
 
 int ffemb_load_sparse_inputs(const ffemb_table_t *tables, int num_tables, const int64_t *full,

@@ -25,6 +25,7 @@
 // The shape of the summation tree depends only on (sorted order, CH1, CH2): bit-reproducible
 // run to run, unlike the reference's atomics.  Rows with a single lookup get exactly the
 // reference's arithmetic (g summed into 0, then one FFMA), i.e. bit-identical updates.
+#include <cub/block/block_radix_sort.cuh>
 #include <cub/device/device_radix_sort.cuh>
 
 #include <stdlib.h>
@@ -92,6 +93,66 @@ keygen_kernel(const __grid_constant__ TableBatch tb, int64_t B, K *keys, uint32_
   vals[td.lookup_base + i] = ((uint32_t)blockIdx.y << BAG_BITS) | (uint32_t)b;
 }
 
+
+// ---- 1+2 for small batches: keygen + sort of a table's lookups inside ONE CTA ---------------------
+// The device-wide radix sort is a chain of 6-7 dependent launches whatever the size; at 2K-16K lookups
+// per table (BASELINE configs 1 and 2) that chain IS the step (55 of 82 us, 87 of 147 us).  The key
+// order is (table, row) and a table's lookups are contiguous in the lookup numbering, so each table
+// can be sorted on its own: one CTA of 1024 threads per table reads the indices straight from the
+// index tensor (keygen fused), sorts (local row, (table, bag)) pairs on the ceil(log2 R_t) row bits in
+// shared memory (cub::BlockRadixSort: LSD, stable — bags ascend inside a run of equal rows, like the
+// device-wide sort) and writes the table's stretch of the sorted arrays.  One launch, all tables in
+// parallel, 2-6 passes of 4 bits each in shared memory.
+static constexpr int kSegThreads = 1024;
+static constexpr int kSegMaxItems = 16;  // up to 16384 lookups per table
+
+template <int ITEMS>
+__global__ void __launch_bounds__(kSegThreads)
+seg_sort_kernel(const __grid_constant__ TableBatch tb, int64_t B, uint32_t *__restrict__ keys_out,
+                uint32_t *__restrict__ vals_out) {
+  using Sort = cub::BlockRadixSort<uint32_t, kSegThreads, ITEMS, uint32_t>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  typename Sort::TempStorage &tmp = *reinterpret_cast<typename Sort::TempStorage *>(smem_raw);
+  const int t = blockIdx.x;
+  const TableDesc &td = tb.t[t];
+  const int L = td.L;
+  const int n = (int)(B * (int64_t)L);
+  if (n == 0) return;
+  uint32_t k[ITEMS], v[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; i++) {
+    const int q = threadIdx.x * ITEMS + i;
+    k[i] = 0xffffffffu;  // padding: sorts behind every lookup (ties keep the input order: padding is last)
+    v[i] = 0u;
+    if (q < n) {
+      k[i] = (uint32_t)__ldg(td.idx + q);
+      v[i] = ((uint32_t)t << BAG_BITS) | (uint32_t)(q / L);
+    }
+  }
+  int end_bit = 32 - __clz((unsigned)(td.R > 1 ? td.R - 1 : 1));
+  Sort(tmp).Sort(k, v, 0, end_bit);
+  const uint32_t base = (uint32_t)tb.row_base[t];
+#pragma unroll
+  for (int i = 0; i < ITEMS; i++) {
+    const int q = threadIdx.x * ITEMS + i;
+    if (q < n) {
+      keys_out[td.lookup_base + q] = base + k[i];
+      vals_out[td.lookup_base + q] = v[i];
+    }
+  }
+}
+
+template <int ITEMS>
+static cudaError_t launch_seg_sort(const TableBatch &tb, int64_t B, uint32_t *keys_out, uint32_t *vals_out,
+                                   cudaStream_t s) {
+  using Sort = cub::BlockRadixSort<uint32_t, kSegThreads, ITEMS, uint32_t>;
+  const size_t sm = sizeof(typename Sort::TempStorage);
+  cudaError_t e = cudaFuncSetAttribute(seg_sort_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+  if (e != cudaSuccess) return e;
+  seg_sort_kernel<ITEMS><<<tb.num_tables, kSegThreads, sm, s>>>(tb, B, keys_out, vals_out);
+  return cudaGetLastError();
+}
+
 // table of a global row id: row_base is ascending, <= 65 entries
 __device__ __forceinline__ int find_table(const TableBatch &tb, uint64_t key) {
   int lo = 0, hi = tb.num_tables - 1;
@@ -112,10 +173,12 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
                                             const float *rows_in, int64_t n, int64_t tile, int CH,
                                             bool active, int D, float lr,
                                             K *keys_out, float *rows_out, int sub, int sl,
-                                            const OptArgs *oa = nullptr) {
+                                            const OptArgs *oa = nullptr, const uint8_t *consumed = nullptr) {
   constexpr K INV = KeyTraits<K>::INV;
   constexpr int UNR = (C == 1) ? 4 : (C == 2 ? 2 : 1);
   const int D4 = D >> 2;
+  // a slot combine_kernel has already summed and applied reads as invalid
+  auto ldk = [&](int64_t q) -> K { return (consumed && consumed[q]) ? INV : keys[q]; };
   const int64_t t0 = tile * CH;
   const int64_t t1 = active ? min(n, t0 + CH) : t0;
 
@@ -132,9 +195,9 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
     const int64_t p = p0 + sl;
     K k = INV, kn = INV, kn2 = INV;
     if (p < t1) {
-      k = keys[p];
-      if (p + 1 < n) kn = keys[p + 1];
-      if (p + 2 < n) kn2 = keys[p + 2];
+      k = ldk(p);
+      if (p + 1 < n) kn = ldk(p + 1);
+      if (p + 2 < n) kn2 = ldk(p + 2);
     }
     // does the run of entry p stop at p?  (lookahead crosses the tile edge on purpose)
     const bool is_end = (k != INV) && !(kn == k || (kn == INV && kn2 == k));
@@ -178,8 +241,8 @@ __device__ __forceinline__ void reduce_tile(const TableBatch &tb, const K *keys,
           seen = true;
           const int64_t q = p0 + jj + u;
           K km1 = INV, km2 = INV;
-          if (q >= 1) km1 = keys[q - 1];
-          if (q >= 2) km2 = keys[q - 2];
+          if (q >= 1) km1 = ldk(q - 1);
+          if (q >= 2) km2 = ldk(q - 2);
           first_open = (km1 == ek[u]) || (km1 == INV && km2 == ek[u]);
         }
 #pragma unroll
@@ -259,6 +322,11 @@ __device__ __forceinline__ uint32_t mix_cta(uint32_t i, uint32_t grid, uint32_t 
   return a1 != a0 ? a0 : split + (i - a0);
 }
 
+// Marks of the level-1 partial slots, one byte each (two per tile), written 0 by level 1 and 1 by
+// combine_kernel for the slots it has summed and applied; the 32-bit word in front of them is the
+// "chains left for the tree" flag (reset by level 1, set by combine_kernel).
+__host__ __device__ __forceinline__ uint32_t *up_flag(uint16_t *consumed) { return reinterpret_cast<uint32_t *>(consumed) - 1; }
+
 struct __align__(16) EntryDesc {
   const float *gp;  // output-grad row of this lookup (nullptr: past the end of the array)
   float *wp;        // table row to update when this entry ends its run, else nullptr
@@ -270,7 +338,7 @@ template <typename K, int G, int C, int MODE, bool AVG, bool PIPE>
 __global__ void __launch_bounds__(L1Threads<G>::value, 512 / L1Threads<G>::value)
 reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
                const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
-               float *rows_out, int flags, uint32_t split, const OptArgs *oa) {
+               float *rows_out, int flags, uint32_t split, const OptArgs *oa, uint16_t *consumed) {
   constexpr int THREADS = L1Threads<G>::value;
   constexpr int CH1 = Ch1<G>::value;
   constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
@@ -281,6 +349,7 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   EntryDesc *wd = reinterpret_cast<EntryDesc *>(smem_raw) + warp * EPW;
   float2 *wscale = reinterpret_cast<float2 *>(smem_raw + sizeof(EntryDesc) * WARPS * EPW) + warp * EPW;
+  if (blockIdx.x == 0 && threadIdx.x == 0) up_flag(consumed)[0] = 0;  // "chains left for the tree": set by combine_kernel
   const int64_t wbase = ((int64_t)mix_cta(blockIdx.x, gridDim.x, split) * WARPS + warp) * EPW;
   if (wbase >= n) return;  // warp-uniform; only __syncwarp below
   const int D4 = D >> 2;
@@ -313,6 +382,7 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
   const int64_t tile = wbase / CH1 + sub;
   const int64_t t0 = tile * CH1;
   if (t0 >= n) return;  // this slot's tile is empty (its descriptors are all null)
+  if (sl == 0) consumed[tile] = 0;  // (both partial slots of the tile: not yet taken by combine_kernel)
   const EntryDesc *dq = wd + sub * CH1;
   const float2 *sq = wscale + sub * CH1;
   const int cnt = (int)min((int64_t)CH1, n - t0);
@@ -498,25 +568,170 @@ reduce1_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
 #include "ffemb_reduce1_ring.cuh"
 namespace ffemb {
 
+
+// ---- everything above level 1 in ONE launch, for runs cut by a few tile edges (the usual case) ----
+// Level 1 leaves, per tile s, a head partial (slot 2s: the tile's first run began earlier and ends
+// here) and a tail partial (slot 2s+1: its last run goes on).  A run cut by tile edges is therefore a
+// CHAIN  tail(s), tail(s+1) ... tail(e-1), head(e)  — tiles s+1 .. e-1 lie inside the run — and chains
+// of different runs are independent.  One slot of G lanes per tile s: if tail(s) is the FIRST piece of
+// its chain (tail(s-1) has another key) the slot finds the chain's end (its G lanes look at G tiles per
+// round), adds the pieces in order and does the run's one read-modify-write of the table row — all
+// chains in parallel, no serial walk over tiles of partial slots, no further levels.  The pieces it
+// used are marked in `consumed`.  A chain of more than kMaxChain pieces (one row with thousands of
+// lookups: skewed indices) is left to the tree below (reduce_level / reduce_tail, which read marked
+// slots as invalid) and the "chains left" flag is raised; when it stays 0 the tree kernels return at
+// once.  The order of the adds depends on the sorted order and CH1 only: bit-reproducible.
+static constexpr int kMaxChain = 128;
+
+template <typename K, int G, int C, int MODE>
+__global__ void __launch_bounds__(kThreads)
+combine_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
+               const float *__restrict__ rows, uint16_t *consumed16, int64_t ntiles, int D, float lr,
+               const OptArgs *oa) {
+  constexpr K INV = KeyTraits<K>::INV;
+  constexpr int SLOTS = 32 / G;
+  constexpr int PER = G >= 8 ? 1 : 8 / G;           // tiles a lane probes per round (narrow slots: 8 per round)
+  constexpr int ROUNDS = kMaxChain / (G * PER) > 0 ? kMaxChain / (G * PER) : 1;
+  uint8_t *consumed = reinterpret_cast<uint8_t *>(consumed16);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane / G, sl = lane % G;
+  const int D4 = D >> 2;
+  const int64_t nwarps = (int64_t)gridDim.x * (kThreads / 32);
+  // a warp scans 32 tiles at a time for chain starts (coalesced key reads; most tiles start none) ...
+  for (int64_t base = ((int64_t)blockIdx.x * (kThreads / 32) + warp) * 32; base < ntiles; base += nwarps * 32) {
+    const int64_t sc = base + lane;
+    K kc = INV;
+    if (sc < ntiles) kc = keys[2 * sc + 1];
+    const bool is_start = kc != INV && (sc == 0 || keys[2 * sc - 1] != kc);
+    uint32_t pending = __ballot_sync(0xffffffffu, is_start);
+    // ... and its slots of G lanes take the starts SLOTS at a time
+    while (pending) {  // warp-uniform
+      const int pick = (int)__fns(pending, 0, sub + 1);       // the (sub+1)-th start, 0xffffffff: none left for this slot
+      const bool start = pick >= 0 && pick < 32;
+      const int src = start ? pick : 0;
+      const int64_t s = base + src;
+      const K kt = shfl_key<K>(kc, src);
+#pragma unroll
+      for (int i = 0; i < SLOTS; i++) pending &= pending - 1;  // the SLOTS lowest starts are taken
+      // 1. where does the chain end?  (keys only: a chain that is too long costs a few probes, no row loads)
+      bool done = !start, ok = false;
+      int64_t t = s + 1;      // next tile of the chain
+      int conts = 0;          // tiles lying inside the run (their tail partial is a piece)
+#pragma unroll 1
+      for (int r = 0; r < ROUNDS; r++) {  // uniform trip count: the ballots need every lane
+#pragma unroll
+        for (int pp = 0; pp < PER; pp++) {
+          const int64_t tt = t + pp * G + sl;
+          K kh = INV, kn = INV;
+          if (!done && tt < ntiles) {
+            kh = keys[2 * tt];
+            kn = keys[2 * tt + 1];
+          }
+          constexpr uint32_t GMASK = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
+          const uint32_t endm = (__ballot_sync(0xffffffffu, !done && kh == kt) >> (sub * G)) & GMASK;
+          const uint32_t conm = (__ballot_sync(0xffffffffu, !done && kh != kt && kn == kt) >> (sub * G)) & GMASK;
+          if (!done) {
+            const uint32_t stop = ~conm & GMASK;             // first tile of this probe that is not inside the run
+            const int nc = stop ? __ffs(stop) - 1 : G;
+            conts += nc;
+            if (nc < G) {
+              done = true;
+              ok = ((endm >> nc) & 1u) != 0;                 // the chain's last piece: the head partial of that tile
+            }
+          }
+        }
+        t += (int64_t)PER * G;
+        if (__ballot_sync(0xffffffffu, !done) == 0) break;   // (warp-uniform)
+      }
+      if (!start) continue;
+      if (!ok) {  // longer than kMaxChain pieces: the tree's
+        if (sl == 0) up_flag(consumed16)[0] = 1u;
+        continue;
+      }
+  // 2. the pieces in order: tail(s), tail(s+1 .. s+conts), head(s+conts+1); loads UB at a time, adds in order
+  constexpr int UB = C == 1 ? 8 : (C == 2 ? 4 : 2);
+  float4 acc[C], w[C];
+  const int tbl = find_table(tb, (uint64_t)kt);
+  float *wp = tb.t[tbl].table + (int64_t)((uint64_t)kt - tb.row_base[tbl]) * D;
+#pragma unroll
+  for (int c = 0; c < C; c++) {
+    if (sl + c * G < D4) {
+      w[c] = ld_f4(wp + 4 * (sl + c * G));  // (in flight while the pieces are added)
+      acc[c] = ld_f4(rows + (2 * s + 1) * (int64_t)D + 4 * (sl + c * G));
+    }
+  }
+  const int npieces = conts + 1;  // after tail(s)
+#pragma unroll 1
+  for (int i0 = 0; i0 < npieces; i0 += UB) {
+    float4 v[UB][C];
+#pragma unroll
+    for (int u = 0; u < UB; u++) {
+      const int i = i0 + u;
+      if (i < npieces) {
+        const int64_t q = i < conts ? 2 * (s + 1 + i) + 1 : 2 * (s + 1 + conts);
+#pragma unroll
+        for (int c = 0; c < C; c++)
+          if (sl + c * G < D4) v[u][c] = ld_f4(rows + q * (int64_t)D + 4 * (sl + c * G));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UB; u++) {
+      if (i0 + u < npieces) {
+#pragma unroll
+        for (int c = 0; c < C; c++)
+          if (sl + c * G < D4) f4_add(acc[c], v[u][c]);
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < C; c++) {
+    if (sl + c * G < D4) {
+      float4 o = w[c];
+      if (MODE == APPLY_SGD) {  // W -= lr*gt, contracted like the reference's FFMA
+        o.x = fmaf(-acc[c].x, lr, o.x); o.y = fmaf(-acc[c].y, lr, o.y);
+        o.z = fmaf(-acc[c].z, lr, o.z); o.w = fmaf(-acc[c].w, lr, o.w);
+      } else if (MODE == APPLY_SGDX) {
+        o = sgdx_fragment(oa, tbl, tb.t[tbl].table, wp + 4 * (sl + c * G), o, acc[c],
+                          (uint64_t)kt - tb.row_base[tbl], sl == 0 && c == 0);
+      } else {
+        f4_add(o, acc[c]);
+      }
+      st_f4(wp + 4 * (sl + c * G), o);
+    }
+  }
+  // the pieces are spent: tail(s), tail(s+1 .. s+conts), head(s+conts+1)
+  for (int i = sl; i < conts; i += G) consumed[2 * (s + 1 + i) + 1] = 1;
+  if (sl == 0) {
+    consumed[2 * s + 1] = 1;
+    consumed[2 * (s + 1 + conts)] = 1;
+  }
+    }
+  }
+}
+
 template <typename K, int G, int C, int MODE>
 __global__ void __launch_bounds__(kThreads)
 reduce_level_kernel(const __grid_constant__ TableBatch tb, const K *keys,
                     const float *rows_in, int64_t n, int CH, int D, float lr,
-                    K *keys_out, float *rows_out, const OptArgs *oa) {
+                    K *keys_out, float *rows_out, const OptArgs *oa, const uint32_t *flag,
+                    const uint8_t *consumed) {
+  if (*flag == 0) return;  // combine_kernel left no chain for the tree (the usual case)
   constexpr int SLOTS = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int sub = lane / G, sl = lane % G;
   const int64_t tile = ((int64_t)blockIdx.x * (kThreads / 32) + warp) * SLOTS + sub;
   const int64_t ntiles = (n + CH - 1) / CH;
   reduce_tile<K, G, C, MODE>(tb, keys, rows_in, n, tile, CH, tile < ntiles, D, lr, keys_out, rows_out,
-                             sub, sl, oa);
+                             sub, sl, oa, consumed);
 }
 
 // All remaining levels in ONE CTA: level i reads buffer (i&1), writes buffer ((i+1)&1).
 template <typename K, int G, int C, int MODE>
 __global__ void __launch_bounds__(kThreads)
 reduce_tail_kernel(const __grid_constant__ TableBatch tb, K *keys_a, float *rows_a, K *keys_b,
-                   float *rows_b, int64_t n, int CH, int D, float lr, const OptArgs *oa) {
+                   float *rows_b, int64_t n, int CH, int D, float lr, const OptArgs *oa, const uint32_t *flag,
+                   const uint8_t *consumed) {
+  if (*flag == 0) return;  // combine_kernel left no chain for the tree (the usual case)
   constexpr int SLOTS = 32 / G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int sub = lane / G, sl = lane % G;
@@ -528,13 +743,36 @@ reduce_tail_kernel(const __grid_constant__ TableBatch tb, K *keys_a, float *rows
     const int64_t ntiles = (n + CH - 1) / CH;
     for (int64_t base = 0; base < ntiles; base += nslots) {
       const int64_t tile = base + slot;
-      reduce_tile<K, G, C, MODE>(tb, kin, rin, n, tile, CH, tile < ntiles, D, lr, kout, rout, sub, sl, oa);
+      reduce_tile<K, G, C, MODE>(tb, kin, rin, n, tile, CH, tile < ntiles, D, lr, kout, rout, sub, sl, oa, consumed);
     }
     if (ntiles <= 1) break;
     __syncthreads();  // partial rows written by this CTA are visible to it after the barrier
+    consumed = nullptr;  // (the marks belong to the level-1 partials only)
     n = 2 * ntiles;
     K *tk = kin; kin = kout; kout = tk;
     float *tr = rin; rin = rout; rout = tr;
+  }
+}
+
+
+// ---- AVG / MEAN: the gradient of a bag's rows is output-grad / in_dim (embedding.cu:206-211) --------
+// One IEEE division per output-grad element, ONCE per bag, into scratch rows [B][D]; level 1 then adds
+// the quotients like plain sums.  Same bits as dividing per lookup (the quotient does not depend on the
+// lookup), 1/L of the divisions.  Descriptor reuse: t[].out = source (row stride `ogs`), t[].table =
+// destination (row stride D), t[].L = divisor.
+static __global__ void __launch_bounds__(256)
+prescale_kernel(const __grid_constant__ TableBatch tp, int64_t B, int D, int64_t ogs) {
+  const TableDesc &td = tp.t[blockIdx.y];
+  const int D4 = D >> 2;
+  const float Lf = (float)td.L;
+  const int64_t total = B * (int64_t)D4;
+  const uint64_t pol_keep = policy_evict_last(), pol_stream = policy_evict_first();
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
+    const int64_t b = i / D4;
+    const int c4 = (int)(i - b * D4);
+    float4 v = ldg_row_hint(td.out + b * ogs + 4 * c4, pol_stream);
+    v.x = __fdiv_rn(v.x, Lf); v.y = __fdiv_rn(v.y, Lf); v.z = __fdiv_rn(v.z, Lf); v.w = __fdiv_rn(v.w, Lf);
+    st_row_hint(td.table + b * (int64_t)D + 4 * c4, v, pol_keep);  // re-read L times by level 1
   }
 }
 
@@ -567,6 +805,7 @@ struct Carve {
   size_t cub_bytes;
   char *pkeys[2];
   float *prows[2];
+  uint16_t *consumed;   // marks of the level-1 partial slots (one byte each), behind the 32-bit "chains left" flag
   size_t total;
 };
 static Carve carve(char *base, int64_t n, int64_t total_rows, int64_t D) {
@@ -594,6 +833,8 @@ static Carve carve(char *base, int64_t n, int64_t total_rows, int64_t D) {
   c.prows[0] = (float *)take((size_t)s0 * D * 4);
   c.pkeys[1] = take((size_t)s1 * ksz);
   c.prows[1] = (float *)take((size_t)s1 * D * 4);
+  char *marks = take(16 + (size_t)s0);
+  c.consumed = marks ? (uint16_t *)(marks + 4) : nullptr;
   c.total = off;
   return c;
 }
@@ -697,7 +938,23 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
   K *keys_a = (K *)c.keys_a, *keys_b = (K *)c.keys_b;
   int max_l = 1;
   for (int t = 0; t < tb.num_tables; t++) max_l = tb.t[t].L > max_l ? tb.t[t].L : max_l;
-  if (stage != STAGE_APPLY) {
+  // small batches: every table's lookups sorted inside one CTA, keygen fused (FFEMB_OWN_SORT=0: the
+  // device-wide sort, A/B runs); empty slots (padded) need the device-wide order
+  bool seg = std::is_same<K, uint32_t>::value && !tb.padded && tuning().own_sort != 0 &&
+             B * (int64_t)max_l <= (int64_t)kSegThreads * kSegMaxItems;
+  for (int t = 0; t < tb.num_tables; t++) seg = seg && tb.t[t].R <= 0x7fffffffll;
+  if (seg) {
+    if constexpr (std::is_same<K, uint32_t>::value) if (stage != STAGE_APPLY) {
+      ProfScope prof(FFEMB_PHASE_SORT, 1, s);
+      const int64_t per = (B * max_l + kSegThreads - 1) / kSegThreads;
+      uint32_t *ko = (uint32_t *)keys_b;
+      cudaError_t e = per <= 2 ? launch_seg_sort<2>(tb, B, ko, c.vals_b, s)
+                    : per <= 4 ? launch_seg_sort<4>(tb, B, ko, c.vals_b, s)
+                    : per <= 8 ? launch_seg_sort<8>(tb, B, ko, c.vals_b, s)
+                               : launch_seg_sort<16>(tb, B, ko, c.vals_b, s);
+      if (e != cudaSuccess) return cuda_fail(e, "per-table sort launch");
+    }
+  } else if (stage != STAGE_APPLY) {
     ProfScope prof(FFEMB_PHASE_KEYGEN, 1, s);
     dim3 grid((unsigned)((B * max_l + kThreads - 1) / kThreads), tb.num_tables);
     keygen_kernel<K><<<grid, kThreads, 0, s>>>(tb, B, keys_a, c.vals_a);
@@ -705,7 +962,7 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
   int end_bit = 1;
   const uint64_t max_key = (uint64_t)total_rows - (tb.padded ? 0 : 1);  // (empty slots carry key = total_rows)
   while (end_bit < (int)sizeof(K) * 8 && (max_key >> end_bit) != 0) end_bit++;
-  if (stage != STAGE_APPLY) {
+  if (stage != STAGE_APPLY && !seg) {
     // onesweep: histogram + scan + one pass per 8 key bits
     ProfScope prof(FFEMB_PHASE_SORT, 2 + (end_bit + 7) / 8, s);
     size_t tmp = c.cub_bytes;
@@ -736,7 +993,7 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     if (tuning().r1_pipe >= 0) pipe = tuning().r1_pipe != 0;
     const size_t sm_sum = EPC * sizeof(EntryDesc), sm_avg = EPC * (sizeof(EntryDesc) + sizeof(float2));
     auto go = [&](auto kern, size_t sm) {
-      kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], flags, split, oa);
+      kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], flags, split, oa, c.consumed);
     };
     // D <= 128: the cp.async ring variant, 4 entries ahead (measured: cfg3 1.36 -> 1.22 ms against the
     // register double buffer; cfg5, whose gathers miss L2, 11.4 ms against 14.5 for the register-
@@ -750,7 +1007,7 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
       auto gor = [&](auto kern, int S) {
         const size_t sm = EPC * sizeof(EntryDesc) + (size_t)(T1 / 32) * S * 2 * 32 * 16;
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], split, oa);
+        kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], split, oa, c.consumed);
       };
       if constexpr (C == 1) {
         const bool avg = aggr != FFEMB_AGGR_SUM;
@@ -772,19 +1029,31 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
     // D = 128, 2048 at D = 16) finish in the single-CTA tail instead of paying another grid launch
     const int64_t small_level = (int64_t)kSmallLevel * SLOTS;
     for (int64_t mm = m; mm > small_level; mm = 2 * ((mm + CH2 - 1) / CH2)) ups++;
-    ProfScope prof(FFEMB_PHASE_REDUCE_UP, ups, s);
+    const bool fused = tuning().up_fused != 0;  // FFEMB_UP_FUSED=0: the tree alone (the round-1 form, A/B runs)
+    ProfScope prof(FFEMB_PHASE_REDUCE_UP, ups + (fused ? 1 : 0), s);
+    const uint32_t *flag = up_flag(c.consumed);
+    const uint8_t *marks = (const uint8_t *)c.consumed;
+    if (fused) {
+      // every chain of <= kMaxChain partials in one launch; the tree below then usually has nothing left
+      const int64_t want = (ntiles1 + 32 * (kThreads / 32) - 1) / (32 * (kThreads / 32));  // 32 tiles per warp and round
+      combine_kernel<K, G, C, MODE><<<(unsigned)(want < 148 * 8 ? want : 148 * 8), kThreads, 0, s>>>(
+          tb, pk0, c.prows[0], c.consumed, ntiles1, D, lr, oa);
+    } else {
+      cudaMemsetAsync((void *)flag, 1, 4, s);  // (non-zero: the tree runs unconditionally)
+    }
     int cur = 0;
     K *pk[2] = {pk0, pk1};
     while (m > small_level) {  // grid-wide levels while the partial array is large
       const int64_t tiles = (m + CH2 - 1) / CH2;
       reduce_level_kernel<K, G, C, MODE>
           <<<(unsigned)((tiles + slots_per_cta - 1) / slots_per_cta), kThreads, 0, s>>>(
-              tb, pk[cur], c.prows[cur], m, CH2, D, lr, pk[cur ^ 1], c.prows[cur ^ 1], oa);
+              tb, pk[cur], c.prows[cur], m, CH2, D, lr, pk[cur ^ 1], c.prows[cur ^ 1], oa, flag, cur == 0 && m == 2 * ntiles1 ? marks : nullptr);
+      marks = nullptr;
       m = 2 * tiles;
       cur ^= 1;
     }
     reduce_tail_kernel<K, G, C, MODE><<<1, kThreads, 0, s>>>(tb, pk[cur], c.prows[cur], pk[cur ^ 1],
-                                                            c.prows[cur ^ 1], m, CH2, D, lr, oa);
+                                                            c.prows[cur ^ 1], m, CH2, D, lr, oa, flag, marks);
   }
   return cuda_fail(cudaGetLastError(), "sorted backward launch");
 }
@@ -908,6 +1177,39 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
   tb.row_base[tb.num_tables] = rows_l;
   const int64_t rows = (int64_t)rows_l;
   const Carve c = carve((char *)ws, (int64_t)n, rows > 0 ? rows : 1, D);
+  int aggr_l1 = aggr;
+  // AVG / MEAN with room in the workspace (ffemb_backward_workspace_avg): divide once per bag up front
+  // and let the segmented sum run as a plain sum (FFEMB_PRESCALE=0: divide in the walk, A/B runs)
+  if (aggr != FFEMB_AGGR_SUM && stage != STAGE_SORT && n > 0 && tuning().prescale != 0) {
+    const bool all = tb.og_stride != D;  // (one row stride per call: a strided source moves every table)
+    TableBatch tp;
+    memset(&tp, 0, sizeof(tp));
+    size_t extra = 0;
+    for (int t = 0; t < tb.num_tables; t++) {
+      if (tb.t[t].L >= 2 || all) {
+        tp.t[tp.num_tables] = tb.t[t];
+        tp.t[tp.num_tables].lookup_base = (uint32_t)t;
+        tp.num_tables++;
+        extra += prescale_bytes(B, D);
+      }
+    }
+    if (tp.num_tables > 0 && ws_bytes >= need + extra) {
+      char *dst = (char *)ws + need;
+      for (int k = 0; k < tp.num_tables; k++) {
+        tp.t[k].table = (float *)dst;
+        tb.t[tp.t[k].lookup_base].out = (float *)dst;
+        dst += prescale_bytes(B, D);
+      }
+      {
+        ProfScope prof(FFEMB_PHASE_PRESCALE, 1, s);
+        const int64_t want = (B * (D / 4) + 255) / 256;
+        dim3 grid((unsigned)(want < 148 * 8 ? want : 148 * 8), tp.num_tables);
+        prescale_kernel<<<grid, 256, 0, s>>>(tp, B, (int)D, tb.og_stride);
+      }
+      tb.og_stride = D;
+      aggr_l1 = FFEMB_AGGR_SUM;  // (for the sorted tables only: the bag-major kernels keep the call's aggr)
+    }
+  }
   // The bag-major kernels of the small tables are shared-memory-bound and touch neither the sort
   // buffers nor the sorted tables: when there is sorted work too they are forked onto a side stream
   // (per host thread and device) and run UNDER the radix sort / the segmented sum instead of in front
@@ -948,17 +1250,17 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
       OptArgs *oa = (OptArgs *)((char *)ws + c.total + small_partials_bound(D));
       cudaError_t e = cudaMemcpyAsync(oa, &o, sizeof(o), cudaMemcpyHostToDevice, s);
       if (e != cudaSuccess) return cuda_fail(e, "optimizer arguments upload");
-      rc = wide_keys(rows) ? dispatch_wide(tb, (int)D, B, aggr, o.lr, n, rows, c, s, stage, (int64_t)n_stream, oa, APPLY_SGDX)
-                           : dispatch_g<uint32_t, APPLY_SGDX>(tb, (int)D, B, aggr, o.lr, n, rows, c, s, stage, (int64_t)n_stream, oa);
+      rc = wide_keys(rows) ? dispatch_wide(tb, (int)D, B, aggr_l1, o.lr, n, rows, c, s, stage, (int64_t)n_stream, oa, APPLY_SGDX)
+                           : dispatch_g<uint32_t, APPLY_SGDX>(tb, (int)D, B, aggr_l1, o.lr, n, rows, c, s, stage, (int64_t)n_stream, oa);
     }
     if (rc) return rc;
     return launch_sgdx_untouched(tb, (int)D, o, s);
   }
   if (n == 0) return FFEMB_OK;
   if (wide_keys(rows))
-    return dispatch_wide(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream, nullptr, (int)mode);
-  return mode == APPLY_SGD ? dispatch_g<uint32_t, APPLY_SGD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream, nullptr)
-                           : dispatch_g<uint32_t, APPLY_GRAD>(tb, (int)D, B, aggr, lr, n, rows, c, s, stage, (int64_t)n_stream, nullptr);
+    return dispatch_wide(tb, (int)D, B, aggr_l1, lr, n, rows, c, s, stage, (int64_t)n_stream, nullptr, (int)mode);
+  return mode == APPLY_SGD ? dispatch_g<uint32_t, APPLY_SGD>(tb, (int)D, B, aggr_l1, lr, n, rows, c, s, stage, (int64_t)n_stream, nullptr)
+                           : dispatch_g<uint32_t, APPLY_GRAD>(tb, (int)D, B, aggr_l1, lr, n, rows, c, s, stage, (int64_t)n_stream, nullptr);
 }
 
 // ---- the atomic comparison: reference-equivalent unordered scatter ---------------------------

@@ -37,6 +37,8 @@ static constexpr int kSmallThreads = 512, kSmallCtas = 148 * 2, kChunkBags = 16;
 // 0 = sorted path, 1 = tiny (register accumulators), 2 = small (shared-memory accumulator)
 int backward_path(int64_t R, int64_t L, int64_t D, int64_t B) {
   if (tuning().small == 0) return 0;  // tuning aid: FFEMB_SMALL=0 forces the sorted path
+  // (D = 16 was tried for the tiny path in round 2: its kernels cost cfg2 0.11 ms where the sorted path's
+  // share was 0.03 — too little work per bag for a chunk-staged kernel)
   if (D % 4 != 0 || D < 32 || D > 128 || L < 1 || L > kSmallMaxBag || R < 1) return 0;
   const int64_t n = B * L;
   if (n < 16384 || n < 16 * R) return 0;  // little duplication / little work: sorting is fine

@@ -64,7 +64,7 @@ int cuda_fail(cudaError_t e, const char *what);
 struct Tuning {
   long long stream_mb, l1_kb;
   int fwd_perm, fwd_avg_div, fwd_target, r1_mix, r1_flags, r1_pipe, r1_ring, small, small_fork,
-      up_fused, hot, slab_mb, own_sort, xpush;
+      up_fused, hot, slab_mb, own_sort, xpush, prescale;
 };
 const Tuning &tuning();
 
@@ -169,6 +169,8 @@ int launch_backward_sorted(const TableBatch &tb, int64_t D, int64_t B, int aggr,
 int launch_load_sparse(const ffemb_table_t *tables, int num_tables, const int64_t *full, int64_t row_len,
                        const int32_t *sample_ids, int64_t first_sample, int64_t B, cudaStream_t s);
 size_t backward_workspace_bytes(int64_t num_lookups, int64_t total_rows, int64_t D);
+// scratch of one table's pre-scaled output-grad (AVG / MEAN backward), 256-byte granules
+static inline size_t prescale_bytes(int64_t B, int64_t D) { return ((size_t)B * (size_t)D * 4 + 255) & ~(size_t)255; }
 // tables whose whole gradient fits on chip (ffemb_backward_small.cu)
 int backward_path(int64_t R, int64_t L, int64_t D, int64_t B);  // 0 sorted, 1 tiny, 2 small
 size_t small_partials_bound(int64_t D);

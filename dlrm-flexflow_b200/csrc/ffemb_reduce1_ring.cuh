@@ -30,7 +30,7 @@ template <typename K, int G, int MODE, bool AVG, int S>
 __global__ void __launch_bounds__(L1Threads<G>::value)
 reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
                     const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
-                    float *rows_out, uint32_t split, const OptArgs *oa) {
+                    float *rows_out, uint32_t split, const OptArgs *oa, uint16_t *consumed) {
   constexpr int THREADS = L1Threads<G>::value;
   constexpr int CH1 = Ch1<G>::value;
   constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
@@ -42,6 +42,7 @@ reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__
   // (conflict-free); a lane only ever reads back what it copied itself
   float4 *ring = reinterpret_cast<float4 *>(smem_raw + sizeof(EntryDesc) * WARPS * EPW) +
                  (size_t)warp * S * 2 * 32 + lane;
+  if (blockIdx.x == 0 && threadIdx.x == 0) up_flag(consumed)[0] = 0;  // "chains left for the tree": set by combine_kernel
   const int64_t wbase = ((int64_t)mix_cta(blockIdx.x, gridDim.x, split) * WARPS + warp) * EPW;
   if (wbase >= n) return;  // warp-uniform
   const int D4 = D >> 2;
@@ -71,6 +72,7 @@ reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__
   const int64_t tile = wbase / CH1 + sub;
   const int64_t t0 = tile * CH1;
   if (t0 >= n) return;
+  if (sl == 0) consumed[tile] = 0;  // (both partial slots of the tile: not yet taken by combine_kernel)
   const bool own = sl < D4;
   const EntryDesc *dq = wd + sub * CH1;
   int cnt = (int)min((int64_t)CH1, n - t0);

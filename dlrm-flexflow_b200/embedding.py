@@ -179,7 +179,10 @@ class EmbeddingCollection:
             for s, e in self._chunks():
                 n = batch * sum(self.bags[s:e])
                 rows = sum(int(w.shape[0]) for w in self.weights[s:e])
-                need = lib().ffemb_backward_workspace(int(n), int(rows), self.dim)
+                if self.aggr != AGGR_MODE_SUM:   # room for the once-per-bag quotients of the AVG backward
+                    need = lib().ffemb_backward_workspace_avg(int(n), int(rows), self.dim, int(batch), e - s)
+                else:
+                    need = lib().ffemb_backward_workspace(int(n), int(rows), self.dim)
                 self._ws.append(torch.empty(max(need, 256), dtype=torch.uint8, device=self.device))
         return self._ws
 

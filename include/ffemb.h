@@ -333,6 +333,16 @@ FFEMB_API int ffemb_backward_sgd_concat(const ffemb_table_t *tables, int num_tab
  * tables holding `total_rows` = sum_t R_t rows of D floats.  0 on invalid arguments.         */
 FFEMB_API size_t ffemb_backward_workspace(int64_t num_lookups, int64_t total_rows, int64_t D);
 
+/* The same plus room for the AVG / MEAN backward's pre-scaled output-grads.  embed_backward divides the
+ * output-grad by in_dim for EVERY lookup (src/ops/embedding.cu:206-211: gradient = output_grad[i] /
+ * in_dim inside the per-element thread, re-done for each of the bag's rows); the quotient only depends
+ * on the bag, so with this much scratch the sorted backward divides ONCE per bag (IEEE division, the
+ * same bits) into the workspace and the segmented sum adds the quotients — the per-lookup division was
+ * 42 % of the segmented sum at bag width 64.  A workspace sized by ffemb_backward_workspace still
+ * works: the division then stays in the walk.  B = batch, num_tables = tables of the call.      */
+FFEMB_API size_t ffemb_backward_workspace_avg(int64_t num_lookups, int64_t total_rows, int64_t D, int64_t B,
+                                    int num_tables);
+
 /* Which backward algorithm a table of R rows, bag width L takes at batch B (informational; the
  * accounting in bench.py uses it): 0 = radix sort + segmented sum, 1 = "tiny" (R <= 16, register
  * accumulators), 2 = "small" (whole [R][D] gradient in shared memory).  All are deterministic.  */
@@ -380,7 +390,8 @@ FFEMB_API int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int6
 #define FFEMB_PHASE_INPUT 8     /* sparse-input delivery (ffemb_load_sparse_inputs) */
 #define FFEMB_PHASE_DENSE 9     /* general SGD: the pass over the rows a step did not touch */
 #define FFEMB_PHASE_SYNC 10     /* cross-rank flag kernels (ffemb_sync_signal / ffemb_sync_wait) */
-#define FFEMB_NUM_PHASES 11
+#define FFEMB_PHASE_PRESCALE 11 /* AVG / MEAN backward: output-grad / in_dim, once per bag, ahead of the segmented sum */
+#define FFEMB_NUM_PHASES 12
 FFEMB_API int ffemb_profile_enable(int on);
 FFEMB_API int ffemb_profile_collect(float *ms_per_phase, int64_t *launches_per_phase);
 FFEMB_API int64_t ffemb_launch_count(void);

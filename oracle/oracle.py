@@ -384,5 +384,9 @@ def dropin_gpu():
         L = _bind_gpu(C.CDLL(os.path.join(HERE, "_ref", "libffdropin_gpu.so")))
         L.ffdropin_gpu_backward_sgd_task.argtypes = [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _int, _f32]
         L.ffdropin_gpu_backward_sgd_task.restype = None
+        pp = C.POINTER(C.c_void_p)
+        L.ffdropin_gpu_group_task.argtypes = [_int, _int, pp, pp, pp, C.POINTER(C.c_int64), _i64, _i64,
+                                              C.POINTER(C.c_int64), _int, _f32, _int]
+        L.ffdropin_gpu_group_task.restype = None
         _dropin_gpu = L
     return _dropin_gpu

@@ -126,6 +126,14 @@ EmbeddingMeta *make_meta(int aggr) {
 void ffemb_embedding_backward_sgd_task(const Legion::Task *task,
                                        const std::vector<Legion::PhysicalRegion> &regions,
                                        Legion::Context ctx, Legion::Runtime *runtime);
+/* the per-GPU batched leaf bodies of dlrm-flexflow_b200/csrc/flexflow/embedding_group_ffemb.cu */
+struct FFEmbGroupArgs { int num_tables; float lr; int prepared; int parity; };
+void ffemb_embedding_group_forward_task(const Legion::Task *, const std::vector<Legion::PhysicalRegion> &,
+                                        Legion::Context, Legion::Runtime *);
+void ffemb_embedding_group_prepare_task(const Legion::Task *, const std::vector<Legion::PhysicalRegion> &,
+                                        Legion::Context, Legion::Runtime *);
+void ffemb_embedding_group_backward_sgd_task(const Legion::Task *, const std::vector<Legion::PhysicalRegion> &,
+                                             Legion::Context, Legion::Runtime *);
 #endif
 
 extern "C" {
@@ -152,6 +160,32 @@ void ffdropin_gpu_backward_sgd_task(const int64_t *idx, const float *outgrad, fl
   f.task.args = &lr;
   f.task.arglen = sizeof(lr);
   ffemb_embedding_backward_sgd_task(&f.task, f.regions, NULL, &f.runtime);
+  delete m;
+}
+#endif
+
+#ifdef FFEMB_DROPIN
+/* The per-GPU batched leaf tasks behind the frames Legion would hand them: one task, the regions of
+ * `n` tables listed back to back.  what: 0 forward (idx, out, W), 1 prepare (idx, W), 2 backward + SGD
+ * (idx, outgrad, W RW; prepared = the prepare task ran before).                                   */
+void ffdropin_gpu_group_task(int what, int n, const int64_t *const *idx, float *const *out, float *const *W,
+                             const int64_t *L, int64_t D, int64_t B, const int64_t *R, int aggr, float lr,
+                             int prepared) {
+  TaskFrame f;
+  for (int t = 0; t < n; t++) {
+    f.add((void *)idx[t], L[t], B);
+    if (what != 1) f.add((void *)out[t], D, B);
+    f.add((void *)W[t], R[t], D);
+  }
+  EmbeddingMeta *m = make_meta(aggr);
+  f.task.local_args = &m;
+  f.task.local_arglen = sizeof(m);
+  FFEmbGroupArgs a = {n, lr, prepared, 0};
+  f.task.args = &a;
+  f.task.arglen = sizeof(a);
+  if (what == 0) ffemb_embedding_group_forward_task(&f.task, f.regions, NULL, &f.runtime);
+  else if (what == 1) ffemb_embedding_group_prepare_task(&f.task, f.regions, NULL, &f.runtime);
+  else ffemb_embedding_group_backward_sgd_task(&f.task, f.regions, NULL, &f.runtime);
   delete m;
 }
 #endif

@@ -542,6 +542,57 @@ def test_dropin_task_bodies_match_reference_task_bodies(oracle, torch_cuda, R, D
         assert np.all(np.abs(a - b) <= 2 * table_tol(W) * np.maximum(1, np.sqrt(cnt))[:, None])
 
 
+@pytest.mark.skipif(not _have_dropin(), reason="oracle/_ref not built (needs /root/reference at build time)")
+@pytest.mark.parametrize("aggr", [21, 22])
+@pytest.mark.parametrize("prepared", [0, 1])
+def test_dropin_group_leaf_tasks_match_reference_per_table_tasks(oracle, torch_cuda, aggr, prepared):
+    """The per-GPU batched leaf tasks of csrc/flexflow/embedding_group_ffemb.cu (ONE Legion task listing
+    the regions of all tables of a GPU: forward; index sort; backward + SGD on the tables themselves)
+    driven through the (Task, PhysicalRegion) frames and the reference's own TensorAccessor objects,
+    against the reference's per-table tasks run one by one: forward_task (bit-exact), then
+    ZeroInitializer -> backward_task -> SGDOptimizer::ps_update_task per table."""
+    import ctypes as C
+    torch = torch_cuda
+    ref, ours = oracle.ref_gpu(), oracle.dropin_gpu()
+    shapes = [(1000, 1), (50000, 7), (7, 20), (300, 5), (120, 12)]   # sorted, tiny and small paths in one group
+    D, B = 128, 2049
+    Ws, idxs, gs = [], [], []
+    for i, (R, L) in enumerate(shapes):
+        W, idx, g = make_inputs(R, D, L, B, seed=31 * i + R)
+        Ws.append(W); idxs.append(idx); gs.append(g)
+    n = len(shapes)
+    d_idx = [dev(torch, x) for x in idxs]
+    d_g = [dev(torch, x) for x in gs]
+    d_W = [dev(torch, x) for x in Ws]
+    d_out = [torch.full((B, D), float("nan"), device="cuda") for _ in shapes]
+    ws = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    ours.ffref_gpu_set_workspace(ws.data_ptr(), ws.numel())
+    arr = lambda ts: (C.c_void_p * n)(*[t.data_ptr() for t in ts])
+    Ls = (C.c_int64 * n)(*[l for _, l in shapes])
+    Rs = (C.c_int64 * n)(*[r for r, _ in shapes])
+    ours.ffdropin_gpu_group_task(0, n, arr(d_idx), arr(d_out), arr(d_W), Ls, D, B, Rs, aggr, 0.0, 0)
+    torch.cuda.synchronize()
+    for i, (R, L) in enumerate(shapes):
+        want = torch.full((B, D), float("nan"), device="cuda")
+        ref.ffref_gpu_forward_task(d_idx[i].data_ptr(), want.data_ptr(), d_W[i].data_ptr(), L, D, B, R, aggr)
+        torch.cuda.synchronize()
+        assert torch.equal(d_out[i], want), ("group forward", i)
+    if prepared:
+        ours.ffdropin_gpu_group_task(1, n, arr(d_idx), arr(d_out), arr(d_W), Ls, D, B, Rs, aggr, 0.0, 0)
+    ours.ffdropin_gpu_group_task(2, n, arr(d_idx), arr(d_g), arr(d_W), Ls, D, B, Rs, aggr, 0.01, prepared)
+    torch.cuda.synchronize()
+    for i, (R, L) in enumerate(shapes):
+        G = torch.zeros((R, D), device="cuda")  # Op::zero_grad
+        ref.ffref_gpu_backward_task(d_idx[i].data_ptr(), d_g[i].data_ptr(), G.data_ptr(), L, D, B, R, aggr)
+        Wref = dev(torch, Ws[i])
+        ref.ffref_gpu_sgd_task(G.data_ptr(), Wref.data_ptr(), R, D, 0.01, 0.0)
+        torch.cuda.synchronize()
+        a, b = d_W[i].cpu().numpy(), Wref.cpu().numpy()
+        cnt = np.bincount(idxs[i].reshape(-1), minlength=R)
+        assert np.array_equal(a[cnt <= 1], b[cnt <= 1]), ("group backward: single-lookup / untouched rows", i)
+        assert np.all(np.abs(a - b) <= 2 * table_tol(Ws[i]) * np.maximum(1, np.sqrt(cnt))[:, None]), ("group backward", i)
+
+
 # ---------------------------------------------------------------------------------------------
 # sparse-input delivery (SURVEY 8f-2): DataLoader::load_sparse_input, all tables in one launch
 # ---------------------------------------------------------------------------------------------
@@ -902,3 +953,46 @@ def test_rowwise_route_and_padded_backward_emulated_ranks(ffemb, oracle, torch_c
         want = oracle.reference_step(idx[t], dx[:, t * D:(t + 1) * D].copy(), Ws[t].copy(), aggr, lr)
         tol = table_tol(Ws[t]) * np.sqrt(np.maximum(cnt, 1))[:, None] * 2
         assert np.all(np.abs(new[t].astype(np.float64) - want) <= tol), (t, "updated table")
+
+
+@pytest.mark.parametrize("aggr", [22, 122])
+@pytest.mark.parametrize("D", [16, 128, 256])
+def test_avg_backward_division_once_per_bag_equals_division_per_lookup(ffemb, oracle, torch_cuda, aggr, D):
+    """AGGR_MODE_AVG backward: gradient = output_grad / in_dim (embedding.cu:206-211).  With a workspace
+    sized by ffemb_backward_workspace_avg the sorted backward divides once per bag into scratch and sums
+    the quotients; with the plain workspace it divides inside the walk.  Same IEEE quotients, same order
+    of adds: the updated tables must be bit-identical — denormal, huge and zero gradients included."""
+    import ctypes as C
+    torch = torch_cuda
+    rows, bags, B = [5000, 70000, 900], [9, 1, 20], 3001
+    T = len(rows)
+    rng = np.random.default_rng(D + aggr)
+    Ws = [rng.uniform(-0.5, 0.5, (r, D)).astype(np.float32) for r in rows]
+    idx = [rng.integers(0, r, (B, l), dtype=np.int64) for r, l in zip(rows, bags)]
+    gs = [rng.uniform(-1, 1, (B, D)).astype(np.float32) for _ in rows]
+    gs[0][::7] *= 1e-39   # denormal quotients
+    gs[0][3::11] *= 1e37  # huge
+    gs[2][5] = 0.0
+    n, total = sum(B * l for l in bags), sum(rows)
+    L_ = ffemb.lib()
+    small = L_.ffemb_backward_workspace(n, total, D)
+    big = L_.ffemb_backward_workspace_avg(n, total, D, B, T)
+    assert big >= small + T * B * D * 4
+    d_idx, d_g = [dev(torch, x) for x in idx], [dev(torch, x) for x in gs]
+    res = []
+    for nbytes in (small, big):
+        dW = [dev(torch, w) for w in Ws]
+        ws = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+        arr = (ffemb.binding.ffemb_table_t * T)()
+        for t in range(T):
+            arr[t].idx, arr[t].out, arr[t].table = d_idx[t].data_ptr(), d_g[t].data_ptr(), dW[t].data_ptr()
+            arr[t].R, arr[t].L = rows[t], bags[t]
+        ffemb.binding.check(L_.ffemb_backward_sgd_batched(arr, T, D, B, aggr, 0.01, ws.data_ptr(), nbytes, None))
+        torch.cuda.synchronize()
+        res.append([w.cpu().numpy() for w in dW])
+    for t in range(T):
+        assert np.array_equal(res[0][t].view(np.uint32), res[1][t].view(np.uint32)), t
+        if aggr == 22:
+            want = oracle.reference_step(idx[t], gs[t].copy(), Ws[t].copy(), aggr, 0.01)
+            cnt = np.bincount(idx[t].reshape(-1), minlength=rows[t])
+            assert np.array_equal(res[1][t][cnt <= 1], want[cnt <= 1]), (t, "single-lookup rows vs the reference step")
