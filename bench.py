@@ -52,8 +52,10 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--placement", default="balanced", choices=["modulo", "balanced"],
                     help="N>1: modulo = the reference's t %% G; balanced = greedy by measured per-lookup cost")
-    ap.add_argument("--groups", type=int, default=2,
-                    help="N>1, fused exchange: pipeline groups per rank (1 = forward(all), push(all), backward(all))")
+    ap.add_argument("--groups", type=int, default=0,
+                    help="N>1, fused exchange: pipeline groups per rank (1 = forward(all), push(all), backward(all)); "
+                         "0 = auto: 2 up to 4 GPUs, 1 beyond (measured, profiles/r2_scaling.md: at 8 GPUs a rank's "
+                         "share is launch-latency-bound and a second group only doubles the launches)")
     ap.add_argument("--trace", action="store_true",
                     help="N>1: after the timed region, one more step with CUDA events around every piece of the "
                          "pipelined schedule; per-rank timelines go to stderr (tuning aid)")
@@ -285,6 +287,8 @@ def main():
     # shard plan: whole tables by t % N (the reference's generator) or by cost, heavy tables split by
     # columns, this rank's parts dealt into pipeline groups (sharding.plan_shards); the NCCL comparison
     # form moves whole tables only
+    if args.groups <= 0:
+        args.groups = 2 if world <= 4 else 1
     fused = world > 1 and args.exchange == "fused"
     plan = pkg.sharding.plan_shards(wl.rows, wl.bags, wl.dim, world, args.placement,
                                     split=fused and not args.no_split, groups=args.groups if fused else 1)

@@ -51,6 +51,7 @@ const Tuning &tuning() {
     x.own_sort = (int)num("FFEMB_OWN_SORT");
     x.xpush = (int)num("FFEMB_XPUSH");
     x.prescale = (int)num("FFEMB_PRESCALE");
+    x.fwd_bulk = (int)num("FFEMB_FWD_BULK");
     return x;
   }();
   return t;

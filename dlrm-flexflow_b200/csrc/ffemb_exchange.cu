@@ -108,41 +108,6 @@ struct PushArgs {
   int64_t n, stride;  // samples, floats between consecutive rows of dx
 };
 
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n .reg .pred P;\n mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n selp.b32 %0, 1, 0, P;\n}"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void bulk_g2s(void *smem, const void *gmem, uint32_t bytes, uint64_t *bar) {
-  asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                   smem_u32(smem)),
-               "l"(gmem), "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
-}
-__device__ __forceinline__ void bulk_s2g(void *gmem, const void *smem, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem), "r"(smem_u32(smem)),
-               "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void bulk_wait_read() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-template <int N> __device__ __forceinline__ void bulk_wait() {
-  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
-}
-
 // Work item i -> (row block i / nparts, part i % nparts): every wave of CTAs writes to all parts, i.e.
 // to all destination GPUs at once.  One warp per CTA; lane r fetches row r of the tile, lane 0 owns the
 // barriers and issues the single contiguous store of the tile.
@@ -213,7 +178,7 @@ __global__ void __launch_bounds__(32) push_bulk_kernel(const __grid_constant__ P
 }
 
 int launch_push_bulk(const TableBatch &tb, const int32_t *widths, const float *dx, int64_t n, int64_t first,
-                     int64_t stride, cudaStream_t s) {
+                     int64_t stride, cudaStream_t s, int warps_per_sm) {
   PushArgs a;
   memset(&a, 0, sizeof(a));
   a.nparts = tb.num_tables;
@@ -235,8 +200,12 @@ int launch_push_bulk(const TableBatch &tb, const int32_t *widths, const float *d
   }
   a.max_tiles = (int32_t)max_tiles;
   const int64_t items = max_tiles * tb.num_tables;
-  int ctas_per_sm = 4;
-  if (tuning().xpush > 1) ctas_per_sm = tuning().xpush;  // tuning aid: CTAs (= warps) per SM
+  // resident CTAs (= warps) per SM.  Measured at N = 2 (profiles/r2_scaling.md): the push alone moves
+  // 218 MB in 0.56 / 0.48 / 0.42 / 0.37 ms with 2 / 4 / 8 / 16, but UNDER the neighbouring group's
+  // gather-pool / segmented-sum kernels the step is fastest with 2 (1.754 vs 1.841 / 1.926 / 1.926 ms):
+  // a caller that overlaps the push asks for few warps, one that runs it alone for many.
+  int ctas_per_sm = warps_per_sm > 0 ? (warps_per_sm > 16 ? 16 : warps_per_sm) : 4;
+  if (tuning().xpush > 1) ctas_per_sm = tuning().xpush;  // tuning aid
   const int64_t cap = 148ll * ctas_per_sm;
   const unsigned grid = (unsigned)(items < cap ? items : cap);
   const size_t sm = (size_t)kPushStages * kPushTileBytes + kPushStages * sizeof(uint64_t);
@@ -301,7 +270,9 @@ int ffemb_exchange_backward_parts(const ffemb_table_t *parts, int num_parts, con
     widths[p] = w;
     bulk = bulk && w % 4 == 0 && w * 4 <= 8192 && parts[p].reserved % 4 == 0 && (uintptr_t)parts[p].out % 16 == 0;
   }
-  if (bulk) return launch_push_bulk(tb, widths, dx, n_samples, first_sample, row_stride, (cudaStream_t)stream);
+  if (bulk)
+    return launch_push_bulk(tb, widths, dx, n_samples, first_sample, row_stride, (cudaStream_t)stream,
+                            parts[0].R > 0 && parts[0].R <= 64 ? (int)parts[0].R : 0);
   // fallback / comparison (FFEMB_XPUSH=0): the load-store kernel, one launch per run of equal widths
   for (int p0 = 0; p0 < num_parts;) {
     int p1 = p0;

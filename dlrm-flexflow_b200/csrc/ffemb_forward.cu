@@ -411,6 +411,94 @@ static void launch_vec(const TableBatch &tb_in, int D, int64_t B, int ag, const 
   else launch_vec2<G, C, false>(tb, D, B, ag, target, ctas, om, s);
 }
 
+
+// ---- the measured comparison: rows gathered with TMA bulk copies (FFEMB_FWD_BULK=S) ----------------
+// north_star: "TMA tile-gather where ncu shows it wins".  A gathered row is one contiguous piece of
+// 4*D bytes at a data-dependent address — no tile, nothing to multicast — so the TMA form of this
+// gather is ONE cp.async.bulk per row (instead of D/4 16-byte LDGs), issued by lane 0 of the warp
+// that owns the bag into a ring of S stages per warp in shared memory, completion counted on one
+// mbarrier per stage; every lane then adds its 16-byte fragment from shared memory.  Adds stay
+// sequential in j: bit-identical to fwd_kernel.  SUM, D <= 128, plain output only — it exists to be
+// measured against fwd_kernel (profiles/r2_tma_ab.md), which stays the product path.
+static constexpr int kBulkWarps = 16;
+template <int S>
+__global__ void __launch_bounds__(kBulkWarps * 32)
+fwd_bulk_kernel(const __grid_constant__ TableBatch tb, int D, int64_t B, int target) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float *ring = reinterpret_cast<float *>(smem_raw) + (size_t)warp * S * D;
+  uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + (size_t)kBulkWarps * S * D * 4) + warp * S;
+  if (lane == 0) {
+    for (int s = 0; s < S; s++) mbar_init(bar + s, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncwarp();
+  int t = 0;
+  while (t + 1 < tb.num_tables && blockIdx.x >= tb.cta_base[t + 1]) t++;
+  const TableDesc &td = tb.t[t];
+  const int L = td.L;
+  const int bpw = fwd_bags_per_slot(L, target);
+  const int64_t b0 = ((int64_t)(blockIdx.x - tb.cta_base[t]) * kBulkWarps + warp) * bpw;
+  const int nb = (int)min((int64_t)bpw, B - b0);
+  if (nb <= 0) return;
+  const int64_t *ip = td.idx + b0 * (int64_t)L;
+  const int n = nb * L;
+  const uint32_t rowbytes = (uint32_t)D * 4u;
+  const bool own = lane < (D >> 2);
+  auto issue = [&](int e) {
+    if (e < n && lane == 0) {
+      const int st = e % S;
+      const int64_t r = __ldg(ip + e);
+      mbar_expect_tx(bar + st, rowbytes);
+      bulk_g2s(ring + (size_t)st * D, td.table + r * (int64_t)D, rowbytes, bar + st);
+    }
+  };
+#pragma unroll
+  for (int e = 0; e < S - 1; e++) issue(e);
+  uint32_t phases = 0;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  int j = 0;
+  int64_t bag = b0;
+  if (L == 0) {
+    for (int i = 0; i < nb; i++)
+      if (own) st_stream(td.out + (b0 + i) * (int64_t)D + 4 * lane, acc);
+    return;
+  }
+  for (int e = 0; e < n; e++) {
+    issue(e + S - 1);  // its stage was read by every lane before the __syncwarp that ended iteration e - 1
+    const int st = e % S;
+    while (!mbar_try_wait(bar + st, (phases >> st) & 1u)) {}
+    phases ^= 1u << st;
+    if (own) f4_add(acc, *reinterpret_cast<const float4 *>(ring + (size_t)st * D + 4 * lane));
+    if (++j == L) {
+      if (own) st_stream(td.out + bag * (int64_t)D + 4 * lane, acc);
+      acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      j = 0;
+      bag++;
+    }
+    __syncwarp();
+  }
+}
+
+template <int S>
+static int launch_forward_bulk(const TableBatch &tb_in, int D, int64_t B, cudaStream_t s) {
+  TableBatch tb = tb_in;
+  const int target = 128;
+  uint32_t ctas = 0;
+  for (int t = 0; t < tb.num_tables; t++) {
+    tb.cta_base[t] = ctas;
+    const int64_t per_cta = (int64_t)fwd_bags_per_slot(tb.t[t].L, target) * kBulkWarps;
+    ctas += (uint32_t)((B + per_cta - 1) / per_cta);
+  }
+  tb.cta_base[tb.num_tables] = ctas;
+  const size_t sm = (size_t)kBulkWarps * S * D * 4 + (size_t)kBulkWarps * S * sizeof(uint64_t);
+  cudaError_t e = cudaFuncSetAttribute(fwd_bulk_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+  if (e != cudaSuccess) return cuda_fail(e, "bulk forward smem opt-in");
+  fwd_bulk_kernel<S><<<ctas, kBulkWarps * 32, sm, s>>>(tb, D, B, target);
+  return cuda_fail(cudaGetLastError(), "bulk forward launch");
+}
+
 int launch_forward(const TableBatch &tb, int64_t D64, int64_t B, int aggr, const OutMap &om, cudaStream_t s) {
   const int D = (int)D64;
   const int ag = aggr == FFEMB_AGGR_SUM ? AG_SUM : (aggr == FFEMB_AGGR_AVG ? AG_AVG : AG_MEAN);
@@ -424,6 +512,12 @@ int launch_forward(const TableBatch &tb, int64_t D64, int64_t B, int aggr, const
     vec = vec && om.stride % 4 == 0;
     for (int h = 0; h < om.npeers; h++) vec = vec && (uintptr_t)om.peer[h] % 16 == 0;
     for (int t = 0; t < tb.num_tables; t++) vec = vec && tb.t[t].lookup_base % 4 == 0;
+  }
+  if (vec && tuning().fwd_bulk > 0 && om.npeers == 0 && ag == AG_SUM && D <= 128) {
+    // FFEMB_FWD_BULK=4|8|16: the TMA bulk-copy row gather, measured against fwd_kernel (A/B runs only)
+    if (tuning().fwd_bulk >= 16) return launch_forward_bulk<16>(tb, D, B, s);
+    if (tuning().fwd_bulk >= 8) return launch_forward_bulk<8>(tb, D, B, s);
+    return launch_forward_bulk<4>(tb, D, B, s);
   }
   if (!vec) {
     dim3 grid((unsigned)((B + kThreads / 32 - 1) / (kThreads / 32)), tb.num_tables);

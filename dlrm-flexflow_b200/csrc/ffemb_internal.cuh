@@ -64,7 +64,7 @@ int cuda_fail(cudaError_t e, const char *what);
 struct Tuning {
   long long stream_mb, l1_kb;
   int fwd_perm, fwd_avg_div, fwd_target, r1_mix, r1_flags, r1_pipe, r1_ring, small, small_fork,
-      up_fused, hot, slab_mb, own_sort, xpush, prescale;
+      up_fused, hot, slab_mb, own_sort, xpush, prescale, fwd_bulk;
 };
 const Tuning &tuning();
 
@@ -88,7 +88,7 @@ int launch_exchange_backward(const TableBatch &tb, int64_t D, const float *dx, i
                              int64_t stride, cudaStream_t s);
 // push of parts of mixed width with bulk copies (ffemb_exchange.cu); tb.t[p].lookup_base = column offset
 int launch_push_bulk(const TableBatch &tb, const int32_t *widths, const float *dx, int64_t n, int64_t first,
-                     int64_t stride, cudaStream_t s);
+                     int64_t stride, cudaStream_t s, int warps_per_sm = 0);
 int launch_backward_atomic(const TableBatch &tb, int64_t D, int64_t B, int aggr, cudaStream_t s);
 enum ApplyMode { APPLY_SGD = 0, APPLY_GRAD = 1, APPLY_SGDX = 2 };
 // APPLY_SGDX: the reference's full sgd_update (/root/reference/src/runtime/optimizer_kernel.cu:23-41:
@@ -316,6 +316,43 @@ __device__ __forceinline__ float4 f4_div_exact(float4 a, float d, float r) {
   if (!(div_rn_safe(a.x) && div_rn_safe(a.y) && div_rn_safe(a.z) && div_rn_safe(a.w))) q = f4_div_ieee(a, d);
   return q;
 }
+// ---- TMA bulk copies (cp.async.bulk) + mbarrier: the push over NVLink (ffemb_exchange.cu) and the bulk
+// row-gather experiment of the forward (ffemb_forward.cu) ---------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n .reg .pred P;\n mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n selp.b32 %0, 1, 0, P;\n}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void bulk_g2s(void *smem, const void *gmem, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem)),
+               "l"(gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void *gmem, const void *smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem), "r"(smem_u32(smem)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N> __device__ __forceinline__ void bulk_wait() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
 __device__ __forceinline__ int64_t shfl_i64(int64_t v, int src) {
   int lo = __shfl_sync(0xffffffffu, (int)(v & 0xffffffffll), src);
   int hi = __shfl_sync(0xffffffffu, (int)(v >> 32), src);

@@ -131,7 +131,9 @@ FFEMB_API int ffemb_exchange_backward(const ffemb_table_t *tables, int num_table
  *   parts[p].out      = the owner's output-grad buffer of the part, [B][w_p] floats (peer-mapped)
  *   parts[p].reserved = first column of the part inside a row of dx
  *   parts[p].L        = w_p, the part's width in floats (a multiple of 4)
- * idx / table / R are ignored.  Rows travel as tiles of up to 8 KB: cp.async.bulk global -> shared,
+ * idx / table are ignored.  parts[0].R, when in 1..16, is a hint: warps the push keeps resident per SM
+ * (default 4) — few (2) when it runs UNDER compute kernels of a neighbouring table group, many (16) when
+ * it runs alone; R of the other parts is ignored.  Rows travel as tiles of up to 8 KB: cp.async.bulk global -> shared,
  * then ONE contiguous cp.async.bulk shared -> peer global per tile (large posted NVLink writes issued
  * by a few dozen resident warps, so the push runs under the compute kernels of the neighbouring table
  * group); unaligned shapes fall back to 16-byte load/store per lane.                            */

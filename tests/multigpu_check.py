@@ -128,31 +128,34 @@ def main():
                         dup = B * bags[p.table] / rows[p.table] + 1
                         assert torch.allclose(Wp[k][j], want, rtol=0, atol=1e-6 * 0.01 * dup ** 0.5 * 8 + 1e-7), \
                             ("pipelined", aggr, split_tables, it, p, "updated part far from the unsharded table")
-            # the same step replayed from CUDA graphs (ShardedStepGraph): two more steps, alternating parity
-            caps = []
+            # the same step replayed from a CUDA graph (ShardedStepGraph) on the SAME state: eager step, tables put
+            # back, graph step — interaction input, routed output-grads and updated parts must be bit-identical
             for it in (3, 4):
                 idx_it = [(i + it) % r for i, r in zip(idx, rows)]
                 idxg = [[idx_it[p.table] for p in mine[k]] for k in range(K)]
-                caps.append((sstep.capture(idxg, 0.01, parity=it % 2), idx_it, idxg))
-            for (gr, idx_it, idxg), it in zip(caps, (3, 4)):
                 dxs = torch.rand((B, T * D), device=dev, generator=torch.Generator(device=dev).manual_seed(100 + it)) - 0.5
                 fx.dx.copy_(dxs[lo:hi])
-                want_x = torch.cat(tcoll.forward(idx_it), dim=1)
-                x = gr.replay()[:hi - lo]
-                assert torch.allclose(x, want_x[lo:hi], rtol=0, atol=1e-5), ("graph replay", aggr, split_tables, it, "x differs")
-                tcoll.backward_sgd(idx_it, [dxs[:, t * D:(t + 1) * D].contiguous() for t in range(T)], 0.01)
+                saved = [[w.clone() for w in Wp[k]] for k in range(K)]
+                x_e = sstep.run(idxg, 0.01)[:hi - lo].clone()
                 torch.cuda.synchronize()
+                dist.barrier()
+                after_e = [[w.clone() for w in Wp[k]] for k in range(K)]
+                og_e = [[g.clone() for g in fx.outgrads_by_group[k]] for k in range(K)]
+                for k in range(K):
+                    for j in range(len(Wp[k])):
+                        Wp[k][j].copy_(saved[k][j])
+                torch.cuda.synchronize()
+                dist.barrier()
+                gr = sstep.capture(idxg, 0.01, parity=fx.parity ^ 1)
+                x_g = gr.replay()[:hi - lo]
+                torch.cuda.synchronize()
+                assert torch.equal(x_g, x_e), ("graph replay", aggr, split_tables, it, "interaction input differs from the eager step")
                 for k in range(K):
                     for j, p in enumerate(mine[k]):
-                        c0 = p.table * D + p.col0
-                        assert torch.equal(fx.outgrads_by_group[k][j], dxs[:, c0:c0 + p.width]), \
-                            ("graph replay", aggr, split_tables, it, p, "routed output-grad differs")
-                        want = truth[p.table][:, p.col0:p.col0 + p.width]
-                        dup = B * bags[p.table] / rows[p.table] + 1
-                        assert torch.allclose(Wp[k][j], want, rtol=0, atol=(it + 1) * (1e-6 * 0.01 * dup ** 0.5 * 8 + 1e-7)), \
-                            ("graph replay", aggr, split_tables, it, p, "updated part far from the unsharded table")
-            del caps
-            dist.barrier()
+                        assert torch.equal(fx.outgrads_by_group[k][j], og_e[k][j]), ("graph replay", it, p, "routed output-grad")
+                        assert torch.equal(Wp[k][j], after_e[k][j]), ("graph replay", it, p, "updated part differs from the eager step")
+                del gr
+                dist.barrier()
         # ---- forward-only loop across ranks (no backward between the steps): x of step k must survive
         # until this rank has compared it although the peers are already storing step k + 1 ----
         fx = pkg.exchange.FusedTableWiseExchange(T, owner, B, D, rank, world, dev)
