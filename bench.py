@@ -10,8 +10,13 @@ A "step" is one pass of the hot path over one batch of synthetic input:
 Default workload = BASELINE.json configs[2] (MLPerf Criteo-Terabyte shape: 26 tables up to 40M
 rows x 128, multi-hot 1..20, batch 64K) — the config the north star's roofline and scaling
 targets are quoted on; it fits one B200 (96 GB of tables).  --workload 1|2|4|5 selects the
-others.  The table set and the global batch are fixed as N grows ("scaling": "strong"), tables
-placed t % N like the reference's strategy generator.
+others.  The table set and the global batch are fixed as N grows ("scaling": "strong").  Placement at
+N > 1: --placement balanced (the default and the headline: cost-aware, heavy tables split by columns,
+sharding.plan_shards — the plan is printed in config.shard_plan and named in config.parallelism) or
+--placement modulo, table t whole on GPU t % N like the reference's strategy generator
+(examples/cpp/DLRM/strategies/dlrm_strategy.cc:252-256).  At N > 1 the whole pipelined step is replayed
+from one CUDA graph per index batch (--graph off: eager), and one un-timed parity step runs first
+("parity_ok" in the line).  --workload 4 (row-wise, 8 GPUs): route kernel + the owners' padded backward.
 
 value   : device-resident inputs, CUDA events on the launch stream, max over ranks.
 e2e     : the same step through the host-side operator mirror with HOST (pinned) buffers:
@@ -72,6 +77,9 @@ def parse():
     ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
                     help="N=1: replay the step from a CUDA graph (StepGraph); auto = the launch-bound small "
                          "configs (<= 2M lookups per step: cfg1, cfg2), where it is worth 1.6-1.9x")
+    ap.add_argument("--l2-persist", type=int, default=-1,
+                    help="experiment: cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, MB) before the run "
+                         "(-1: leave the device as it is)")
     ap.add_argument("--aggr", type=int, default=0, help="override the workload's aggregation (21 SUM, 22 AVG literal, 122 MEAN): experiments")
     ap.add_argument("--rowwise", default="routed", choices=["routed", "legacy"],
                     help="cfg4: routed = bucketise by owner + remote stores + owners reduce their own lookups (SURVEY 8e); "
@@ -275,6 +283,14 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
+    if args.l2_persist >= 0:
+        import ctypes
+        rt = ctypes.CDLL("libcudart.so.12")
+        rc = rt.cudaDeviceSetLimit(6, ctypes.c_size_t(args.l2_persist << 20))   # cudaLimitPersistingL2CacheSize
+        got = ctypes.c_size_t(0)
+        rt.cudaDeviceGetLimit(ctypes.byref(got), 6)
+        print(f"[l2-persist] cudaDeviceSetLimit rc={rc}, limit now {got.value >> 20} MB, "
+              f"max {torch.cuda.get_device_properties(dev).L2_cache_size >> 20} MB L2", file=sys.stderr)
     wl = pkg.synth.config(args.workload, args.scale)
     if args.aggr:
         wl.aggr = args.aggr

@@ -236,9 +236,9 @@ class FusedTableWiseExchange:
                 arr[i].out = int(self.hg.buffer_ptrs[p.rank]) + self.g_off[(p.table, p.col0)] * 4
                 arr[i].reserved, arr[i].L = p.table * self.D + p.col0, p.width
             # resident warps per SM (hint): the push of a pipelined step runs under the neighbouring group's
-            # compute kernels (few warps: measured at N = 2); beyond 4 GPUs a rank's share is latency-bound,
-            # nothing of substance overlaps the push and it should simply be fast (many warps)
-            arr[0].R = 2 if (self.K > 1 and self.world <= 4) else 16
+            # compute kernels — few warps (measured at N = 2: 1.754 ms per step with 2, 1.841 with the default
+            # 4).  At N = 8 the push is bound by the fabric, not by its warps (0.201 ms with 16, 0.204 with 4)
+            arr[0].R = 2 if (self.K > 1 and self.world <= 4) else 0
             self._push[k] = (arr, len(ps))
         arr, n = self._push[k]
         if self.local_batch and n:
