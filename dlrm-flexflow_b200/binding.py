@@ -142,7 +142,7 @@ def lib():
 
 
 PHASES = ["forward", "keygen", "sort", "reduce1", "reduce_up", "atomic", "small", "exchange", "input", "dense",
-          "sync", "prescale"]
+          "sync", "prescale", "hot"]
 
 
 def profile_enable(on=True):

@@ -52,6 +52,7 @@ const Tuning &tuning() {
     x.xpush = (int)num("FFEMB_XPUSH");
     x.prescale = (int)num("FFEMB_PRESCALE");
     x.fwd_bulk = (int)num("FFEMB_FWD_BULK");
+    x.sort_aligned = (int)num("FFEMB_SORT_ALIGNED");
     return x;
   }();
   return t;

@@ -30,6 +30,7 @@
 
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <type_traits>
 
 #include "ffemb_internal.cuh"
@@ -602,7 +603,8 @@ combine_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys
     const int64_t sc = base + lane;
     K kc = INV;
     if (sc < ntiles) kc = keys[2 * sc + 1];
-    const bool is_start = kc != INV && (sc == 0 || keys[2 * sc - 1] != kc);
+    // (a tail partial the hot-row path has already used — the ragged head of a hot run — starts nothing)
+    const bool is_start = kc != INV && !consumed[2 * sc + 1] && (sc == 0 || keys[2 * sc - 1] != kc);
     uint32_t pending = __ballot_sync(0xffffffffu, is_start);
     // ... and its slots of G lanes take the starts SLOTS at a time
     while (pending) {  // warp-uniform
@@ -780,6 +782,250 @@ prescale_kernel(const __grid_constant__ TableBatch tp, int64_t B, int D, int64_t
 static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 static inline bool wide_keys(int64_t total_rows) { return (uint64_t)total_rows >= 0xffffffffull; }
 
+// ---- hot rows ---------------------------------------------------------------------------------------
+static constexpr int64_t kHotMinLookups = 1 << 22;  // calls below this many sorted lookups never look for hot rows
+static constexpr int kHotMin = 8192;                // a run of this many sorted lookups is "hot"
+static constexpr int kHotStep = kHotMin / 2;        // the sorted keys are probed every kHotStep entries
+static constexpr int kHotCtas = 64;                 // CTAs (bag ranges) per table in hot_sum_kernel
+struct HotRun {
+  uint32_t lo, hi;      // the run's WHOLE tiles: sorted positions [lo, hi), multiples of CH1
+  uint32_t start, end;  // the run itself: [start, end)
+  uint64_t key;         // global row id
+  int32_t table;
+  int32_t pad;
+};
+
+
+// Hot rows.  Under skew (BASELINE config 5: Zipf 1.05, bag 64) a few hundred rows per table hold half of
+// all lookups; through level 1 each of those lookups is a 4*D-byte gather of an output-grad row from L2
+// although the SAME few thousand output-grad rows are asked for again and again.  A run of >= kHotMin
+// sorted lookups therefore leaves level 1:
+//   hot_select : the sorted keys are probed every kHotStep entries; the first probe inside a run finds
+//                the run's ends by binary search; runs of >= kHotMin entries go on a list.
+//   hot_mark   : the run's WHOLE level-1 tiles are marked — level 1 skips them (and writes no partials);
+//                the run's ragged head and tail stay ordinary level-1 entries and arrive as the tail
+//                partial of the tile before / the head partial of the tile after.
+//   hot_sum    : BAG-major.  A CTA owns a range of bags of one table, stages the output-grad rows of 64 KB
+//                slices of it in shared memory (one TMA bulk copy per slice, double-buffered) and every
+//                warp adds, for the runs it owns, the slice's entries — a run's entries are bag-ascending,
+//                so a cursor per run walks them slice by slice — into REGISTER accumulators: an
+//                output-grad row is read from L2 once per CTA instead of once per lookup.
+//   hot_apply  : per run, head fragment + the CTAs' partial sums in bag order + tail fragment, then the
+//                run's one read-modify-write of the table row; the two fragments are marked consumed.
+// Every order is fixed by the sorted order and the shapes: bit-reproducible.  The set of hot runs is
+// "every run of >= kHotMin entries" — never capped, so it does not depend on the list's (atomic) order.
+__host__ __device__ __forceinline__ int64_t hot_base(const TableBatch &tb, int t) {
+  return (int64_t)(tb.t[t].lookup_base / kHotMin) + t;
+}
+
+template <typename K>
+__global__ void __launch_bounds__(256)
+hot_select_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys, int64_t n, int CH1,
+                  HotRun *list, uint32_t *cnt, int64_t cap) {
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  const int64_t q = i * kHotStep;
+  if (q >= n) return;
+  const K k = keys[q];
+  if ((uint64_t)k >= tb.row_base[tb.num_tables]) return;           // empty slots
+  if (i > 0 && keys[q - kHotStep] == k) return;                    // not the first probe inside its run
+  int64_t lo = i > 0 ? q - kHotStep + 1 : 0, hi = q;               // first position of k in (q - step, q]
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (keys[mid] < k) lo = mid + 1; else hi = mid;
+  }
+  const int64_t start = lo;
+  lo = q + 1; hi = n;                                               // first position after k in (q, n]
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (keys[mid] <= k) lo = mid + 1; else hi = mid;
+  }
+  const int64_t end = lo;
+  if (end - start < kHotMin) return;
+  const int64_t tlo = (start + CH1 - 1) / CH1 * CH1, thi = end / CH1 * CH1;
+  if (thi <= tlo) return;
+  // the list is cut into one segment per table (a table of n_t lookups has at most n_t / kHotMin hot runs),
+  // so that hot_sum finds a table's runs without searching; the order inside a segment is arbitrary
+  const int t = find_table(tb, (uint64_t)k);
+  const int64_t slot = hot_base(tb, t) + atomicAdd(cnt + t, 1u);
+  if (slot >= cap) return;  // (cannot happen)
+  HotRun r;
+  r.lo = (uint32_t)tlo; r.hi = (uint32_t)thi; r.start = (uint32_t)start; r.end = (uint32_t)end;
+  r.key = (uint64_t)k;
+  r.table = t;
+  r.pad = 0;
+  list[slot] = r;
+}
+
+static __global__ void __launch_bounds__(256)
+hot_mark_kernel(const __grid_constant__ TableBatch tb, const HotRun *__restrict__ list,
+                const uint32_t *__restrict__ cnt, int CH1, uint8_t *marks) {
+  const int tab = blockIdx.y;
+  const uint32_t nrun = cnt[tab];
+  for (uint32_t h = blockIdx.x; h < nrun; h += gridDim.x) {
+    const HotRun r = list[hot_base(tb, tab) + h];
+    for (int64_t t = r.lo / CH1 + threadIdx.x; t < r.hi / CH1; t += 256) marks[t] = 1;
+  }
+}
+
+static constexpr int kHotWarps = 8, kHotKW = 32;         // runs per pass and CTA: kHotWarps * kHotKW (lane i of a warp keeps run i's cursor)
+static constexpr int kHotSliceBytes = 64 << 10;          // output-grad rows staged per slice
+
+static __global__ void __launch_bounds__(kHotWarps * 32, 1)
+hot_sum_kernel(const __grid_constant__ TableBatch tb, const uint32_t *__restrict__ vals, int64_t B, int D,
+               const HotRun *__restrict__ list, const uint32_t *__restrict__ cnt, float *__restrict__ partials) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float *slice[2] = {reinterpret_cast<float *>(smem_raw), reinterpret_cast<float *>(smem_raw + kHotSliceBytes)};
+  uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + 2 * kHotSliceBytes);
+  const int t = blockIdx.y, c = blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nm = (int)cnt[t];
+  if (nm == 0) return;
+  const int64_t base = hot_base(tb, t);
+  if (threadIdx.x == 0) {
+    mbar_init(bar, 1);
+    mbar_init(bar + 1, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+  const TableDesc &td = tb.t[t];
+  const int64_t per = (B + gridDim.x - 1) / gridDim.x;
+  const int64_t bag0 = (int64_t)c * per, bag1 = min(B, bag0 + per);
+  const int SB = kHotSliceBytes / (D * 4);                 // bags per slice
+  const int D4 = D >> 2;
+  const bool own = lane < D4;
+  uint32_t phases = 0u;  // bit b: parity of the phase buffer b's barrier completes next
+  for (int g0 = 0; g0 < nm; g0 += kHotWarps * kHotKW) {   // passes of 256 runs (one for a few hundred hot rows)
+    // this warp's runs: lane i keeps the cursor / limit / list slot of run g0 + warp*KW + i
+    uint32_t cur = 0, lim = 0, slot = 0xffffffffu;
+    if (lane < kHotKW && g0 + warp * kHotKW + lane < nm) {
+      slot = (uint32_t)(base + g0 + warp * kHotKW + lane);
+      const HotRun r = list[slot];
+      auto first_bag_ge = [&](int64_t bag) {               // entries of a run are bag-ascending
+        uint32_t lo = r.lo, hi = r.hi;
+        while (lo < hi) {
+          const uint32_t mid = (lo + hi) >> 1;
+          if ((int64_t)(vals[mid] & BAG_MASK) < bag) lo = mid + 1; else hi = mid;
+        }
+        return lo;
+      };
+      cur = first_bag_ge(bag0);
+      lim = first_bag_ge(bag1);
+    }
+    float4 acc[kHotKW];
+#pragma unroll
+    for (int i = 0; i < kHotKW; i++) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int nslices = bag1 > bag0 ? (int)((bag1 - bag0 + SB - 1) / SB) : 0;
+    auto load = [&](int sidx) {                            // one bulk copy per slice (og_stride == D: contiguous)
+      if (threadIdx.x == 0 && sidx < nslices) {
+        const int64_t sb0 = bag0 + (int64_t)sidx * SB;
+        const uint32_t bytes = (uint32_t)(min((int64_t)SB, bag1 - sb0) * D * 4);
+        mbar_expect_tx(bar + (sidx & 1), bytes);
+        bulk_g2s(slice[sidx & 1], td.out + sb0 * (int64_t)D, bytes, bar + (sidx & 1));
+      }
+    };
+    load(0);
+    for (int sidx = 0; sidx < nslices; sidx++) {
+      load(sidx + 1);                                      // (its buffer was released by the barrier below)
+      const int bf = sidx & 1;
+      while (!mbar_try_wait(bar + bf, (phases >> bf) & 1u)) {}
+      phases ^= 1u << bf;
+      const int64_t sb0 = bag0 + (int64_t)sidx * SB, sb1 = min(bag1, sb0 + SB);
+      const float *gs = slice[bf];
+      // the first 32 entries of every run of this warp at its cursor, all loads in flight together (one
+      // L2 round trip per slice instead of one per run)
+      const int nsb = (int)(sb1 - sb0);                     // bags of this slice
+      int first[kHotKW];                                   // bag - sb0 (>= nsb: not in this slice)
+#pragma unroll
+      for (int i = 0; i < kHotKW; i++) {
+        const uint32_t cu = __shfl_sync(0xffffffffu, cur, i), li = __shfl_sync(0xffffffffu, lim, i);
+        first[i] = cu + lane < li ? (int)((int64_t)(vals[cu + lane] & BAG_MASK) - sb0) : nsb;
+      }
+#pragma unroll
+      for (int i = 0; i < kHotKW; i++) {
+        uint32_t cu = __shfl_sync(0xffffffffu, cur, i);
+        const uint32_t li = __shfl_sync(0xffffffffu, lim, i);
+        // the slice's entries of the run are summed on their own and then added to the run's accumulator:
+        // blocks of a few hundred addends, like the tiles of level 1 (one long serial fp32 sum of 10^4..10^5
+        // addends loses two digits the tiled sum keeps)
+        float4 part = make_float4(0.f, 0.f, 0.f, 0.f);
+        auto add_entries = [&](int rel, int nin) {        // the first nin lanes hold bags of this slice
+          for (int e0 = 0; e0 < nin; e0 += 8) {            // 8 shared-memory loads in flight, adds in entry order
+            float4 x[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+              const int b = __shfl_sync(0xffffffffu, rel, (e0 + u) & 31);
+              x[u] = make_float4(0.f, 0.f, 0.f, 0.f);      // (past the slice's entries: + 0 changes nothing)
+              if (own && e0 + u < nin) x[u] = *reinterpret_cast<const float4 *>(gs + (size_t)b * D + 4 * lane);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++) f4_add(part, x[u]);
+          }
+        };
+        auto ld_rel = [&](uint32_t p) {                    // bag - sb0 of entry p + lane (nsb: not this slice's)
+          return p + lane < li ? (int)((int64_t)(vals[p + lane] & BAG_MASK) - sb0) : nsb;
+        };
+        int rel = first[i];
+        while (cu < li) {                                  // warp-uniform
+          const int nin = __popc(__ballot_sync(0xffffffffu, rel < nsb));   // a prefix: bags ascend
+          add_entries(rel, nin);
+          cu += nin;
+          if (nin < 32) break;
+          rel = ld_rel(cu);
+        }
+        if (own) f4_add(acc[i], part);
+        if (lane == i) cur = cu;
+      }
+      __syncthreads();                                     // every warp is done with slice[bf]
+    }
+#pragma unroll
+    for (int i = 0; i < kHotKW; i++) {
+      const uint32_t sl_i = __shfl_sync(0xffffffffu, slot, i);
+      if (sl_i != 0xffffffffu && own)
+        st_f4(partials + ((size_t)sl_i * kHotCtas + c) * D + 4 * lane, acc[i]);
+    }
+  }
+}
+
+template <typename K, int MODE>
+__global__ void __launch_bounds__(256)
+hot_apply_kernel(const __grid_constant__ TableBatch tb, const HotRun *__restrict__ list,
+                 const uint32_t *__restrict__ cnt, int CH1, int D, float lr,
+                 const float *__restrict__ partials, const float *__restrict__ prows, uint16_t *consumed16) {
+  uint8_t *consumed = reinterpret_cast<uint8_t *>(consumed16);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tab = blockIdx.y;
+  const uint32_t nrun = cnt[tab];
+  const int D4 = D >> 2;
+  const bool own = lane < D4;
+  for (uint32_t hh = blockIdx.x * 8 + warp; hh < nrun; hh += gridDim.x * 8) {
+    const int64_t h = hot_base(tb, tab) + hh;
+    const HotRun r = list[h];
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool has_head = r.start < r.lo, has_tail = r.hi < r.end;
+    const int64_t th = r.start / CH1, tt = r.hi / CH1;    // tiles of the ragged head / tail
+    if (has_head && own) acc = ld_f4(prows + (2 * th + 1) * (int64_t)D + 4 * lane);    // its tail partial
+    for (int cc = 0; cc < kHotCtas; cc++)
+      if (own) f4_add(acc, ld_f4(partials + ((size_t)h * kHotCtas + cc) * D + 4 * lane));
+    if (has_tail && own) f4_add(acc, ld_f4(prows + (2 * tt) * (int64_t)D + 4 * lane));  // its head partial
+    float *wp = tb.t[r.table].table + (int64_t)(r.key - tb.row_base[r.table]) * D;
+    if (own) {
+      float4 o = ld_f4(wp + 4 * lane);
+      if (MODE == APPLY_SGD) {  // W -= lr*gt, contracted like the reference's FFMA
+        o.x = fmaf(-acc.x, lr, o.x); o.y = fmaf(-acc.y, lr, o.y);
+        o.z = fmaf(-acc.z, lr, o.z); o.w = fmaf(-acc.w, lr, o.w);
+      } else {
+        f4_add(o, acc);
+      }
+      st_f4(wp + 4 * lane, o);
+    }
+    if (lane == 0) {
+      if (has_head) consumed[2 * th + 1] = 1;
+      if (has_tail) consumed[2 * tt] = 1;
+    }
+  }
+}
+
 struct Levels {
   int count;            // number of partial buffers
   int64_t slots[8];     // partial slots of level i output (2 * tiles)
@@ -806,6 +1052,12 @@ struct Carve {
   char *pkeys[2];
   float *prows[2];
   uint16_t *consumed;   // marks of the level-1 partial slots (one byte each), behind the 32-bit "chains left" flag
+  // hot rows (skewed indices): runs of >= kHotMin sorted lookups leave level 1, see hot_select_kernel
+  uint32_t *hot_cnt;    // number of hot runs found this step
+  HotRun *hot_list;
+  uint8_t *hot_marks;   // one byte per level-1 tile: 1 = the tile lies inside a hot run (level 1 skips it)
+  float *hot_partials;  // [run][kHotCtas][D]
+  int64_t hot_cap;      // capacity of hot_list (0: no hot path at this size)
   size_t total;
 };
 static Carve carve(char *base, int64_t n, int64_t total_rows, int64_t D) {
@@ -835,6 +1087,11 @@ static Carve carve(char *base, int64_t n, int64_t total_rows, int64_t D) {
   c.prows[1] = (float *)take((size_t)s1 * D * 4);
   char *marks = take(16 + (size_t)s0);
   c.consumed = marks ? (uint16_t *)(marks + 4) : nullptr;
+  c.hot_cap = tuning().hot > 0 && n >= kHotMinLookups && D <= 128 ? n / kHotMin + FFEMB_MAX_TABLES + 2 : 0;  // (opt-in)
+  c.hot_cnt = (uint32_t *)take(c.hot_cap ? 256 : 0);
+  c.hot_list = (HotRun *)take((size_t)c.hot_cap * sizeof(HotRun));
+  c.hot_marks = (uint8_t *)take(c.hot_cap ? (size_t)(s0 / 2) : 0);
+  c.hot_partials = (float *)take((size_t)c.hot_cap * kHotCtas * D * 4);
   c.total = off;
   return c;
 }
@@ -962,7 +1219,28 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
   int end_bit = 1;
   const uint64_t max_key = (uint64_t)total_rows - (tb.padded ? 0 : 1);  // (empty slots carry key = total_rows)
   while (end_bit < (int)sizeof(K) * 8 && (max_key >> end_bit) != 0) end_bit++;
-  if (stage != STAGE_APPLY && !seg) {
+  if (stage != STAGE_APPLY && !seg && tb.sort_bits > 0) {
+    // aligned key space: one sort per table on that table's row bits (the table bits above them are the
+    // same for the whole stretch); same temp storage, same stream
+    int launches = 0;
+    for (int t = 0; t < tb.num_tables; t++) {
+      int bits = 1;
+      while (bits < 32 && ((uint64_t)(tb.t[t].R > 1 ? tb.t[t].R - 1 : 1) >> bits) != 0) bits++;
+      launches += B * tb.t[t].L > 0 ? 2 + (bits + 7) / 8 : 0;
+    }
+    ProfScope prof(FFEMB_PHASE_SORT, launches, s);
+    for (int t = 0; t < tb.num_tables; t++) {
+      const int64_t nt = B * (int64_t)tb.t[t].L;
+      if (nt == 0) continue;
+      int bits = 1;
+      while (bits < 32 && ((uint64_t)(tb.t[t].R > 1 ? tb.t[t].R - 1 : 1) >> bits) != 0) bits++;
+      const size_t lb = tb.t[t].lookup_base;
+      size_t tmp = c.cub_bytes;
+      cudaError_t e = cub::DeviceRadixSort::SortPairs(c.cub_tmp, tmp, keys_a + lb, keys_b + lb, c.vals_a + lb,
+                                                      c.vals_b + lb, (int)nt, 0, bits, s);
+      if (e != cudaSuccess) return cuda_fail(e, "radix sort (per table)");
+    }
+  } else if (stage != STAGE_APPLY && !seg) {
     // onesweep: histogram + scan + one pass per 8 key bits
     ProfScope prof(FFEMB_PHASE_SORT, 2 + (end_bit + 7) / 8, s);
     size_t tmp = c.cub_bytes;
@@ -977,6 +1255,27 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
   const int64_t slots_per_cta = (int64_t)(kThreads / 32) * SLOTS;
   const int64_t ntiles1 = (n + CH1 - 1) / CH1;
   K *pk0 = (K *)c.pkeys[0], *pk1 = (K *)c.pkeys[1];
+  // hot rows (skew): runs of >= kHotMin lookups leave level 1 (see hot_select_kernel).  Needs plain [B][D]
+  // output-grads (the pre-scaled ones of the AVG path qualify), one fragment per lane, no empty slots.
+  // OPT-IN (FFEMB_HOT=1): parity-green, but as measured in round 2 (profiles/r2_single_gpu.md) hot_sum
+  // takes 8-9 ms on cfg5 where it relieves level 1 of 2.2 ms and the upper levels of 0.3 ms
+  int ring_depth = 4;
+  if (tuning().r1_ring >= 0) ring_depth = tuning().r1_ring;
+  const bool hot = C == 1 && ring_depth > 0 && MODE != APPLY_SGDX && c.hot_cap > 0 && !tb.padded &&
+                   tb.og_stride == D && aggr == FFEMB_AGGR_SUM && tuning().hot > 0 && n < (1ll << 32);
+  if (hot) {
+    ProfScope prof(FFEMB_PHASE_HOT, 4, s);
+    cudaMemsetAsync(c.hot_cnt, 0, 256, s);
+    cudaMemsetAsync(c.hot_marks, 0, (size_t)ntiles1, s);
+    const int64_t probes = (n + kHotStep - 1) / kHotStep;
+    hot_select_kernel<K><<<(unsigned)((probes + 255) / 256), 256, 0, s>>>(tb, keys_b, n, CH1, c.hot_list, c.hot_cnt,
+                                                                         c.hot_cap);
+    hot_mark_kernel<<<dim3(64, tb.num_tables), 256, 0, s>>>(tb, c.hot_list, c.hot_cnt, CH1, c.hot_marks);
+    const size_t sm = 2 * kHotSliceBytes + 64;
+    cudaFuncSetAttribute(hot_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    hot_sum_kernel<<<dim3(kHotCtas, tb.num_tables), kHotWarps * 32, sm, s>>>(tb, c.vals_b, B, D, c.hot_list, c.hot_cnt,
+                                                                            c.hot_partials);
+  }
   {
     ProfScope prof(FFEMB_PHASE_REDUCE1, 1, s);
     constexpr int T1 = L1Threads<G>::value;
@@ -1007,7 +1306,8 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
       auto gor = [&](auto kern, int S) {
         const size_t sm = EPC * sizeof(EntryDesc) + (size_t)(T1 / 32) * S * 2 * 32 * 16;
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], split, oa, c.consumed);
+        kern<<<grid1, T1, sm, s>>>(tb, keys_b, c.vals_b, n, D, lr, pk0, c.prows[0], split, oa, c.consumed,
+                                   hot ? c.hot_marks : nullptr);
       };
       if constexpr (C == 1) {
         const bool avg = aggr != FFEMB_AGGR_SUM;
@@ -1021,6 +1321,12 @@ static int run_sorted(const TableBatch &tb, int D, int64_t B, int aggr, float lr
       if constexpr (MODE != APPLY_SGDX) { if (pipe) { go(reduce1_kernel<K, G, C, MODE, true, true>, sm_avg); pipe_done = true; } }
       if (!pipe_done) go(reduce1_kernel<K, G, C, MODE, true, false>, sm_avg);
     }
+  }
+  if (hot) {  // head fragment + the bag ranges' partial sums + tail fragment, then the row's one update
+    ProfScope prof(FFEMB_PHASE_HOT, 1, s);
+    if constexpr (MODE != APPLY_SGDX)
+      hot_apply_kernel<K, MODE><<<dim3(32, tb.num_tables), 256, 0, s>>>(tb, c.hot_list, c.hot_cnt, CH1, D, lr,
+                                                                        c.hot_partials, c.prows[0], c.consumed);
   }
   int64_t m = 2 * ntiles1;
   if (ntiles1 > 1) {
@@ -1175,6 +1481,29 @@ int launch_backward_sorted(const TableBatch &tb_all, int64_t D, int64_t B, int a
     if (pass == 0) n_stream = n;
   }
   tb.row_base[tb.num_tables] = rows_l;
+  // Few large tables: an ALIGNED key space, (t << kbits) + row, lets every table be sorted on its own row
+  // bits — cfg5: eight 10 M-row tables need 24 bits = 3 radix passes each instead of the 4 passes of the
+  // 27-bit global key (4.7 -> 3.6 ms for 134 M pairs).  Worth it when the passes saved outweigh the extra
+  // chains of launches (measured: ~9.5 ps per pair and pass — 118 us for 12.4 M pairs —, ~45 us per chain); FFEMB_SORT_ALIGNED=0/1 forces.
+  if (tb.num_tables > 1 && !tb.padded && !wide_keys((int64_t)rows_l)) {
+    int kbits = 1, gbits = 1;
+    auto bits_of = [](uint64_t maxv) { int b = 1; while (b < 64 && (maxv >> b) != 0) b++; return b; };
+    gbits = bits_of(rows_l > 1 ? rows_l - 1 : 1);
+    for (int t = 0; t < tb.num_tables; t++) kbits = std::max(kbits, bits_of(tb.t[t].R > 1 ? (uint64_t)tb.t[t].R - 1 : 1));
+    double saved_ns = 0;
+    for (int t = 0; t < tb.num_tables; t++) {
+      const int bt = bits_of(tb.t[t].R > 1 ? (uint64_t)tb.t[t].R - 1 : 1);
+      saved_ns += (double)B * tb.t[t].L * ((gbits + 7) / 8 - (bt + 7) / 8) * 0.0095;
+    }
+    bool aligned = saved_ns > 45e3 * (tb.num_tables - 1) && ((uint64_t)tb.num_tables << kbits) < 0xffffffffull &&
+                   (int64_t)n > (int64_t)kSegThreads * kSegMaxItems * tb.num_tables;
+    if (tuning().sort_aligned >= 0) aligned = tuning().sort_aligned != 0 && ((uint64_t)tb.num_tables << kbits) < 0xffffffffull;
+    if (aligned) {
+      tb.sort_bits = kbits;
+      for (int t = 0; t <= tb.num_tables; t++) tb.row_base[t] = (uint64_t)t << kbits;
+      rows_l = (uint64_t)tb.num_tables << kbits;
+    }
+  }
   const int64_t rows = (int64_t)rows_l;
   const Carve c = carve((char *)ws, (int64_t)n, rows > 0 ? rows : 1, D);
   int aggr_l1 = aggr;

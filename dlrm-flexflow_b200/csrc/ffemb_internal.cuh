@@ -42,6 +42,10 @@ struct TableBatch {
   // keygen gives them the key `row_base[num_tables]` (one past the last row), they sort to the end
   // and level 1 never loads anything for them
   int32_t padded;
+  // bwd: > 0 = the key space is ALIGNED — table t's keys are (t << sort_bits) + row — and every table's
+  // stretch of the lookup array is sorted on its own, on its own row bits (fewer radix passes than the
+  // global sort when the tables are large and few: launch_backward_sorted decides)
+  int32_t sort_bits;
   // floats between consecutive rows of the output-grad buffers (bwd).  D: plain [B][D] buffers;
   // larger: td.out points at the table's column block inside a wider row-major matrix — the
   // gradient of the Concat output (ffemb_backward_sgd_concat)
@@ -64,7 +68,7 @@ int cuda_fail(cudaError_t e, const char *what);
 struct Tuning {
   long long stream_mb, l1_kb;
   int fwd_perm, fwd_avg_div, fwd_target, r1_mix, r1_flags, r1_pipe, r1_ring, small, small_fork,
-      up_fused, hot, slab_mb, own_sort, xpush, prescale, fwd_bulk;
+      up_fused, hot, slab_mb, own_sort, xpush, prescale, fwd_bulk, sort_aligned;
 };
 const Tuning &tuning();
 

@@ -30,7 +30,8 @@ template <typename K, int G, int MODE, bool AVG, int S>
 __global__ void __launch_bounds__(L1Threads<G>::value)
 reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__ keys,
                     const uint32_t *__restrict__ vals, int64_t n, int D, float lr, K *keys_out,
-                    float *rows_out, uint32_t split, const OptArgs *oa, uint16_t *consumed) {
+                    float *rows_out, uint32_t split, const OptArgs *oa, uint16_t *consumed,
+                    const uint8_t *__restrict__ hot_marks) {
   constexpr int THREADS = L1Threads<G>::value;
   constexpr int CH1 = Ch1<G>::value;
   constexpr int SLOTS = 32 / G, WARPS = THREADS / 32, EPW = SLOTS * CH1;
@@ -46,6 +47,13 @@ reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__
   const int64_t wbase = ((int64_t)mix_cta(blockIdx.x, gridDim.x, split) * WARPS + warp) * EPW;
   if (wbase >= n) return;  // warp-uniform
   const int D4 = D >> 2;
+  if (SLOTS == 1 && hot_marks && hot_marks[wbase / CH1]) {  // the warp's one tile lies inside a hot run: nothing to do
+    if (lane == 0) {
+      consumed[wbase / CH1] = 0;
+      keys_out[2 * (wbase / CH1)] = keys_out[2 * (wbase / CH1) + 1] = INV;
+    }
+    return;
+  }
 
   // ---- phase 1: descriptors (parallel over lanes) ----
 #pragma unroll
@@ -73,6 +81,10 @@ reduce1_ring_kernel(const __grid_constant__ TableBatch tb, const K *__restrict__
   const int64_t t0 = tile * CH1;
   if (t0 >= n) return;
   if (sl == 0) consumed[tile] = 0;  // (both partial slots of the tile: not yet taken by combine_kernel)
+  if (hot_marks && hot_marks[tile]) {  // the tile lies inside a hot run: hot_sum_kernel adds its entries
+    if (sl == 0) keys_out[2 * tile] = keys_out[2 * tile + 1] = INV;
+    return;
+  }
   const bool own = sl < D4;
   const EntryDesc *dq = wd + sub * CH1;
   int cnt = (int)min((int64_t)CH1, n - t0);

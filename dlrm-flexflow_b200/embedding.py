@@ -335,7 +335,7 @@ class StepGraph:
     the place of the caller's own work on the capture stream (interaction, dense layers).
     (The sgdx / adam entry points are not capturable: their scalar arguments change every step.)"""
 
-    def __init__(self, coll, batch, lr, idx=None, outs=None, out_grads=None, between=None):
+    def __init__(self, coll, batch, lr, idx=None, outs=None, out_grads=None, between=None, overlap_sort=True):
         dev = coll.device
         self.coll, self.batch, self.lr = coll, int(batch), float(lr)
         new = lambda shape, dt: torch.zeros(shape, dtype=dt, device=dev)
@@ -349,11 +349,21 @@ class StepGraph:
         coll.backward_sgd(self.idx, self.out_grads, 0.0)
         torch.cuda.synchronize(dev)
         self.graph = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(device=dev) if overlap_sort else None
         with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+            main = torch.cuda.current_stream(dev)
+            if side is not None:
+                # the index sort needs the indices only: a second branch of the graph, next to the forward
+                # pass (and the caller's work in `between`); the segmented sum joins it (at these sizes the
+                # sort is one CTA per table and the forward a few dozen CTAs: they run side by side)
+                side.wait_stream(main)
+                coll.backward_prepare(self.idx, stream=side)
             coll.forward(self.idx, self.outs)
             if between is not None:
                 between(self)
-            coll.backward_sgd(self.idx, self.out_grads, self.lr)
+            if side is not None:
+                main.wait_stream(side)
+            coll.backward_sgd(self.idx, self.out_grads, self.lr, prepared=side is not None)
 
     def replay(self):
         self.graph.replay()

@@ -393,7 +393,8 @@ FFEMB_API int ffemb_check_indices(const int64_t *idx, int64_t n, int64_t R, int6
 #define FFEMB_PHASE_DENSE 9     /* general SGD: the pass over the rows a step did not touch */
 #define FFEMB_PHASE_SYNC 10     /* cross-rank flag kernels (ffemb_sync_signal / ffemb_sync_wait) */
 #define FFEMB_PHASE_PRESCALE 11 /* AVG / MEAN backward: output-grad / in_dim, once per bag, ahead of the segmented sum */
-#define FFEMB_NUM_PHASES 12
+#define FFEMB_PHASE_HOT 12      /* skewed indices: rows with thousands of lookups summed bag-major (select, mark, sum, apply) */
+#define FFEMB_NUM_PHASES 13
 FFEMB_API int ffemb_profile_enable(int on);
 FFEMB_API int ffemb_profile_collect(float *ms_per_phase, int64_t *launches_per_phase);
 FFEMB_API int64_t ffemb_launch_count(void);

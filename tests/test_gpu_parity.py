@@ -996,3 +996,82 @@ def test_avg_backward_division_once_per_bag_equals_division_per_lookup(ffemb, or
             want = oracle.reference_step(idx[t], gs[t].copy(), Ws[t].copy(), aggr, 0.01)
             cnt = np.bincount(idx[t].reshape(-1), minlength=rows[t])
             assert np.array_equal(res[1][t][cnt <= 1], want[cnt <= 1]), (t, "single-lookup rows vs the reference step")
+
+
+@pytest.mark.parametrize("aggr", [21, 22])
+def test_backward_aligned_key_space_per_table_sorts(ffemb, oracle, torch_cuda, aggr):
+    """Few large batches of lookups into tables whose own row bits need fewer radix passes than the global
+    key (here 2 x 60000 rows: 16 bits each, 17 together, 4.2 M lookups per table) take the ALIGNED key
+    space — table t's keys are (t << 16) + row and every table's stretch is sorted on its own.  Same
+    contract as any batched backward: untouched and single-lookup rows bit-identical to the reference
+    step, repeated rows within the summation bound."""
+    torch = torch_cuda
+    rows, bags, D, B = [60000, 60000], [64, 64], 16, 65536
+    rng = np.random.default_rng(17 + aggr)
+    Ws = [rng.uniform(-0.5, 0.5, (r, D)).astype(np.float32) for r in rows]
+    idx = [rng.integers(0, r, (B, l), dtype=np.int64) for r, l in zip(rows, bags)]
+    idx[0][:, 0] = 59999                       # a hot last row right below the next table's key range
+    idx[1][::3, 1] = 0                         # and a hot first row of the next table
+    gs = [rng.uniform(-1, 1, (B, D)).astype(np.float32) for _ in rows]
+    d_idx, d_g = [dev(torch, x) for x in idx], [dev(torch, x) for x in gs]
+    together = [dev(torch, w) for w in Ws]
+    ffemb.EmbeddingCollection(together, bags, aggr).backward_sgd(d_idx, d_g, 0.01)
+    torch.cuda.synchronize()
+    for t in range(len(rows)):
+        got = together[t].cpu().numpy()
+        want = oracle.reference_step(idx[t], gs[t].copy(), Ws[t].copy(), aggr, 0.01)
+        cnt = np.bincount(idx[t].reshape(-1), minlength=rows[t])
+        assert np.array_equal(got[cnt <= 1], want[cnt <= 1]), (t, "single-lookup / untouched rows")
+        tol = table_tol(Ws[t]) * np.sqrt(np.maximum(cnt, 1))[:, None] * 2
+        assert np.all(np.abs(got.astype(np.float64) - want) <= tol), (t, "updated table")
+
+
+@pytest.mark.parametrize("aggr,D", [(21, 64), (22, 128), (21, 16)])
+def test_backward_hot_rows_under_skew(ffemb, oracle, torch_cuda, aggr, D):
+    """Skewed indices through the default path (level 1 + combine + the tree for chains of > 128 partials):
+    one row with 630 K lookups (several per bag), a hot LAST row of a table and a hot FIRST row of the next
+    one, rows of 7000-9500 lookups.  Untouched and single-lookup rows bit-identical to the reference step,
+    repeated rows within the summation bound of the fp64 sum, and two runs on the same inputs bit-identical
+    (the reference's atomics are not).  test_backward_hot_rows_opt_in runs the same data through the opt-in
+    bag-major hot-row kernels."""
+    torch = torch_cuda
+    rows, bags, B = [100000, 50000], [32, 32], 65536      # 4.2 M sorted lookups: the hot path's minimum
+    rng = np.random.default_rng(3 + aggr + D)
+    Ws = [rng.uniform(-0.5, 0.5, (r, D)).astype(np.float32) for r in rows]
+    idx = [rng.integers(0, r, (B, l), dtype=np.int64) for r, l in zip(rows, bags)]
+    flat0 = idx[0].reshape(-1)
+    sel = rng.random(flat0.size)
+    flat0[sel < 0.30] = 5                       # one very hot row (~630 K lookups, several per bag)
+    flat0[(sel >= 0.30) & (sel < 0.31)] = 99999  # the table's last row, hot (~21 K)
+    for k in range(6):                          # rows around the threshold: 7000 .. 9500 lookups
+        m = (sel >= 0.32 + 0.006 * k) & (sel < 0.32 + 0.006 * k + (7000 + 500 * k) / flat0.size)
+        flat0[m] = 1000 + k
+    flat1 = idx[1].reshape(-1)
+    flat1[rng.random(flat1.size) < 0.05] = 0    # the next table's first row, hot
+    gs = [rng.uniform(-1, 1, (B, D)).astype(np.float32) for _ in rows]
+    d_idx, d_g = [dev(torch, x) for x in idx], [dev(torch, x) for x in gs]
+    res = []
+    for rep in range(2):
+        dW = [dev(torch, w) for w in Ws]
+        ffemb.EmbeddingCollection(dW, bags, aggr).backward_sgd(d_idx, d_g, 0.01)
+        torch.cuda.synchronize()
+        res.append([w.cpu().numpy() for w in dW])
+    for t in range(len(rows)):
+        assert np.array_equal(res[0][t].view(np.uint32), res[1][t].view(np.uint32)), (t, "not reproducible")
+        want = oracle.reference_step(idx[t], gs[t].copy(), Ws[t].copy(), aggr, 0.01)
+        cnt = np.bincount(idx[t].reshape(-1), minlength=rows[t])
+        got = res[0][t]
+        assert np.array_equal(got[cnt <= 1], want[cnt <= 1]), (t, "single-lookup / untouched rows")
+        exact = Ws[t].astype(np.float64) - 0.01 * oracle.backward_dense_f64(idx[t], gs[t], rows[t], aggr)
+        tol = table_tol(Ws[t]) * np.sqrt(np.maximum(cnt, 1))[:, None]
+        assert np.all(np.abs(got - exact) <= tol), (t, "updated table vs the fp64 sum")
+
+
+def test_backward_hot_rows_opt_in(torch_cuda):
+    """FFEMB_HOT=1 (a process of its own: the tuning switches are read once): rows with >= 8192 lookups
+    leave level 1 and are summed bag-major (hot_select / hot_mark / hot_sum / hot_apply) — same bars."""
+    import subprocess
+    env = dict(os.environ, FFEMB_HOT="1")
+    r = subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "hot_rows_check.py")], env=env,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "hot_rows_check ok" in r.stdout, r.stdout[-3000:]
