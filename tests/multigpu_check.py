@@ -243,6 +243,10 @@ def main():
                         cnt = torch.bincount(idx[t].reshape(-1), minlength=rows3[t])[r0:r0 + rc.local_rows[t]]
                         assert torch.equal(mine[cnt <= 1], want[cnt <= 1]), ("row-wise collection: single-lookup rows differ", t, legacy)
                     assert torch.allclose(mine, want, rtol=0, atol=2e-6), ("row-wise collection update differs", t, legacy, it)
+                # (the checks above read the routed buffers from outside the protocol: nobody may route the
+                # next step's lookups into them before every rank is done looking)
+                torch.cuda.synchronize()
+                dist.barrier()
             dist.barrier()
     if rank == 0:
         print(f"multigpu_check ok: world={world}, fused and nccl exchanges bit-exact vs single GPU")
