@@ -45,6 +45,30 @@ def shard_rows(rows: int, world: int, rank: int) -> int:
     return max(0, min(rows, (rank + 1) * rps) - rank * rps)
 
 
+def route_slots(idx, rows: int, world: int, owner: int):
+    """Host statement of what ffemb_rowwise_route (include/ffemb.h) leaves in owner `owner`'s slot
+    array for one table: idx [B][L] global row ids of the WHOLE batch -> int64 [B][L] with
+    row - owner*rows_per_shard where `owner` holds the row and -1 (empty slot) elsewhere.  Slot
+    positions are the global (sample, j) positions: nothing is compacted."""
+    import numpy as np
+    idx = np.asarray(idx, np.int64)
+    rps = rows_per_shard(rows, world)
+    mine = (idx // rps) == owner
+    return np.where(mine, idx - owner * rps, -1).astype(np.int64)
+
+
+def route_bytes(batch: int, bags, dim: int, world: int, owners_per_bag=None) -> int:
+    """NVLink + local bytes ONE rank stores in a route of its ceil(batch/world) samples: 8 bytes per
+    lookup and owner for the slots, plus one gradient row of dim floats per (bag, owner) pair —
+    `owners_per_bag` distinct owners on average (default: min(L, world), the uniform-index bound)."""
+    ext = (batch + world - 1) // world
+    total = 0
+    for L in bags:
+        pairs = min(L, world) if owners_per_bag is None else owners_per_bag
+        total += ext * L * 8 * world + int(ext * pairs * dim * 4)
+    return total
+
+
 @dataclass
 class TableWisePlan:
     """Who owns what, and the all-to-all split sizes (in floats) of one exchange.

@@ -197,3 +197,82 @@ def test_plan_round_trips_through_the_strategy_file_format(ffemb, tmp_path):
     st = S.plan_strategy(whole, 8)
     assert S.owners_from_strategy(st, wl.num_tables) == [next(p.rank for p in whole if p.table == t)
                                                          for t in range(wl.num_tables)]
+
+
+# ---- row-wise routed backward: the host statement of the slot arrays (include/ffemb.h, ffemb_rowwise_route)
+def test_route_slots_is_the_oracles_stable_bucketing(ffemb, oracle):
+    S = ffemb.sharding
+    rng = np.random.default_rng(11)
+    for R, G, B, L in [(1000, 4, 37, 3), (17, 8, 64, 1), (5, 2, 9, 7), (4096, 3, 50, 4)]:
+        idx = rng.integers(0, R, (B, L), dtype=np.int64)
+        offsets, perm, local = oracle.route_rows(idx.reshape(-1), R, G)
+        for g in range(G):
+            slots = S.route_slots(idx, R, G, g)
+            assert slots.shape == idx.shape and slots.dtype == np.int64
+            pos = np.flatnonzero(slots.reshape(-1) >= 0)
+            # same positions, same order (global (sample, j) order) and same local rows as the
+            # oracle's stable bucketing; everything else is an empty slot
+            lo, hi = offsets[g], offsets[g + 1]
+            assert np.array_equal(pos, perm[lo:hi])
+            assert np.array_equal(slots.reshape(-1)[pos], local[lo:hi])
+            assert np.all(slots.reshape(-1)[np.setdiff1d(np.arange(B * L), pos)] == -1)
+            assert slots.max(initial=-1) < S.shard_rows(R, G, g)
+        # every lookup lands on exactly one owner
+        owners = sum((S.route_slots(idx, R, G, g) >= 0).astype(np.int64) for g in range(G))
+        assert np.all(owners == 1)
+
+
+def test_routed_backward_on_slot_arrays_equals_the_unsharded_step(ffemb, oracle):
+    """Owner g's backward over its slot array (empty slots skipped, equal rows met in global
+    (sample, j) order) + SGD on its shard == the rows of the unsharded reference step, bit for bit."""
+    S = ffemb.sharding
+    rng = np.random.default_rng(12)
+    for R, G, B, L, D, aggr in [(300, 4, 48, 3, 8, oracle.AGGR_SUM), (64, 8, 128, 2, 16, oracle.AGGR_SUM),
+                                (33, 2, 40, 5, 4, oracle.AGGR_AVG)]:
+        idx = rng.integers(0, R, (B, L), dtype=np.int64)
+        idx[: B // 4] = idx[0]  # heavy duplicates: order of accumulation matters
+        W = rng.standard_normal((R, D)).astype(np.float32)
+        og = rng.standard_normal((B, D)).astype(np.float32)
+        want = oracle.reference_step(idx, og, W, aggr=aggr, lr=0.05)
+        rps = S.rows_per_shard(R, G)
+        got = np.empty_like(W)
+        for g in range(G):
+            n = S.shard_rows(R, G, g)
+            if n == 0:
+                continue
+            slots = S.route_slots(idx, R, G, g)
+            # an empty slot touches nothing: send it to a throw-away row past the shard
+            filled = np.where(slots >= 0, slots, n)
+            grad = oracle.backward_dense(filled, og, n + 1, aggr=aggr)[:n]
+            got[g * rps:g * rps + n] = oracle.sgd_update(W[g * rps:g * rps + n], grad, 0.05)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def test_plan_groups_are_consistent_across_ranks(ffemb):
+    """Every rank derives the plan alone (no exchange of plans): same inputs -> same parts, and the
+    pipeline groups partition every rank's parts — num_groups(plan) is a property of the PLAN, not of
+    one rank's share (the world-8 IndexError of round 2)."""
+    S, wl = ffemb.sharding, ffemb.synth.config(3)
+    for world in (2, 4, 8):
+        for groups in (1, 2, 3):
+            a = S.plan_shards(wl.rows, wl.bags, wl.dim, world, "balanced", True, groups)
+            b = S.plan_shards(wl.rows, wl.bags, wl.dim, world, "balanced", True, groups)
+            key = lambda p: (p.table, p.col0, p.width, p.rank, p.group)
+            assert list(map(key, a)) == list(map(key, b))
+            K = S.num_groups(a)
+            assert K >= 1
+            assert all(0 <= p.group < K for p in a)
+            for r in range(world):
+                mine = [p for p in a if p.rank == r]
+                assert max((p.group for p in mine), default=0) < K
+
+
+def test_route_bytes_accounting(ffemb):
+    S = ffemb.sharding
+    # one table, bag 4, world 2, batch 8: ext 4 samples; slots 4*4*8*2 = 256 B; rows 4 bags * 2 owners * 16*4
+    assert S.route_bytes(8, [4], 16, 2) == 256 + 4 * 2 * 64
+    # bag 1: one owner per bag whatever the world
+    assert S.route_bytes(8, [1], 16, 8) == 1 * 1 * 8 * 8 + 1 * 1 * 64
+    assert S.route_bytes(8, [4], 16, 2, owners_per_bag=1.5) == 256 + int(4 * 1.5 * 64)
+    # grows with the world on the slot side only
+    assert S.route_bytes(1024, [2, 2], 64, 8) > S.route_bytes(1024, [2, 2], 64, 2) // 4
