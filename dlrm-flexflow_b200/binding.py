@@ -112,6 +112,8 @@ def lib():
     L.ffemb_backward_dense_atomic.argtypes = [vp, vp, vp, i64, i64, i64, i32, vp]
     L.ffemb_backward_dense.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_sgd.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, f32, vp, sz, vp]
+    L.ffemb_backward_sgd_static.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, f32, vp]
+    L.ffemb_static_scratch_bytes.restype = sz
     L.ffemb_backward_sgd_batched.argtypes = [tp, i32, i64, i64, i32, f32, vp, sz, vp]
     L.ffemb_backward_prepare.argtypes = [tp, i32, i64, i64, i32, vp, sz, vp]
     L.ffemb_backward_sgd_prepared.argtypes = [tp, i32, i64, i64, i32, f32, vp, sz, vp]

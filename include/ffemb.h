@@ -247,6 +247,22 @@ FFEMB_API int ffemb_backward_sgd(const int64_t *idx, const float *outgrad, float
                        int64_t D, int64_t B, int64_t R, int aggr, float lr, void *workspace,
                        size_t workspace_bytes, ffemb_stream_t stream);
 
+/* The same step for callers that cannot allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The scratch of the sorted backward lives in a file-scope device
+ * array of FFEMB_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it
+ * until the process exits) instead of a caller-supplied workspace; the call allocates nothing (no
+ * cudaMalloc / cudaFree, no allocating library routine), runs the launch sequence of
+ * ffemb_backward_sgd and gives bit-identical results.  Shapes whose
+ * ffemb_backward_workspace(B*L, R, D) exceeds the array are refused with FFEMB_EWORKSPACE and a
+ * message naming both sizes.  All calls on a device share the array, which keeps the last call's
+ * contents: the span a call uses is cleared on `stream` first, and calls that overlap on the GPU
+ * (different streams, or host threads, on one device) RACE — serialise them.                   */
+#define FFEMB_STATIC_SCRATCH_BYTES (64u << 20)
+FFEMB_API size_t ffemb_static_scratch_bytes(void);
+FFEMB_API int ffemb_backward_sgd_static(const int64_t *idx, const float *outgrad, float *table, int64_t L,
+                              int64_t D, int64_t B, int64_t R, int aggr, float lr, ffemb_stream_t stream);
+
 FFEMB_API int ffemb_backward_sgd_batched(const ffemb_table_t *tables, int num_tables, int64_t D, int64_t B,
                                int aggr, float lr, void *workspace, size_t workspace_bytes,
                                ffemb_stream_t stream);
