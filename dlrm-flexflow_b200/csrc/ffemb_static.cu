@@ -13,6 +13,8 @@
 
 #include <cuda_runtime.h>
 
+#include <atomic>
+
 namespace {
 
 constexpr size_t kStaticScratchBytes = (size_t)FFEMB_STATIC_SCRATCH_BYTES;
@@ -24,13 +26,8 @@ __global__ void static_scratch_anchor_kernel(unsigned char **where) { *where = g
 
 // g_static_scratch is a host-side stand-in here, not a device address: the kernels get the address
 // cudaGetSymbolAddress reports for the CURRENT device, looked up once per device.
-struct DeviceScratch {
-  void *ptr;
-  bool tried;
-  cudaError_t err;
-};
 constexpr int kMaxDevices = 64;
-DeviceScratch g_dev[kMaxDevices];
+std::atomic<void *> g_dev_ptr[kMaxDevices];  // zero-initialised: not looked up yet
 
 int static_scratch(void **out) {
   int dev = -1;
@@ -41,15 +38,17 @@ int static_scratch(void **out) {
     return FFEMB_EINVAL;
   }
   (void)&static_scratch_anchor_kernel;
-  DeviceScratch &d = g_dev[dev];
-  if (!d.tried) {  // (idempotent: two host threads racing here store the same address)
-    void *p = nullptr;
-    d.err = cudaGetSymbolAddress(&p, g_static_scratch);
-    d.ptr = d.err == cudaSuccess ? p : nullptr;
-    d.tried = true;
+  void *p = g_dev_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {  // first call on this device (two host threads racing here store the same address)
+    e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) return ffemb::cuda_fail(e, "cudaGetSymbolAddress(static scratch)");
+    if (!p) {
+      ffemb::set_error("cudaGetSymbolAddress(static scratch) returned a null address");
+      return FFEMB_ECUDA;
+    }
+    g_dev_ptr[dev].store(p, std::memory_order_release);
   }
-  if (d.err != cudaSuccess || !d.ptr) return ffemb::cuda_fail(d.err, "cudaGetSymbolAddress(static scratch)");
-  *out = d.ptr;
+  *out = p;
   return FFEMB_OK;
 }
 
