@@ -94,3 +94,35 @@ def test_dropin_binding_defines_the_reference_symbols():
     und = subprocess.run(["nm", "-D", "--undefined-only", so], stdout=subprocess.PIPE, text=True, check=True).stdout
     assert "ffemb_forward" in und and "ffemb_backward_sgd" in und  # the numeric work is libffemb's
     assert "embed_forward" not in out and "embed_backward" not in out  # none of the reference kernels
+
+
+def test_header_is_plain_c_and_struct_layouts_match_the_ctypes_mirror(ffemb, tmp_path):
+    """include/ffemb.h must compile as C99 (the boundary is a C ABI: no C++ types in it) and as C++11
+    (the reference's dialect, CMakeLists.txt), and the ctypes mirror in binding.py must lay the
+    descriptor structs out exactly as the C compiler does."""
+    import ctypes as C
+    import subprocess
+    B = ffemb.binding
+    structs = ["ffemb_table_t", "ffemb_sgd_t", "ffemb_adam_t", "ffemb_exchange_t", "ffemb_sync_t", "ffemb_route_t"]
+    src = tmp_path / "layout.c"
+    body = "".join(f'  printf("{s} %zu\\n", sizeof({s}));\n' for s in structs)
+    body += '  printf("R %zu\\n", offsetof(ffemb_table_t, R));\n  printf("L %zu\\n", offsetof(ffemb_table_t, L));\n'
+    body += '  printf("num_peers %zu\\n", offsetof(ffemb_exchange_t, num_peers));\n'
+    body += '  printf("row_stride %zu\\n", offsetof(ffemb_exchange_t, row_stride));\n'
+    body += '  printf("samples_per_peer %zu\\n", offsetof(ffemb_route_t, samples_per_peer));\n'
+    body += '  printf("cap %llu\\n", (unsigned long long)FFEMB_STATIC_SCRATCH_BYTES);\n'
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "ffemb.h"\nint main(void) {\n' + body + "  return 0;\n}\n")
+    inc = os.path.join(ROOT, "include")
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", f"-I{inc}", str(src), "-o", str(exe)],
+                   check=True)
+    subprocess.run(["g++", "-std=c++11", "-Wall", "-Wextra", "-Werror", f"-I{inc}", "-x", "c++", "-fsyntax-only", str(src)],
+                   check=True)
+    out = dict(l.split() for l in subprocess.run([str(exe)], stdout=subprocess.PIPE, text=True, check=True).stdout.splitlines())
+    for s in structs:
+        assert int(out[s]) == C.sizeof(getattr(B, s)), s
+    assert int(out["R"]) == B.ffemb_table_t.R.offset and int(out["L"]) == B.ffemb_table_t.L.offset
+    assert int(out["num_peers"]) == B.ffemb_exchange_t.num_peers.offset
+    assert int(out["row_stride"]) == B.ffemb_exchange_t.row_stride.offset
+    assert int(out["samples_per_peer"]) == B.ffemb_route_t.samples_per_peer.offset
+    assert int(out["cap"]) == int(B.lib().ffemb_static_scratch_bytes())
