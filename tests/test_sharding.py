@@ -276,3 +276,67 @@ def test_route_bytes_accounting(ffemb):
     assert S.route_bytes(8, [4], 16, 2, owners_per_bag=1.5) == 256 + int(4 * 1.5 * 64)
     # grows with the world on the slot side only
     assert S.route_bytes(1024, [2, 2], 64, 8) > S.route_bytes(1024, [2, 2], 64, 2) // 4
+
+
+# ---- property tests (hypothesis): strategy files and shard plans over random shapes ---------------
+def test_random_strategy_files_round_trip_and_load_in_the_reference(ffemb, oracle, tmp_path):
+    import pytest
+    from hypothesis import given, settings, strategies as st, HealthCheck
+    S = ffemb.sharding
+    have_ref = oracle.ref_cpu_available()
+
+    name = st.text(alphabet="abcdefghijklmnopqrstuvwxyzABCDEFGHIJKLMNOPQRSTUVWXYZ0123456789_", min_size=1, max_size=24)
+    dims = st.lists(st.integers(1, 4), min_size=1, max_size=4).filter(lambda d: int(np.prod(d)) <= 32)
+
+    @st.composite
+    def config(draw):
+        d = draw(dims)
+        n = int(np.prod(d))
+        ids = draw(st.lists(st.integers(0, 1023), min_size=n, max_size=n))
+        return S.ParallelConfig(draw(st.sampled_from([S.DEVICE_GPU, S.DEVICE_CPU])), d, ids)
+
+    case = {"n": 0}
+
+    @settings(max_examples=40, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+    @given(st.dictionaries(name, config(), min_size=1, max_size=12))
+    def run(strategies):
+        case["n"] += 1
+        p = str(tmp_path / f"s{case['n']}.strategy")
+        S.write_strategy(p, strategies)
+        back = S.read_strategy(p)
+        assert back == strategies
+        if have_ref:  # the reference's own loader sees the same thing, op by op
+            for op, c in strategies.items():
+                assert oracle.ref_strategy_load_op(p, op) == (c.device_type, c.dims, c.device_ids)
+
+    run()
+    assert case["n"] >= 10
+
+
+def test_random_shard_plans_cover_every_column_once_and_survive_the_file_format(ffemb, tmp_path):
+    from hypothesis import given, settings, strategies as st, HealthCheck
+    S = ffemb.sharding
+    case = {"n": 0}
+
+    @settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+    @given(st.lists(st.tuples(st.integers(1, 50_000_000), st.integers(1, 64)), min_size=1, max_size=30),
+           st.sampled_from([16, 32, 64, 128, 256]), st.sampled_from([1, 2, 3, 4, 8]),
+           st.sampled_from(["balanced", "modulo"]), st.booleans(), st.integers(1, 3))
+    def run(tables, dim, world, kind, split, groups):
+        case["n"] += 1
+        rows, bags = [r for r, _ in tables], [l for _, l in tables]
+        parts = S.plan_shards(rows, bags, dim, world, kind, split, groups)
+        _check_plan(S, parts, rows, dim, world)
+        assert all(0 <= p.group < S.num_groups(parts) for p in parts)
+        if not split or kind == "modulo":
+            assert all(p.width == dim for p in parts)
+        if kind == "modulo":
+            assert [p.rank for p in sorted(parts, key=lambda p: p.table)] == [t % world for t in range(len(rows))]
+        path = str(tmp_path / f"p{case['n']}.strategy")
+        S.write_strategy(path, S.plan_strategy(parts, world))
+        back = S.parts_from_strategy(S.read_strategy(path), len(rows), dim)
+        key = lambda p: (p.table, p.col0, p.width, p.rank)
+        assert sorted(map(key, back)) == sorted(map(key, parts))
+
+    run()
+    assert case["n"] >= 10
