@@ -126,3 +126,35 @@ def test_header_is_plain_c_and_struct_layouts_match_the_ctypes_mirror(ffemb, tmp
     assert int(out["row_stride"]) == B.ffemb_exchange_t.row_stride.offset
     assert int(out["samples_per_peer"]) == B.ffemb_route_t.samples_per_peer.offset
     assert int(out["cap"]) == int(B.lib().ffemb_static_scratch_bytes())
+
+
+def test_rowwise_route_and_padded_backward_validate_before_touching_a_device(ffemb):
+    import ctypes as C
+    L, b = ffemb.lib(), ffemb.binding
+    tabs = (b.ffemb_table_t * 1)()
+    tabs[0].idx, tabs[0].R, tabs[0].L, tabs[0].reserved = 64, 1000, 2, 0
+    rt = b.ffemb_route_t()
+    rt.num_peers, rt.rank, rt.samples_per_peer = 2, 0, 8
+    # NULL peer buffers
+    assert L.ffemb_rowwise_route(tabs, 1, 16, 8, 256, 16, C.byref(rt), None) == 1 and b"peer_slots" in L.ffemb_last_error()
+    for h in range(2):
+        rt.peer_slots[h], rt.peer_rows[h] = 1024, 4096
+    assert L.ffemb_rowwise_route(tabs, 1, 16, 9, 256, 16, C.byref(rt), None) == 1      # more samples than a peer's block
+    assert L.ffemb_rowwise_route(tabs, 1, 18, 8, 256, 20, C.byref(rt), None) == 1      # D not a multiple of 4
+    assert L.ffemb_rowwise_route(tabs, 1, 16, 8, 260, 16, C.byref(rt), None) == 1      # dx misaligned
+    assert L.ffemb_rowwise_route(tabs, 1, 16, 8, 256, 8, C.byref(rt), None) == 1       # row_stride < D
+    rt.rank = 2
+    assert L.ffemb_rowwise_route(tabs, 1, 16, 8, 256, 16, C.byref(rt), None) == 1      # rank outside the peer set
+    rt.rank = 1
+    tabs[0].reserved = 4
+    assert L.ffemb_rowwise_route(tabs, 1, 16, 8, 256, 16, C.byref(rt), None) == 1      # block past the row
+    tabs[0].reserved, tabs[0].R = 0, 0
+    assert L.ffemb_rowwise_route(tabs, 1, 16, 8, 256, 16, C.byref(rt), None) == 1      # rows of the whole table unknown
+    tabs[0].R = 1000
+    assert L.ffemb_rowwise_route(tabs, 1, 16, 0, None, 16, C.byref(rt), None) == 0     # no samples: nothing launched
+    assert L.ffemb_rowwise_route(tabs, 1, 16, 8, 256, 16, None, None) == 1
+    # the owner's side: same workspace contract as every batched backward
+    tabs[0].out, tabs[0].table = 256, 512
+    assert L.ffemb_backward_sgd_padded(tabs, 1, 16, 8, ffemb.AGGR_MODE_SUM, 0.01, None, 0, None) == 3
+    assert b"workspace" in L.ffemb_last_error()
+    assert L.ffemb_backward_sgd_padded(tabs, 1, 16, 8, ffemb.AGGR_MODE_NONE, 0.01, None, 0, None) == 1
