@@ -271,12 +271,15 @@ def plan_shards(rows, bags, dim, world, kind="balanced", split=True, groups=1, h
         cost = lambda p: part_cost(rows[p.table], bags[p.table], dim, p.width)
         mean = sum(cost(p) for p in parts) / world
         if split:
+            pieces = [1] * T  # a table is never cut into more parts than there are ranks to hold them
             for _ in range(2):  # halves, then quarters
                 nxt = []
                 for p in parts:
-                    if cost(p) > 0.75 * mean and p.width % 8 == 0 and p.width >= 32:
+                    if (cost(p) > 0.75 * mean and p.width % 8 == 0 and p.width >= 32
+                            and pieces[p.table] < world):
                         h = p.width // 2
                         nxt += [Part(p.table, p.col0, h, 0), Part(p.table, p.col0 + h, h, 0)]
+                        pieces[p.table] += 1
                     else:
                         nxt.append(p)
                 parts = nxt
@@ -317,29 +320,43 @@ def num_groups(parts):
 
 def plan_strategy(parts, world):
     """The plan in the reference's strategy-file vocabulary (write_strategy): a whole table is
-    "embedding<i>" with a [1,1] grid on its GPU; a table split into c column parts is a [c,1] grid —
-    dim[0] is the feature dimension (/root/reference/src/runtime/model.cc:726-736) — whose device ids
-    are the parts' ranks in column order.  (The reference's Embedding refuses such a grid,
-    src/ops/embedding.cu:84-85: the file is then only readable by this library's planner.)"""
+    "embedding<i>" with a [1,1] grid on its GPU; a table split by columns is a [c,1] grid — dim[0] is the
+    feature dimension (/root/reference/src/runtime/model.cc:726-736) — of c = dim / (narrowest part)
+    equal cells whose device ids are the parts' ranks in column order, a part twice as wide as the
+    narrowest one filling two neighbouring cells (a half next to two quarters: [4,1], ids a a b c).
+    (The reference's Embedding refuses such a grid, src/ops/embedding.cu:84-85: the file is then only
+    readable by this library's planner.)"""
     s = {}
     by_table = {}
     for p in parts:
         by_table.setdefault(p.table, []).append(p)
     for t, ps in by_table.items():
         ps = sorted(ps, key=lambda p: p.col0)
-        s[f"embedding{t}"] = ParallelConfig(DEVICE_GPU, [len(ps), 1], [int(p.rank) for p in ps])
+        cell = min(p.width for p in ps)
+        if any(p.width % cell or p.col0 % cell for p in ps):
+            raise ValueError(f"embedding{t}: column parts are not multiples of the narrowest one")
+        ids = [int(p.rank) for p in ps for _ in range(p.width // cell)]
+        s[f"embedding{t}"] = ParallelConfig(DEVICE_GPU, [len(ids), 1], ids)
     s["concat"] = ParallelConfig(DEVICE_GPU, [1, world], list(range(world)))
     return s
 
 
 def parts_from_strategy(strategies, num_tables, dim):
-    """Inverse of plan_strategy (groups are not part of the file: all 0)."""
+    """Inverse of plan_strategy (groups are not part of the file: all 0): neighbouring cells of one
+    table on the same GPU are one part."""
     parts = []
     for t in range(num_tables):
         c = strategies[f"embedding{t}"]
-        n = c.dims[0]
-        if c.device_type != DEVICE_GPU or len(c.dims) != 2 or c.dims[1] != 1 or dim % n != 0:
+        n = c.dims[0] if c.dims else 0
+        if c.device_type != DEVICE_GPU or len(c.dims) != 2 or c.dims[1] != 1 or n < 1 or dim % n != 0 \
+                or len(c.device_ids) != n:
             raise ValueError(f"embedding{t}: expected a [c,1] grid on GPUs with c dividing the row width")
         w = dim // n
-        parts += [Part(t, i * w, w, int(c.device_ids[i])) for i in range(n)]
+        i = 0
+        while i < n:
+            j = i
+            while j + 1 < n and c.device_ids[j + 1] == c.device_ids[i]:
+                j += 1
+            parts.append(Part(t, i * w, (j - i + 1) * w, int(c.device_ids[i])))
+            i = j + 1
     return parts

@@ -340,3 +340,20 @@ def test_random_shard_plans_cover_every_column_once_and_survive_the_file_format(
 
     run()
     assert case["n"] >= 10
+
+
+def test_plan_never_cuts_a_table_into_more_parts_than_ranks_and_files_hold_uneven_cuts(ffemb, tmp_path):
+    """Found by the property test above: one heavy table on 2 ranks used to be cut into quarters, two of
+    them on each rank (the unsplit half again, with a second index sort); on 3 ranks the cut is a half
+    next to two quarters, which the [c,1] grid of the file holds as 4 cells a a b c."""
+    S = ffemb.sharding
+    two = S.plan_shards([1], [1], 64, 2, "balanced", True, 1)
+    assert sorted((p.col0, p.width, p.rank) for p in two) == [(0, 32, 0), (32, 32, 1)]
+    three = S.plan_shards([1], [1], 64, 3, "balanced", True, 1)
+    assert sorted(p.width for p in three) == [16, 16, 32] and len({p.rank for p in three}) == 3
+    st = S.plan_strategy(three, 3)
+    assert st["embedding0"].dims == [4, 1] and len(set(st["embedding0"].device_ids)) == 3
+    path = str(tmp_path / "uneven.strategy")
+    S.write_strategy(path, st)
+    key = lambda p: (p.table, p.col0, p.width, p.rank)
+    assert sorted(map(key, S.parts_from_strategy(S.read_strategy(path), 1, 64))) == sorted(map(key, three))
