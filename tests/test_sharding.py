@@ -297,7 +297,7 @@ def test_random_strategy_files_round_trip_and_load_in_the_reference(ffemb, oracl
 
     case = {"n": 0}
 
-    @settings(max_examples=40, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+    @settings(max_examples=40, deadline=None, derandomize=True, suppress_health_check=[HealthCheck.function_scoped_fixture])
     @given(st.dictionaries(name, config(), min_size=1, max_size=12))
     def run(strategies):
         case["n"] += 1
@@ -318,7 +318,7 @@ def test_random_shard_plans_cover_every_column_once_and_survive_the_file_format(
     S = ffemb.sharding
     case = {"n": 0}
 
-    @settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+    @settings(max_examples=60, deadline=None, derandomize=True, suppress_health_check=[HealthCheck.function_scoped_fixture])
     @given(st.lists(st.tuples(st.integers(1, 50_000_000), st.integers(1, 64)), min_size=1, max_size=30),
            st.sampled_from([16, 32, 64, 128, 256]), st.sampled_from([1, 2, 3, 4, 8]),
            st.sampled_from(["balanced", "modulo"]), st.booleans(), st.integers(1, 3))
