@@ -128,6 +128,18 @@ class Embedding:
                                        float(lr), ws.data_ptr(), ws.numel(), _stream_ptr(stream)))
         return weight
 
+    def backward_sgd_static(self, input, output_grad, weight, lr, stream=None):
+        """backward_sgd with the scratch in the library's file-scope device array (ffemb_backward_sgd_static,
+        no counterpart in the reference): nothing is allocated — no workspace tensor either — so it can be
+        called where allocation is forbidden.  Shapes beyond FFEMB_STATIC_SCRATCH_BYTES raise FFEmbError
+        (FFEMB_EWORKSPACE); calls that overlap on one device race."""
+        Bsz, L = self._shapes(input, weight)
+        _req(output_grad, torch.float32, "output_grad")
+        check(lib().ffemb_backward_sgd_static(input.data_ptr(), output_grad.data_ptr(), weight.data_ptr(),
+                                              L, self.out_channels, Bsz, self.num_entries, self.aggr,
+                                              float(lr), _stream_ptr(stream)))
+        return weight
+
 
 class EmbeddingCollection:
     """All tables that live on one GPU, driven through the table-batched entry points."""
