@@ -25,8 +25,9 @@
 // FFEmbGroupExchange kept next to the meta — see ffemb_embedding_group_forward_exchange_task.
 //
 // Launcher side (what replaces Embedding::create_weights / forward() / backward() for the ops of a
-// group; Legion itself is absent from the reference checkout, so these are compile- and link-checked
-// only — the leaf bodies above are what the GPU tests drive):
+// group; Legion itself is absent from the reference checkout: the three group launchers are run on the CPU
+// against the stand-in's recording Runtime, tests/test_dropin_launchers.py, create_weights is compile- and
+// link-checked only — the leaf bodies above are what the GPU tests drive):
 //   ffemb_fused_create_weights   src/ops/embedding.cu:58-74   create_grad = false, ParameterSyncType::NONE
 //   ffemb_group_forward          src/ops/embedding.cu:274-306 one launch for the group, no MAP_TO_ZC_MEMORY
 //   ffemb_group_prepare          (new) the index sort, launched right after the forward
@@ -209,7 +210,7 @@ void ffemb_embedding_group_forward_exchange_task(const Task *task, const std::ve
   die_unless_ok(ffemb_sync_signal(&ex->sync, 0, s), "ffemb_sync_signal");
 }
 
-// ---- launcher side (compile- and link-checked; see the header comment) -----------------------------
+// ---- launcher side (see the header comment) --------------------------------------------------------
 // The ops of one GPU.  `meta` is the OpMeta* the FIRST op's init_task made on that GPU (Op::meta[0] of
 // a [1,1] grid): its FFHandler carries the GPU's workSpace.
 struct FFEmbGroup {

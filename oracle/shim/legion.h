@@ -336,15 +336,28 @@ public:
   void add_field(unsigned idx, FieldID f) { region_requirements[idx].add_field(f); }
   void add_future(const Future &f) { futures.push_back(f); }
 };
+/* An index launch keeps what it was built from, so that a test can look at it (Runtime's launch hook
+ * below): task id, launch domain, the by-value argument, the per-point arguments, mapper id and tag. */
 class IndexLauncher {
 public:
   std::vector<RegionRequirement> region_requirements;
   std::vector<Future> futures;
-  IndexLauncher() {}
-  IndexLauncher(TaskID, const IndexSpace &, TaskArgument, const ArgumentMap &,
-                Predicate = Predicate(), bool = false, MapperID = 0, MappingTagID = 0) {}
-  IndexLauncher(TaskID, const Domain &, TaskArgument, const ArgumentMap &,
-                Predicate = Predicate(), bool = false, MapperID = 0, MappingTagID = 0) {}
+  TaskID task_id;
+  Domain launch_domain;
+  TaskArgument global_arg;
+  ArgumentMap argument_map;
+  bool must_parallelism;
+  MapperID map_id;
+  MappingTagID tag;
+  IndexLauncher() : task_id(0), must_parallelism(false), map_id(0), tag(0) {}
+  IndexLauncher(TaskID tid, const IndexSpace &space, TaskArgument arg, const ArgumentMap &map,
+                Predicate = Predicate(), bool must = false, MapperID mid = 0, MappingTagID t = 0)
+      : task_id(tid), launch_domain(space.dom), global_arg(arg), argument_map(map), must_parallelism(must),
+        map_id(mid), tag(t) {}
+  IndexLauncher(TaskID tid, const Domain &dom, TaskArgument arg, const ArgumentMap &map,
+                Predicate = Predicate(), bool must = false, MapperID mid = 0, MappingTagID t = 0)
+      : task_id(tid), launch_domain(dom), global_arg(arg), argument_map(map), must_parallelism(must),
+        map_id(mid), tag(t) {}
   void add_region_requirement(const RegionRequirement &r) { region_requirements.push_back(r); }
   void add_field(unsigned idx, FieldID f) { region_requirements[idx].add_field(f); }
   void add_future(const Future &f) { futures.push_back(f); }
@@ -355,12 +368,20 @@ public:
   InlineLauncher(const RegionRequirement &) {}
 };
 
+/* Launches go nowhere (there is no scheduler here) unless a test installs a hook that looks at them. */
 class Runtime {
 public:
+  typedef void (*IndexLaunchHook)(void *user, const IndexLauncher &launcher);
+  IndexLaunchHook index_launch_hook;
+  void *index_launch_user;
+  Runtime() : index_launch_hook(NULL), index_launch_user(NULL) {}
   Domain get_index_space_domain(Context, const IndexSpace &s) { return s.dom; }
   Domain get_index_space_domain(const IndexSpace &s) { return s.dom; }
   Domain get_index_partition_color_space(Context, const IndexPartition &p) { return p.color_space; }
-  FutureMap execute_index_space(Context, const IndexLauncher &) { return FutureMap(); }
+  FutureMap execute_index_space(Context, const IndexLauncher &l) {
+    if (index_launch_hook) index_launch_hook(index_launch_user, l);
+    return FutureMap();
+  }
   Future execute_task(Context, const TaskLauncher &) { return Future(); }
   void begin_trace(Context, TraceID) {}
   void end_trace(Context, TraceID) {}

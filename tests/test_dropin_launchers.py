@@ -1,0 +1,91 @@
+"""CPU test of the LAUNCHER side of the fast path behind Legion:
+ffemb_group_forward / ffemb_group_prepare / ffemb_group_backward_sgd of
+dlrm-flexflow_b200/csrc/flexflow/embedding_group_ffemb.cu — what replaces Embedding::forward() / backward()
+(/root/reference/src/ops/embedding.cu:274-306, 356-388) for the tables of one GPU — compiled against the
+reference's own headers and run against a Legion stand-in that writes the index launch down
+(oracle/shim/legion.h: Runtime::index_launch_hook; oracle/ref_glue_gpu.cu: ffdropin_group_launch_record).
+
+Nothing is launched and no device is touched (the pointers below are just numbers).  What is held: the task
+id, the single launch point of the table-wise [1,1] grid, the by-value arguments (table count, learning rate
+taken from the SGD optimizer, prepared flag), the per-point OpMeta*, and per table the region requirements
+in the order, privilege and field the leaf bodies read them — and that the (pointer, rectangle) frame made
+from those requirements is the very frame the GPU tests hand the leaf bodies through
+ffdropin_gpu_group_task (test_dropin_group_leaf_tasks_match_reference_per_table_tasks)."""
+import numpy as np
+import pytest
+
+
+@pytest.fixture(scope="module")
+def rec(oracle):
+    if not oracle.dropin_gpu_available():
+        pytest.skip("oracle/_ref/libffdropin_gpu.so not built (needs /root/reference)")
+    try:
+        oracle.dropin_gpu()
+    except OSError as e:  # CUDA runtime libraries absent on this host
+        pytest.skip(f"libffdropin_gpu.so does not load here: {e}")
+    return oracle.dropin_group_launch_record
+
+
+BAGS, ROWS, D, B = [3, 1, 20, 7], [1000, 7, 40_000_000, 155], 128, 65536
+IDX = [0x10000 * (t + 1) for t in range(4)]
+OUT = [0x20000000 + 0x10000 * t for t in range(4)]
+TAB = [0x7F0000000000 + 0x100000000 * t for t in range(4)]
+
+
+def _common(r, n):
+    c = r["consts"]
+    assert r["points"] == 1 and r["point_args"] == 1          # one point: the [1,1] grid of the table-wise strategy
+    assert r["local_arg_is_lead_meta"] and r["local_arglen"] == 8
+    assert not r["must"] and r["mapper_id"] == 0
+    assert r["args"]["len"] == 16 and r["args"]["num_tables"] == n and r["args"]["parity"] == 0
+    for q in r["reqs"]:
+        assert q["coherence"] == c["EXCLUSIVE"] and q["fields"] == [c["FID_DATA"]]
+        # the reference maps the embedding output / output-grad to zero-copy host memory
+        # (src/ops/embedding.cu:296-298, 378-380); the fused mode keeps them in framebuffer memory
+        assert q["tag"] != c["MAP_TO_ZC_MEMORY"] and q["tag"] == 0
+    return c
+
+
+def test_group_forward_launcher(rec):
+    r = rec(0, IDX, OUT, TAB, BAGS, D, B, ROWS)
+    c = _common(r, 4)
+    assert r["task_id"] == c["TASK_FORWARD"] and len(r["reqs"]) == 12
+    for t in range(4):
+        i, o, w = r["reqs"][3 * t:3 * t + 3]
+        assert (i["privilege"], i["base"], i["extent"]) == (c["READ_ONLY"], IDX[t], (BAGS[t], B))
+        assert (o["privilege"], o["base"], o["extent"]) == (c["WRITE_ONLY"], OUT[t], (D, B))
+        assert (w["privilege"], w["base"], w["extent"]) == (c["READ_ONLY"], TAB[t], (ROWS[t], D))
+
+
+def test_group_prepare_launcher_lists_indices_and_tables_only(rec):
+    r = rec(1, IDX, None, TAB, BAGS, D, B, ROWS)
+    c = _common(r, 4)
+    assert r["task_id"] == c["TASK_PREPARE"] and len(r["reqs"]) == 8
+    for t in range(4):
+        i, w = r["reqs"][2 * t:2 * t + 2]
+        assert (i["privilege"], i["base"], i["extent"]) == (c["READ_ONLY"], IDX[t], (BAGS[t], B))
+        assert (w["privilege"], w["base"], w["extent"]) == (c["READ_ONLY"], TAB[t], (ROWS[t], D))
+
+
+@pytest.mark.parametrize("prepared", [False, True])
+def test_group_backward_launcher_updates_the_table_in_place(rec, prepared):
+    r = rec(2, IDX, OUT, TAB, BAGS, D, B, ROWS, lr=0.01, prepared=prepared)
+    c = _common(r, 4)
+    assert r["task_id"] == c["TASK_BACKWARD_SGD"] and len(r["reqs"]) == 12
+    # SGDOptimizer::lr is a double (include/optimizer.h:55); the task gets it as the float sgd_update takes
+    assert r["args"]["lr"] == float(np.float32(0.01)) and r["args"]["prepared"] == int(prepared)
+    for t in range(4):
+        i, g, w = r["reqs"][3 * t:3 * t + 3]
+        assert (i["privilege"], i["base"], i["extent"]) == (c["READ_ONLY"], IDX[t], (BAGS[t], B))
+        assert (g["privilege"], g["base"], g["extent"]) == (c["READ_ONLY"], OUT[t], (D, B))
+        # region 2 is the TABLE, read-write — the reference lists the weight-GRAD here
+        # (src/ops/embedding.cu:384-385) and leaves the update to SGDOptimizer::update
+        assert (w["privilege"], w["base"], w["extent"]) == (c["READ_WRITE"], TAB[t], (ROWS[t], D))
+
+
+def test_one_table_groups_and_task_ids_are_the_custom_gpu_ids(rec):
+    r = rec(0, IDX[:1], OUT[:1], TAB[:1], BAGS[:1], 16, 7, ROWS[:1])
+    c = _common(r, 1)
+    assert len(r["reqs"]) == 3 and r["reqs"][1]["extent"] == (16, 7)
+    # include/model.h keeps CUSTOM_GPU_TASK_ID_1.. free for this; three distinct consecutive ids
+    assert c["TASK_PREPARE"] == c["TASK_FORWARD"] + 1 and c["TASK_BACKWARD_SGD"] == c["TASK_FORWARD"] + 2
