@@ -26,8 +26,8 @@
 //
 // Launcher side (what replaces Embedding::create_weights / forward() / backward() for the ops of a
 // group; Legion itself is absent from the reference checkout: the three group launchers are run on the CPU
-// against the stand-in's recording Runtime, tests/test_dropin_launchers.py, create_weights is compile- and
-// link-checked only — the leaf bodies above are what the GPU tests drive):
+// against the stand-in's recording Runtime, and create_weights against a recording FFModel next to the
+// reference's own (tests/test_dropin_launchers.py) — the leaf bodies above are what the GPU tests drive):
 //   ffemb_fused_create_weights   src/ops/embedding.cu:58-74   create_grad = false, ParameterSyncType::NONE
 //   ffemb_group_forward          src/ops/embedding.cu:274-306 one launch for the group, no MAP_TO_ZC_MEMORY
 //   ffemb_group_prepare          (new) the index sort, launched right after the forward

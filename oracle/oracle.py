@@ -422,3 +422,20 @@ def dropin_group_launch_record(what, idx_ptrs, out_ptrs, W_ptrs, bags, D, B, row
                 consts=dict(READ_ONLY=r[14], WRITE_ONLY=r[15], READ_WRITE=r[16], EXCLUSIVE=r[17], FID_DATA=r[18],
                             MAP_TO_ZC_MEMORY=r[19], TASK_FORWARD=r[20], TASK_PREPARE=r[21], TASK_BACKWARD_SGD=r[22]),
                 reqs=reqs)
+
+
+def create_weights_record(which, name="embedding3", rows=1000, dim=64):
+    """Weight creation written down (ref_glue_gpu.cu, ffref_create_weights_record): which = "reference" runs
+    the reference's own Embedding::create_weights (src/ops/embedding.cu:58-74, libffref_gpu.so), "fused" the
+    drop-in's ffemb_fused_create_weights (libffdropin_gpu.so).  No device is touched."""
+    L = ref_gpu() if which == "reference" else dropin_gpu()
+    L.ffref_create_weights_record.argtypes = [C.c_char_p, _int, _int, C.POINTER(C.c_int64), C.c_char_p]
+    L.ffref_create_weights_record.restype = _int
+    rec = (C.c_int64 * 16)()
+    buf = C.create_string_buffer(64)
+    assert L.ffref_create_weights_record(name.encode(), int(rows), int(dim), rec, buf) == 16
+    r = list(rec)
+    return dict(task_is_calls=r[0], task_is_dims=r[1], weight_calls=r[2], dims=(r[3], r[4]), data_type=r[5],
+                create_grad=bool(r[6]), sync_type=r[7], op_is_this=bool(r[8]), initializer_is_ops=bool(r[9]),
+                consts=dict(DT_FLOAT=r[10], NONE=r[11], PS=r[12], NCCL=r[13]), task_points=r[14],
+                weight_num_dim=r[15], task_is_name=buf.value.decode())

@@ -37,7 +37,19 @@
 /* ---- link-time leftovers (never executed on this path) ---------------------------------- */
 OpMeta::OpMeta(FFHandler _handle) : handle(_handle), profiling(false) {}
 Tensor::Tensor() { numDim = 0; owner_op = NULL; owner_idx = 0; }
-Tensor &Tensor::operator=(const Tensor &) { FFREF_DEAD("Tensor::operator="); }
+/* (plain member-wise assignment, as src/runtime/model.cc:46-61 does it: needed by the weight-creation
+ * record below, where `weights[0] = model.create_linear_weight(...)` assigns a Parameter) */
+Tensor &Tensor::operator=(const Tensor &o) {
+  if (this == &o) return *this;
+  numDim = o.numDim;
+  memcpy(adim, o.adim, sizeof(adim));
+  data_type = o.data_type; sync_type = o.sync_type;
+  owner_op = o.owner_op; owner_idx = o.owner_idx;
+  region = o.region; region_grad = o.region_grad;
+  part = o.part; part_grad = o.part_grad;
+  physical_region = o.physical_region;
+  return *this;
+}
 size_t Tensor::get_volume() const { FFREF_DEAD("Tensor::get_volume"); }
 bool Tensor::get_input_sub_tensor(const ParallelConfig &, Tensor &, OperatorType) {
   FFREF_DEAD("Tensor::get_input_sub_tensor");
@@ -64,12 +76,41 @@ void Op::inner_measure_operator_cost(Simulator *, std::function<void()> const &,
 }
 void *Simulator::allocate(size_t, DataType) { FFREF_DEAD("Simulator::allocate"); }
 void Simulator::free_all() { FFREF_DEAD("Simulator::free_all"); }
-IndexSpace FFModel::get_or_create_task_is(int, const std::string &) { FFREF_DEAD("FFModel"); }
+/* The two FFModel entry points weight creation goes through abort like the rest of the control plane —
+ * unless a test has installed a record (ff*_create_weights_record below): then they write their
+ * arguments down and hand back a [1,1] task space / a bare 2-D parameter. */
+namespace {
+struct WeightsRecord {
+  int task_is_calls, task_is_dims;
+  char task_is_name[MAX_OPNAME];
+  int weight_calls, dims[2], data_type, create_grad, sync_type;
+  const void *op, *initializer;
+};
+WeightsRecord *g_wrec = NULL;
+}  // namespace
+IndexSpace FFModel::get_or_create_task_is(int n, const std::string &name) {
+  if (!g_wrec) FFREF_DEAD("FFModel");
+  g_wrec->task_is_calls++;
+  g_wrec->task_is_dims = n;
+  snprintf(g_wrec->task_is_name, sizeof(g_wrec->task_is_name), "%s", name.c_str());
+  return Legion::IndexSpaceT<2>(Legion::Rect<2>(Legion::Point<2>(0, 0), Legion::Point<2>(0, 0)));
+}
 template <>
 Tensor FFModel::create_tensor<2>(const int *, DataType, const Op *, bool) { FFREF_DEAD("FFModel"); }
 template <>
-Parameter FFModel::create_linear_weight<2, 2>(Op *, const int *, DataType, Initializer *, bool,
-                                              ParameterSyncType) { FFREF_DEAD("FFModel"); }
+Parameter FFModel::create_linear_weight<2, 2>(Op *op, const int *dims, DataType dt, Initializer *init,
+                                              bool create_grad, ParameterSyncType sync) {
+  if (!g_wrec) FFREF_DEAD("FFModel");
+  g_wrec->weight_calls++;
+  g_wrec->dims[0] = dims[0]; g_wrec->dims[1] = dims[1];
+  g_wrec->data_type = (int)dt; g_wrec->create_grad = create_grad; g_wrec->sync_type = (int)sync;
+  g_wrec->op = op; g_wrec->initializer = init;
+  Parameter p;
+  p.numDim = 2;
+  p.adim[0] = dims[1]; p.adim[1] = dims[0];  /* [num_entries][out_channels], like Embedding's ctor */
+  p.data_type = dt; p.sync_type = sync; p.owner_op = op;
+  return p;
+}
 template <>
 void FFModel::create_disjoint_partition<2>(const Tensor &, const IndexSpaceT<2> &,
                                            LogicalPartition &, LogicalPartition &) {
@@ -139,6 +180,7 @@ void ffemb_embedding_group_backward_sgd_task(const Legion::Task *, const std::ve
                                              Legion::Context, Legion::Runtime *);
 /* ... and the launcher side of the same file (what replaces Embedding::forward() / backward()) */
 struct FFEmbGroup { std::vector<Embedding *> ops; };
+void ffemb_fused_create_weights(Embedding *op, FFModel &model);
 void ffemb_group_forward(const FFModel &ff, const FFEmbGroup &g);
 void ffemb_group_prepare(const FFModel &ff, const FFEmbGroup &g);
 void ffemb_group_backward_sgd(const FFModel &ff, const FFEmbGroup &g, bool prepared);
@@ -319,6 +361,42 @@ int ffdropin_group_launch_record(int what, int n, void *const *idx, void *const 
   return R.n;
 }
 #endif
+
+/* Weight creation, written down: libffref_gpu.so runs the reference's own Embedding::create_weights
+ * (src/ops/embedding.cu:58-74), libffdropin_gpu.so the fused mode's ffemb_fused_create_weights, both on
+ * an op with `rows` entries of `dim` floats named `name`; FFModel's two entry points record what they
+ * were asked for.  rec: [0] get_or_create_task_is calls [1] its dimension argument
+ *   [2] create_linear_weight calls [3] dims[0] [4] dims[1] [5] data type [6] create_grad [7] sync type
+ *   [8] 1 if the op passed is this op [9] 1 if the initializer passed is the op's kernel_initializer
+ *   [10] DT_FLOAT [11..13] ParameterSyncType NONE / PS / NCCL [14] points of op->task_is afterwards
+ *   [15] weights[0].numDim afterwards.  name_out (MAX_OPNAME bytes): the name the task space was asked by. */
+int ffref_create_weights_record(const char *name, int rows, int dim, int64_t *rec, char *name_out) {
+  std::vector<char> ff_store(sizeof(FFModel) + alignof(FFModel), 0), op_store(sizeof(Embedding) + alignof(Embedding), 0);
+  FFModel &ff = *(FFModel *)(((uintptr_t)ff_store.data() + alignof(FFModel) - 1) / alignof(FFModel) * alignof(FFModel));
+  Embedding *op = (Embedding *)(((uintptr_t)op_store.data() + alignof(Embedding) - 1) / alignof(Embedding) * alignof(Embedding));
+  snprintf(op->name, sizeof(op->name), "%s", name);
+  op->num_entries = rows;
+  op->out_channels = dim;
+  op->numWeights = 1;
+  op->kernel_initializer = (Initializer *)(uintptr_t)0x1234;  /* only carried */
+  WeightsRecord w;
+  memset(&w, 0, sizeof(w));
+  g_wrec = &w;
+#ifdef FFEMB_DROPIN
+  ffemb_fused_create_weights(op, ff);
+#else
+  op->Embedding::create_weights(ff);
+#endif
+  g_wrec = NULL;
+  rec[0] = w.task_is_calls; rec[1] = w.task_is_dims; rec[2] = w.weight_calls; rec[3] = w.dims[0]; rec[4] = w.dims[1];
+  rec[5] = w.data_type; rec[6] = w.create_grad; rec[7] = w.sync_type; rec[8] = w.op == (const void *)(Op *)op;
+  rec[9] = w.initializer == (const void *)op->kernel_initializer;
+  rec[10] = DT_FLOAT; rec[11] = (int)ParameterSyncType::NONE; rec[12] = (int)ParameterSyncType::PS;
+  rec[13] = (int)ParameterSyncType::NCCL;
+  rec[14] = (int64_t)op->task_is.dom.get_volume(); rec[15] = op->weights[0].numDim;
+  snprintf(name_out, MAX_OPNAME, "%s", w.task_is_name);
+  return 16;
+}
 
 /* Embedding::forward_task (src/ops/embedding.cu:238-272) on device pointers; stream 0
  * (built with DISABLE_LEGION_CUDA_HIJACK, src/runtime/cuda_helper.cu:22-30).               */

@@ -89,3 +89,24 @@ def test_one_table_groups_and_task_ids_are_the_custom_gpu_ids(rec):
     assert len(r["reqs"]) == 3 and r["reqs"][1]["extent"] == (16, 7)
     # include/model.h keeps CUSTOM_GPU_TASK_ID_1.. free for this; three distinct consecutive ids
     assert c["TASK_PREPARE"] == c["TASK_FORWARD"] + 1 and c["TASK_BACKWARD_SGD"] == c["TASK_FORWARD"] + 2
+
+
+def test_fused_create_weights_differs_from_the_reference_in_exactly_two_arguments(oracle, rec):
+    """Embedding::create_weights of the reference (src/ops/embedding.cu:58-74, run here from the reference's
+    own object code) against ffemb_fused_create_weights: same task space (asked for by the op's name, 2-D),
+    same {out_channels, num_entries} fp32 weight with the op's initializer — but no gradient region and no
+    parameter synchronisation, so neither Op::zero_grad nor SGDOptimizer::update nor the gradient
+    all-reduce ever sees the table."""
+    if not oracle.ref_gpu_available():
+        pytest.skip("oracle/_ref/libffref_gpu.so not built")
+    ref = oracle.create_weights_record("reference", "embedding7", rows=39_884_406, dim=128)
+    ours = oracle.create_weights_record("fused", "embedding7", rows=39_884_406, dim=128)
+    c = ref["consts"]
+    for r in (ref, ours):
+        assert r["task_is_calls"] == 1 and r["task_is_dims"] == 2 and r["task_is_name"] == "embedding7"
+        assert r["weight_calls"] == 1 and r["dims"] == (128, 39_884_406) and r["data_type"] == c["DT_FLOAT"]
+        assert r["op_is_this"] and r["initializer_is_ops"] and r["task_points"] == 1 and r["weight_num_dim"] == 2
+    assert ref["create_grad"] is True and ref["sync_type"] in (c["PS"], c["NCCL"])
+    assert ours["create_grad"] is False and ours["sync_type"] == c["NONE"]
+    differ = {k for k in ref if ref[k] != ours[k]}
+    assert differ == {"create_grad", "sync_type"}
