@@ -388,39 +388,43 @@ def dropin_gpu():
         L.ffdropin_gpu_group_task.argtypes = [_int, _int, pp, pp, pp, C.POINTER(C.c_int64), _i64, _i64,
                                               C.POINTER(C.c_int64), _int, _f32, _int]
         L.ffdropin_gpu_group_task.restype = None
-        L.ffdropin_group_launch_record.argtypes = [_int, _int, pp, pp, pp, C.POINTER(C.c_int64), _i64, _i64,
-                                                   C.POINTER(C.c_int64), _int, _f32, _int,
-                                                   C.POINTER(C.c_int64), _int]
-        L.ffdropin_group_launch_record.restype = _int
         _dropin_gpu = L
     return _dropin_gpu
 
 
-def dropin_group_launch_record(what, idx_ptrs, out_ptrs, W_ptrs, bags, D, B, rows, aggr=AGGR_SUM, lr=0.01,
-                               prepared=False):
-    """The launcher side of the per-GPU group tasks (csrc/flexflow/embedding_group_ffemb.cu:
-    ffemb_group_forward / _prepare / _backward_sgd) run against a Legion stand-in that writes the index
-    launch down (ref_glue_gpu.cu, ffdropin_group_launch_record).  Pointers are only carried: no device is
-    touched.  -> dict(task_id, tag, mapper_id, must, points, args=..., local_arg_is_lead_meta, consts=...,
-    reqs=[dict(privilege, coherence, tag, fields, base, extent)])."""
+def launch_record(which, what, idx_ptrs, out_ptrs, W_ptrs, bags, D, B, rows, Wgrad_ptrs=None, aggr=AGGR_SUM,
+                  lr=0.01, prepared=False):
+    """The launcher side run against a Legion stand-in that writes the index launch down (ref_glue_gpu.cu,
+    ffref_launch_record).  which = "fused": the per-GPU group launchers of
+    csrc/flexflow/embedding_group_ffemb.cu (what 0 forward / 1 prepare / 2 backward+SGD, any number of
+    tables); which = "reference": the reference's own Embedding::forward / backward from its object code
+    (what 0 / 2, one table).  Pointers are only carried: no device is touched.
+    -> dict(task_id, tag, mapper_id, must, points, args=..., local_arg_is_lead_meta, consts=...,
+            reqs=[dict(privilege, coherence, tag, fields, base, extent)])."""
     n = len(bags)
+    L = ref_gpu() if which == "reference" else dropin_gpu()
+    pp = C.POINTER(C.c_void_p)
+    L.ffref_launch_record.argtypes = [_int, _int, pp, pp, pp, pp, C.POINTER(C.c_int64), _i64, _i64,
+                                      C.POINTER(C.c_int64), _int, _f32, _int, C.POINTER(C.c_int64), _int]
+    L.ffref_launch_record.restype = _int
     arr = lambda xs: (C.c_void_p * n)(*[int(x) for x in xs]) if xs is not None else None
     i64 = lambda xs: (C.c_int64 * n)(*[int(x) for x in xs])
-    rec = (C.c_int64 * (24 + 8 * 3 * n))()
-    k = dropin_gpu().ffdropin_group_launch_record(int(what), n, arr(idx_ptrs), arr(out_ptrs), arr(W_ptrs), i64(bags),
-                                                  int(D), int(B), i64(rows), int(aggr), float(lr), int(prepared),
-                                                  rec, len(rec))
+    H = 32
+    rec = (C.c_int64 * (H + 8 * 3 * n))()
+    k = L.ffref_launch_record(int(what), n, arr(idx_ptrs), arr(out_ptrs), arr(W_ptrs), arr(Wgrad_ptrs), i64(bags),
+                              int(D), int(B), i64(rows), int(aggr), float(lr), int(prepared), rec, len(rec))
     if k < 0:
-        raise RuntimeError(f"ffdropin_group_launch_record: {k}")
+        raise RuntimeError(f"ffref_launch_record: {k}")
     r = list(rec[:k])
     lr_back = np.array([r[8]], np.int32).view(np.float32)[0]
     reqs = [dict(privilege=e[0], coherence=e[1], tag=e[2], fields=[e[4]] * e[3], base=e[5], extent=(e[6], e[7]))
-            for e in (r[24 + 8 * i:32 + 8 * i] for i in range(r[1]))]
+            for e in (r[H + 8 * i:H + 8 + 8 * i] for i in range(r[1]))]
     return dict(task_id=r[0], tag=r[2], mapper_id=r[3], must=bool(r[4]), points=r[5],
                 args=dict(len=r[6], num_tables=r[7], lr=float(lr_back), prepared=r[9], parity=r[10]),
                 point_args=r[11], local_arg_is_lead_meta=bool(r[12]), local_arglen=r[13],
                 consts=dict(READ_ONLY=r[14], WRITE_ONLY=r[15], READ_WRITE=r[16], EXCLUSIVE=r[17], FID_DATA=r[18],
-                            MAP_TO_ZC_MEMORY=r[19], TASK_FORWARD=r[20], TASK_PREPARE=r[21], TASK_BACKWARD_SGD=r[22]),
+                            MAP_TO_ZC_MEMORY=r[19], TASK_FORWARD=r[20], TASK_PREPARE=r[21], TASK_BACKWARD_SGD=r[22],
+                            EMBED_FWD_TASK_ID=r[23], EMBED_BWD_TASK_ID=r[24]),
                 reqs=reqs)
 
 

@@ -240,22 +240,26 @@ void ffdropin_gpu_group_task(int what, int n, const int64_t *const *idx, float *
 }
 #endif
 
-#ifdef FFEMB_DROPIN
-/* The LAUNCHER side of the per-GPU group tasks (ffemb_group_forward / _prepare / _backward_sgd), driven
- * without Legion and without a GPU: the ops of one GPU are laid out the way FFModel::compile leaves them
- * (a [1,1] task grid, one logical region per input / output / output-grad / table, the op's meta), the
- * launcher runs against a Runtime whose launch hook writes the launch down, and the hook also turns the
- * region requirements into the (Task, PhysicalRegion) frame the leaf task would be handed.  `rec` gets
+/* The LAUNCHER side, driven without Legion and without a GPU.  libffdropin_gpu.so: the per-GPU group
+ * launchers ffemb_group_forward / _prepare / _backward_sgd over `n` tables (what = 0 / 1 / 2);
+ * libffref_gpu.so: the reference's own Embedding::forward / backward (src/ops/embedding.cu:274-306,
+ * 356-388; what = 0 / 2, n = 1) from its object code.  The ops are laid out the way FFModel::compile
+ * leaves them for the table-wise strategy (a [1,1] task grid, one logical region per input / output /
+ * output-grad / table / table-grad, the op's meta), the launcher runs against a Runtime whose launch hook
+ * writes the launch down, and the hook also turns the region requirements into the (pointer, rectangle)
+ * frame a leaf task would be handed.  `rec` gets
  *   [0] task id  [1] #requirements  [2] mapping tag  [3] mapper id  [4] must-parallelism  [5] points
  *   [6] arglen  [7] args.num_tables  [8] bits of args.lr  [9] args.prepared  [10] args.parity
+ *       ([7..10] = 0 for the reference, whose tasks take no by-value argument)
  *   [11] #per-point arguments  [12] 1 if the point's argument is the lead op's OpMeta*  [13] its length
  *   [14..16] READ_ONLY / WRITE_ONLY / READ_WRITE  [17] EXCLUSIVE  [18] FID_DATA  [19] MAP_TO_ZC_MEMORY
- *   [20..22] CUSTOM_GPU_TASK_ID_1..3  [23] 0
+ *   [20..22] CUSTOM_GPU_TASK_ID_1..3  [23] EMBED_FWD_TASK_ID  [24] EMBED_BWD_TASK_ID  [25..31] 0
  *   then per requirement: privilege, coherence, tag, #fields, field, base pointer, extent 0, extent 1
- * — the last three being exactly what ffdropin_gpu_group_task's hand-made frames give the leaf bodies
- * in the GPU tests.  Returns the number of entries written, < 0 on error.  Nothing is launched and no
- * device memory is touched: the pointers are only carried.                                        */
+ * — the last three being what the hand-made frames of ffref_gpu_*_task / ffdropin_gpu_group_task give the
+ * leaf bodies in the GPU tests.  Returns the number of entries written, < 0 on error.  Nothing is
+ * launched and no device memory is touched: the pointers are only carried.                        */
 namespace {
+enum { kRecHead = 32 };
 struct LaunchRecord {
   int64_t *rec;
   int max_rec, n;
@@ -264,25 +268,32 @@ struct LaunchRecord {
 };
 void record_index_launch(void *user, const Legion::IndexLauncher &l) {
   LaunchRecord &R = *(LaunchRecord *)user;
-  const int need = 24 + 8 * (int)l.region_requirements.size();
-  if (need > R.max_rec || l.global_arg.len != sizeof(FFEmbGroupArgs)) { R.n = -2; return; }
-  const FFEmbGroupArgs &a = *(const FFEmbGroupArgs *)l.global_arg.ptr;
+  const int need = kRecHead + 8 * (int)l.region_requirements.size();
+  if (need > R.max_rec) { R.n = -2; return; }
   int64_t *r = R.rec;
+  for (int i = 0; i < kRecHead; i++) r[i] = 0;
   r[0] = l.task_id; r[1] = (int64_t)l.region_requirements.size(); r[2] = (int64_t)l.tag; r[3] = l.map_id;
   r[4] = l.must_parallelism; r[5] = (int64_t)l.launch_domain.get_volume();
-  r[6] = (int64_t)l.global_arg.len; r[7] = a.num_tables;
-  int32_t lr_bits; memcpy(&lr_bits, &a.lr, 4);
-  r[8] = lr_bits; r[9] = a.prepared; r[10] = a.parity;
-  r[11] = (int64_t)l.argument_map.m.size();
-  r[12] = 0; r[13] = 0;
-  if (!l.argument_map.m.empty()) {
-    const Legion::TaskArgument &pa = l.argument_map.m.begin()->second;
-    r[13] = (int64_t)pa.len;
-    r[12] = pa.len == sizeof(OpMeta *) && *(OpMeta *const *)pa.ptr == R.lead_meta;
+  r[6] = (int64_t)l.global_arg.len;
+#ifdef FFEMB_DROPIN
+  if (l.global_arg.len != sizeof(FFEmbGroupArgs)) { R.n = -5; return; }
+  const FFEmbGroupArgs &a = *(const FFEmbGroupArgs *)l.global_arg.ptr;
+  int32_t lr_bits;
+  memcpy(&lr_bits, &a.lr, 4);
+  r[7] = a.num_tables; r[8] = lr_bits; r[9] = a.prepared; r[10] = a.parity;
+#endif
+  r[11] = (int64_t)l.argument_map.size();
+  if (!l.argument_map.bytes.empty()) {
+    const std::vector<char> &pa = l.argument_map.bytes.begin()->second;
+    r[13] = (int64_t)pa.size();
+    OpMeta *given = NULL;
+    if (pa.size() == sizeof(OpMeta *)) memcpy(&given, pa.data(), sizeof(given));
+    r[12] = given == R.lead_meta;
   }
   r[14] = Legion::READ_ONLY; r[15] = Legion::WRITE_ONLY; r[16] = Legion::READ_WRITE; r[17] = Legion::EXCLUSIVE;
   r[18] = FID_DATA; r[19] = (int64_t)MAP_TO_ZC_MEMORY;
-  r[20] = CUSTOM_GPU_TASK_ID_1; r[21] = CUSTOM_GPU_TASK_ID_2; r[22] = CUSTOM_GPU_TASK_ID_3; r[23] = 0;
+  r[20] = CUSTOM_GPU_TASK_ID_1; r[21] = CUSTOM_GPU_TASK_ID_2; r[22] = CUSTOM_GPU_TASK_ID_3;
+  r[23] = EMBED_FWD_TASK_ID; r[24] = EMBED_BWD_TASK_ID;
   /* the frame: one PhysicalRegion per requirement — the single colour of a [1,1] partition is the whole
    * parent region — with the pointer the region was registered with */
   std::vector<Legion::PhysicalRegion> regions;
@@ -292,7 +303,7 @@ void record_index_launch(void *user, const Legion::IndexLauncher &l) {
     if (it == R.base_of->end()) { R.n = -3; return; }
     regions.push_back(Legion::PhysicalRegion(it->second, q.parent.get_index_space().dom));
     const Legion::Domain &d = regions.back().dom;
-    int64_t *e = r + 24 + 8 * i;
+    int64_t *e = r + kRecHead + 8 * i;
     e[0] = q.privilege; e[1] = q.prop; e[2] = (int64_t)q.tag; e[3] = (int64_t)q.privilege_fields.size();
     e[4] = q.privilege_fields.empty() ? -1 : (int64_t)*q.privilege_fields.begin();
     e[5] = (int64_t)(uintptr_t)regions.back().base;
@@ -303,10 +314,13 @@ void record_index_launch(void *user, const Legion::IndexLauncher &l) {
 }
 }  // namespace
 
-int ffdropin_group_launch_record(int what, int n, void *const *idx, void *const *out, void *const *W,
-                                 const int64_t *L, int64_t D, int64_t B, const int64_t *Rows, int aggr, float lr,
-                                 int prepared, int64_t *rec, int max_rec) {
+int ffref_launch_record(int what, int n, void *const *idx, void *const *out, void *const *W, void *const *Wgrad,
+                        const int64_t *L, int64_t D, int64_t B, const int64_t *Rows, int aggr, float lr,
+                        int prepared, int64_t *rec, int max_rec) {
   if (n < 1 || what < 0 || what > 2) return -1;
+#ifndef FFEMB_DROPIN
+  if (n != 1 || what == 1) return -1;  /* the reference launches one op at a time and has no prepare task */
+#endif
   Legion::Runtime runtime;
   Legion::ContextStub ctx;
   /* FFModel and Embedding cannot be constructed here (their constructors belong to the control plane,
@@ -320,7 +334,7 @@ int ffdropin_group_launch_record(int what, int n, void *const *idx, void *const 
   std::map<unsigned, void *> base_of;
   unsigned next_id = 100;
   std::vector<std::vector<char> > op_store(n);
-  FFEmbGroup group;
+  std::vector<Embedding *> ops;
   EmbeddingMeta *meta = make_meta(aggr);
   const Legion::Rect<2> one(Legion::Point<2>(0, 0), Legion::Point<2>(0, 0));
   for (int t = 0; t < n; t++) {
@@ -335,11 +349,12 @@ int ffdropin_group_launch_record(int what, int n, void *const *idx, void *const 
     struct Reg { Legion::LogicalRegion *lr; void *base; int64_t d0, d1; };
     Legion::LogicalPartition part;
     part.ip.color_space = Legion::Domain(one);
-    Reg regs[4] = {{&op->inputs[0].region, idx[t], L[t], B},
+    Reg regs[5] = {{&op->inputs[0].region, idx[t], L[t], B},
                    {&op->outputs[0].region, out ? out[t] : NULL, D, B},
                    {&op->outputs[0].region_grad, out ? out[t] : NULL, D, B},
-                   {&op->weights[0].region, W[t], Rows[t], D}};
-    for (int k = 0; k < 4; k++) {
+                   {&op->weights[0].region, W[t], Rows[t], D},
+                   {&op->weights[0].region_grad, Wgrad ? Wgrad[t] : NULL, Rows[t], D}};
+    for (int k = 0; k < 5; k++) {
       Legion::Rect<2> r(Legion::Point<2>(0, 0), Legion::Point<2>(regs[k].d0 - 1, regs[k].d1 - 1));
       *regs[k].lr = Legion::LogicalRegion(Legion::IndexSpace(Legion::Domain(r)));
       regs[k].lr->id = next_id;
@@ -349,18 +364,26 @@ int ffdropin_group_launch_record(int what, int n, void *const *idx, void *const 
     op->outputs[0].part = part;
     op->outputs[0].part_grad = part;
     op->weights[0].part = part;
-    group.ops.push_back(op);
+    op->weights[0].part_grad = part;
+    ops.push_back(op);
   }
   LaunchRecord R = {rec, max_rec, -4, &base_of, meta};
   runtime.index_launch_hook = record_index_launch;
   runtime.index_launch_user = &R;
+#ifdef FFEMB_DROPIN
+  FFEmbGroup group;
+  group.ops = ops;
   if (what == 0) ffemb_group_forward(ff, group);
   else if (what == 1) ffemb_group_prepare(ff, group);
   else ffemb_group_backward_sgd(ff, group, prepared != 0);
+#else
+  (void)prepared;
+  if (what == 0) ops[0]->Embedding::forward(ff);
+  else ops[0]->Embedding::backward(ff);
+#endif
   delete meta;
   return R.n;
 }
-#endif
 
 /* Weight creation, written down: libffref_gpu.so runs the reference's own Embedding::create_weights
  * (src/ops/embedding.cu:58-74), libffdropin_gpu.so the fused mode's ffemb_fused_create_weights, both on

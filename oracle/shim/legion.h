@@ -302,12 +302,18 @@ public:
   TaskArgument() : ptr(NULL), len(0) {}
   TaskArgument(const void *p, size_t l) : ptr(p), len(l) {}
 };
+/* Like Legion's, the map COPIES the bytes at set_point (the reference's launchers pass the address of a
+ * loop-local OpMeta*, src/ops/embedding.cu:281-284). */
 class ArgumentMap {
 public:
-  std::map<DomainPoint, TaskArgument> m;
+  std::map<DomainPoint, std::vector<char> > bytes;
   template <int N, typename T>
-  void set_point(const Point<N, T> &p, const TaskArgument &a) { m[DomainPoint(p)] = a; }
-  void set_point(const DomainPoint &p, const TaskArgument &a) { m[p] = a; }
+  void set_point(const Point<N, T> &p, const TaskArgument &a) { set_point(DomainPoint(p), a); }
+  void set_point(const DomainPoint &p, const TaskArgument &a) {
+    const char *b = (const char *)a.ptr;
+    bytes[p] = a.len ? std::vector<char>(b, b + a.len) : std::vector<char>();
+  }
+  size_t size() const { return bytes.size(); }
 };
 class Predicate {
 public:

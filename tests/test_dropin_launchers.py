@@ -3,7 +3,8 @@ ffemb_group_forward / ffemb_group_prepare / ffemb_group_backward_sgd of
 dlrm-flexflow_b200/csrc/flexflow/embedding_group_ffemb.cu — what replaces Embedding::forward() / backward()
 (/root/reference/src/ops/embedding.cu:274-306, 356-388) for the tables of one GPU — compiled against the
 reference's own headers and run against a Legion stand-in that writes the index launch down
-(oracle/shim/legion.h: Runtime::index_launch_hook; oracle/ref_glue_gpu.cu: ffdropin_group_launch_record).
+(oracle/shim/legion.h: Runtime::index_launch_hook; oracle/ref_glue_gpu.cu: ffref_launch_record) — and, the same
+way, the reference's own Embedding::forward() / backward() from the reference's object code, side by side.
 
 Nothing is launched and no device is touched (the pointers below are just numbers).  What is held: the task
 id, the single launch point of the table-wise [1,1] grid, the by-value arguments (table count, learning rate
@@ -23,7 +24,7 @@ def rec(oracle):
         oracle.dropin_gpu()
     except OSError as e:  # CUDA runtime libraries absent on this host
         pytest.skip(f"libffdropin_gpu.so does not load here: {e}")
-    return oracle.dropin_group_launch_record
+    return lambda *a, **k: oracle.launch_record("fused", *a, **k)
 
 
 BAGS, ROWS, D, B = [3, 1, 20, 7], [1000, 7, 40_000_000, 155], 128, 65536
@@ -110,3 +111,36 @@ def test_fused_create_weights_differs_from_the_reference_in_exactly_two_argument
     assert ours["create_grad"] is False and ours["sync_type"] == c["NONE"]
     differ = {k for k in ref if ref[k] != ours[k]}
     assert differ == {"create_grad", "sync_type"}
+
+
+def test_group_launchers_against_the_references_own_launchers_table_by_table(oracle, rec):
+    """The reference's Embedding::forward / backward (src/ops/embedding.cu:274-306, 356-388, object code of
+    the reference itself) written down by the same stand-in, one op at a time, against the group launch of
+    the same tables: per table the same regions in the same order with the same privileges and field —
+    except what the fused mode changes on purpose: no MAP_TO_ZC_MEMORY on output / output-grad, and region 2
+    of the backward is the table itself (read-write) where the reference lists the weight-gradient."""
+    if not oracle.ref_gpu_available():
+        pytest.skip("oracle/_ref/libffref_gpu.so not built")
+    GRAD = [0x7E0000000000 + 0x100000000 * t for t in range(4)]
+    fwd = rec(0, IDX, OUT, TAB, BAGS, D, B, ROWS)
+    bwd = rec(2, IDX, OUT, TAB, BAGS, D, B, ROWS)
+    c = fwd["consts"]
+    key = lambda q: (q["privilege"], q["base"], q["extent"], q["fields"], q["coherence"])
+    for t in range(4):
+        one = lambda what: oracle.launch_record("reference", what, IDX[t:t + 1], OUT[t:t + 1], TAB[t:t + 1],
+                                                BAGS[t:t + 1], D, B, ROWS[t:t + 1], Wgrad_ptrs=GRAD[t:t + 1])
+        rf, rb = one(0), one(2)
+        assert rf["task_id"] == c["EMBED_FWD_TASK_ID"] and rb["task_id"] == c["EMBED_BWD_TASK_ID"]
+        for r in (rf, rb):  # one point, the op's OpMeta* per point, no by-value argument
+            assert r["points"] == 1 and r["local_arg_is_lead_meta"] and r["args"]["len"] == 0 and len(r["reqs"]) == 3
+        # forward: identical requirements, but the reference maps the output to zero-copy host memory
+        assert [key(q) for q in rf["reqs"]] == [key(q) for q in fwd["reqs"][3 * t:3 * t + 3]]
+        assert [q["tag"] for q in rf["reqs"]] == [0, c["MAP_TO_ZC_MEMORY"], 0]
+        assert [q["tag"] for q in fwd["reqs"][3 * t:3 * t + 3]] == [0, 0, 0]
+        # backward: regions 0 and 1 identical (tag apart); region 2: weight-grad RW there, the table RW here
+        ours = bwd["reqs"][3 * t:3 * t + 3]
+        assert [key(q) for q in rb["reqs"][:2]] == [key(q) for q in ours[:2]]
+        assert [q["tag"] for q in rb["reqs"]] == [0, c["MAP_TO_ZC_MEMORY"], 0]
+        assert rb["reqs"][2]["privilege"] == ours[2]["privilege"] == c["READ_WRITE"]
+        assert rb["reqs"][2]["extent"] == ours[2]["extent"] == (ROWS[t], D)
+        assert rb["reqs"][2]["base"] == GRAD[t] and ours[2]["base"] == TAB[t]
