@@ -116,7 +116,8 @@ void FFModel::create_disjoint_partition<2>(const Tensor &, const IndexSpaceT<2> 
                                            LogicalPartition &, LogicalPartition &) {
   FFREF_DEAD("FFModel");
 }
-size_t FFConfig::get_hash_id(const std::string &) { return 0; }
+/* (the mapping tag of an op: the hash of its name, as src/runtime/strategy.cc:21-24 forms it) */
+size_t FFConfig::get_hash_id(const std::string &pcname) { return std::hash<std::string>()(pcname); }
 bool FFConfig::find_parallel_config(int, const std::string &, ParallelConfig &) const {
   FFREF_DEAD("FFConfig::find_parallel_config");
 }

@@ -44,6 +44,7 @@ def _common(r, n):
         # the reference maps the embedding output / output-grad to zero-copy host memory
         # (src/ops/embedding.cu:296-298, 378-380); the fused mode keeps them in framebuffer memory
         assert q["tag"] != c["MAP_TO_ZC_MEMORY"] and q["tag"] == 0
+    assert r["tag"] != 0  # the lead op's mapping tag (hash of its name)
     return c
 
 
@@ -144,3 +145,8 @@ def test_group_launchers_against_the_references_own_launchers_table_by_table(ora
         assert rb["reqs"][2]["privilege"] == ours[2]["privilege"] == c["READ_WRITE"]
         assert rb["reqs"][2]["extent"] == ours[2]["extent"] == (ROWS[t], D)
         assert rb["reqs"][2]["base"] == GRAD[t] and ours[2]["base"] == TAB[t]
+        # the mapping tag FFMapper::slice_task places the task by (src/mapper/mapper.cc:346-438): the group
+        # launch carries its LEAD op's — the hash of "embedding0", which is also the name the one-op
+        # reference launches above run under — i.e. the device of every op of the group
+        assert rf["tag"] == rb["tag"] != 0
+        assert fwd["tag"] == bwd["tag"] == rf["tag"]
